@@ -1,0 +1,78 @@
+// Shared device/host helpers for libpulse_envs: error plumbing, launch sizing, and the
+// counter-based Philox-4x32-10 chance tape.
+//
+// Chance tape: every random draw an env consumes is
+//   philox4x32_10(counter = {env_id_lo, env_id_hi, draw_counter, stream_tag},
+//                 key     = {seed_lo, seed_hi})
+// so results depend only on (seed, global env id, counter) and never on grid shape,
+// GPU count or launch order.  oracle/pulse_oracle.c holds an independent restatement.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define PULSE_OK 0
+#define PULSE_EINVAL (-1)
+#define PULSE_ENOTREADY (-2)
+#define PULSE_EUNSUPPORTED (-3)
+
+// stream tags of the chance tape
+#define PULSE_STREAM_POKER_DECK 1u
+#define PULSE_STREAM_ACTION 2u
+#define PULSE_STREAM_TFE_SPAWN 3u
+#define PULSE_STREAM_TFE_RESET 4u
+#define PULSE_STREAM_BJ_DECK 5u
+#define PULSE_STREAM_P2D_INIT 6u
+#define PULSE_STREAM_TETRIS_PIECE 7u
+
+void pulse_set_error(const char* fmt, ...);
+int pulse_check_launch(const char* what);
+
+#define PULSE_REQUIRE(cond, msg)                      \
+  do {                                                \
+    if (!(cond)) {                                    \
+      pulse_set_error("%s: %s", __func__, msg);       \
+      return PULSE_EINVAL;                            \
+    }                                                 \
+  } while (0)
+
+struct PulseU4 { uint32_t x, y, z, w; };
+
+__host__ __device__ __forceinline__ uint32_t pulse_mulhi32(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __umulhi(a, b);
+#else
+  return (uint32_t)(((uint64_t)a * (uint64_t)b) >> 32);
+#endif
+}
+
+__host__ __device__ __forceinline__ PulseU4 pulse_philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2,
+                                                                 uint32_t c3, uint32_t k0, uint32_t k1) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = pulse_mulhi32(M0, c0), lo0 = M0 * c0;
+    uint32_t hi1 = pulse_mulhi32(M1, c2), lo1 = M1 * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  PulseU4 o; o.x = c0; o.y = c1; o.z = c2; o.w = c3;
+  return o;
+}
+
+// One 4-draw block of the tape.
+__host__ __device__ __forceinline__ PulseU4 pulse_tape(uint64_t seed, uint64_t env_id, uint32_t stream,
+                                                        uint32_t counter) {
+  return pulse_philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), counter, stream,
+                             (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+
+// Grid sizing: B200 has 148 SMs; grids are a whole number of waves where the problem is big
+// enough, otherwise just enough CTAs to cover it.
+static inline int pulse_grid_for(long long n, int block, int ctas_per_sm = 8) {
+  long long need = (n + block - 1) / block;
+  long long wave = 148LL * ctas_per_sm;
+  if (need <= wave) return (int)(need > 0 ? need : 1);
+  long long waves = (need + wave - 1) / wave;
+  return (int)(waves * wave);  // grid-stride loops absorb the tail
+}
