@@ -1,0 +1,183 @@
+/* TEST INFRASTRUCTURE ONLY -- see oracle_common.h.
+ * Chance tape (Philox), an independent brute-force poker hand evaluator used to validate the
+ * regenerated HandRanks table, and the Particle2D restatement. */
+#include "oracle_common.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---- Philox-4x32-10 (Salmon et al., SC'11; Random123 constants) ------------------------------ */
+void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+  uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3], k0 = key[0], k1 = key[1];
+  for (int r = 0; r < 10; ++r) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+void oracle_tape(uint64_t seed, uint64_t env_id, uint32_t stream, uint32_t counter, uint32_t out[4]) {
+  uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), counter, stream};
+  uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+  oracle_philox4x32_10(ctr, key, out);
+}
+
+/* ---- brute-force evaluator -------------------------------------------------------------------
+ * Strength key of five cards (cards 1..52, rank = (c-1)>>2, suit = (c-1)&3): category in the top
+ * nibble then tie-break ranks, most significant first.  The 7462 distinct keys, sorted, give
+ * rank-in-category; value = (category << 12) + rank, the HandRanks convention. */
+static uint32_t key5(const int c[5]) {
+  int r[5], cnt[13] = {0};
+  int flush = 1;
+  for (int i = 0; i < 5; ++i) {
+    r[i] = (c[i] - 1) >> 2;
+    cnt[r[i]]++;
+    if (((c[i] - 1) & 3) != ((c[0] - 1) & 3)) flush = 0;
+  }
+  /* order ranks by (count desc, rank desc) */
+  int ord[5], no = 0;
+  for (int want = 4; want >= 1; --want)
+    for (int rk = 12; rk >= 0; --rk)
+      if (cnt[rk] == want) ord[no++] = rk;
+  int distinct = no;
+  int straight = 0, top = 0;
+  if (distinct == 5) {
+    if (ord[0] - ord[4] == 4) { straight = 1; top = ord[0]; }
+    else if (ord[0] == 12 && ord[1] == 3 && ord[4] == 0) { straight = 1; top = 3; }
+  }
+  int cat;
+  if (straight && flush) cat = 9;
+  else if (cnt[ord[0]] == 4) cat = 8;
+  else if (cnt[ord[0]] == 3 && distinct == 2) cat = 7;
+  else if (flush) cat = 6;
+  else if (straight) cat = 5;
+  else if (cnt[ord[0]] == 3) cat = 4;
+  else if (cnt[ord[0]] == 2 && distinct == 3) cat = 3;
+  else if (cnt[ord[0]] == 2) cat = 2;
+  else cat = 1;
+  uint32_t k = (uint32_t)cat << 20;
+  if (straight) return k | ((uint32_t)top << 16);
+  for (int i = 0; i < distinct; ++i) k |= (uint32_t)ord[i] << (16 - 4 * i);
+  return k;
+}
+
+static uint32_t g_keys[7462];
+static int g_nkeys = 0;
+static int g_cat_start[11];
+
+static int cmp_u32(const void* a, const void* b) {
+  uint32_t x = *(const uint32_t*)a, y = *(const uint32_t*)b;
+  return x < y ? -1 : x > y;
+}
+
+static void init_keys(void) {
+  if (g_nkeys) return;
+  uint32_t* all = (uint32_t*)malloc(2598960 * sizeof(uint32_t));
+  int n = 0, c[5];
+  for (c[0] = 1; c[0] <= 52; ++c[0])
+    for (c[1] = c[0] + 1; c[1] <= 52; ++c[1])
+      for (c[2] = c[1] + 1; c[2] <= 52; ++c[2])
+        for (c[3] = c[2] + 1; c[3] <= 52; ++c[3])
+          for (c[4] = c[3] + 1; c[4] <= 52; ++c[4]) all[n++] = key5(c);
+  qsort(all, n, sizeof(uint32_t), cmp_u32);
+  int m = 0;
+  for (int i = 0; i < n; ++i)
+    if (i == 0 || all[i] != all[i - 1]) g_keys[m++] = all[i];
+  free(all);
+  for (int cat = 0; cat <= 10; ++cat) g_cat_start[cat] = m;
+  for (int i = m - 1; i >= 0; --i) g_cat_start[g_keys[i] >> 20] = i;
+#pragma omp critical
+  g_nkeys = m;
+}
+
+int oracle_num_hand_classes(void) { init_keys(); return g_nkeys; }
+
+/* value of the best five of n (5..7) cards */
+int oracle_eval_bruteforce(const int32_t* cards, int n) {
+  init_keys();
+  uint32_t best = 0;
+  int c[5];
+  for (int a = 0; a < n; ++a)
+    for (int b = a + 1; b < n; ++b)
+      for (int d = b + 1; d < n; ++d)
+        for (int e = d + 1; e < n; ++e)
+          for (int f = e + 1; f < n; ++f) {
+            c[0] = cards[a]; c[1] = cards[b]; c[2] = cards[d]; c[3] = cards[e]; c[4] = cards[f];
+            uint32_t k = key5(c);
+            if (k > best) best = k;
+          }
+  uint32_t* p = (uint32_t*)bsearch(&best, g_keys, g_nkeys, sizeof(uint32_t), cmp_u32);
+  int idx = (int)(p - g_keys);
+  int cat = (int)(best >> 20);
+  return (cat << 12) + (idx - g_cat_start[cat] + 1);
+}
+
+/* the reference's walk: p = 53; p = HR[p + card]...; 5/6 cards take one more HR[p]
+ * (PokerGPU.py:437-444, :497-500) */
+int oracle_handranks_walk(const int32_t* hr, const int32_t* cards, int n) {
+  int p = 53;
+  for (int i = 0; i < n; ++i) p = hr[p + cards[i]];
+  if (n < 7) p = hr[p];
+  return p;
+}
+
+/* Full check of a HandRanks table against the brute-force evaluator over every 7-card hand
+ * (133,784,560; OpenMP) when stride == 1, or every stride-th hand.  compare != 0 also evaluates each
+ * visited hand by brute force (21 five-card subsets).  Returns the number of mismatches; fills
+ * cat_counts[10], min7, max7. */
+long long oracle_check_table7(const int32_t* hr, int stride, int compare, long long* cat_counts, int* min7,
+                              int* max7) {
+  init_keys();
+  long long bad = 0;
+  long long cc[10] = {0};
+  int mn = 1 << 30, mx = 0;
+#pragma omp parallel for schedule(dynamic) reduction(+ : bad) reduction(min : mn) reduction(max : mx) reduction(+ : cc[:10])
+  for (int a = 1; a <= 46; ++a) {
+    long long idx = 0;
+    int32_t c[7];
+    c[0] = a;
+    for (c[1] = a + 1; c[1] <= 47; ++c[1])
+      for (c[2] = c[1] + 1; c[2] <= 48; ++c[2])
+        for (c[3] = c[2] + 1; c[3] <= 49; ++c[3])
+          for (c[4] = c[3] + 1; c[4] <= 50; ++c[4])
+            for (c[5] = c[4] + 1; c[5] <= 51; ++c[5])
+              for (c[6] = c[5] + 1; c[6] <= 52; ++c[6]) {
+                if ((idx++ % stride) != 0) continue;
+                int v = oracle_handranks_walk(hr, c, 7);
+                cc[v >> 12 < 10 ? v >> 12 : 0]++;
+                if (v < mn) mn = v;
+                if (v > mx) mx = v;
+                if (compare && v != oracle_eval_bruteforce(c, 7)) bad++;
+              }
+  }
+  for (int i = 0; i < 10; ++i) cat_counts[i] = cc[i];
+  *min7 = mn; *max7 = mx;
+  return bad;
+}
+
+/* ---- Particle2D (environments/Particle2D/Particle2D.py:22-30) ------------------------------- */
+void oracle_particle2d_step(float* state, const float* action, int32_t* steps, float* reward,
+                            uint8_t* terminated, float dt, int max_steps, int n) {
+#pragma omp parallel for if (n > 65536)
+  for (int i = 0; i < n; ++i) {
+    float ax = action[2 * i], ay = action[2 * i + 1];
+    ax = ax < -1.f ? -1.f : (ax > 1.f ? 1.f : ax);                       /* :23 clamp */
+    ay = ay < -1.f ? -1.f : (ay > 1.f ? 1.f : ay);
+    float* s = state + 4 * i;
+    volatile float t;
+    t = ax * dt; s[2] = s[2] + t;                                         /* :24 vel += a*dt */
+    t = ay * dt; s[3] = s[3] + t;
+    t = s[2] * dt; s[0] = s[0] + t;                                       /* :25 pos += vel*dt */
+    t = s[3] * dt; s[1] = s[1] + t;
+    volatile float xx = s[0] * s[0], yy = s[1] * s[1];
+    float dist = sqrtf(xx + yy);                                          /* :26 */
+    volatile float a2x = ax * ax, a2y = ay * ay;
+    volatile float pen = 0.001f * (a2x + a2y);
+    reward[i] = -dist - pen;                                              /* :27 */
+    steps[i] += 1;                                                        /* :28 */
+    terminated[i] = (uint8_t)((dist < 0.1f) | (steps[i] >= max_steps));   /* :29 */
+  }
+}

@@ -1,0 +1,121 @@
+"""TEST INFRASTRUCTURE ONLY.  ctypes front-end of the C oracle (oracle/*.c).  Imported by tests/,
+__graft_entry__.smoke() and bench.py's CPU-baseline legs; never by pulselib_b200."""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+_DIR = Path(__file__).resolve().parent
+_SO = _DIR / "_build" / "liboracle.so"
+_LIB = None
+
+
+def build(force: bool = False) -> Path:
+    srcs = list(_DIR.glob("*.c")) + list(_DIR.glob("*.h"))
+    if force or not _SO.exists() or any(s.stat().st_mtime > _SO.stat().st_mtime for s in srcs):
+        r = subprocess.run(["make", "-C", str(_DIR)] + (["-B"] if force else []), capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"oracle build failed:\n{r.stdout}\n{r.stderr}")
+    return _SO
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        build()
+        _LIB = C.CDLL(str(_SO))
+        _LIB.oracle_check_table7.restype = C.c_longlong
+    return _LIB
+
+
+def p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+class PokerStruct(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("n_games", "n_players", "active_players", "max_players",
+                                         "starting_bbs", "max_bbs", "K", "alpha")] + \
+               [("w1", C.c_float), ("w2", C.c_float)] + \
+               [(n, C.c_void_p) for n in ("decks", "deck_positions", "board", "pots", "stages", "stacks", "hands",
+                                          "current_round_bet", "total_invested", "status", "button", "sb", "bb",
+                                          "idx", "highest", "agg", "acted", "last_raise_size", "prev_invested",
+                                          "is_done", "equity_dirty", "equities", "hand_ranks")] + \
+               [("n_hand_ranks", C.c_int64)]
+
+
+INT_FIELDS_N = ("deck_positions", "pots", "stages", "button", "sb", "bb", "idx", "highest", "agg", "acted",
+                "last_raise_size", "prev_invested")
+INT_FIELDS_NP = ("stacks", "current_round_bet", "total_invested", "status")
+
+
+class OraclePoker:
+    """Reference-shaped PokerGPU on numpy arrays, stepped by oracle_poker.c."""
+
+    def __init__(self, hand_ranks, n_players=6, max_players=10, n_games=100, starting_bbs=100, max_bbs=1000,
+                 w1=.5, w2=.5, K=20, alpha=300):
+        self.L = lib()
+        N, P = n_games, n_players
+        self.n_games, self.n_players, self.max_players = N, P, max_players
+        self.obs_size = 13 + (max_players - 1) * 3
+        self.hand_ranks = np.ascontiguousarray(hand_ranks, dtype=np.int32)
+        self.decks = np.zeros((N, 52), np.int32)
+        self.board = np.full((N, 5), -1, np.int32)
+        self.hands = np.full((N, P, 2), -1, np.int32)
+        for f in INT_FIELDS_N:
+            setattr(self, f, np.zeros(N, np.int32))
+        for f in INT_FIELDS_NP:
+            setattr(self, f, np.zeros((N, P), np.int32))
+        self.is_done = np.zeros(N, np.uint8)
+        self.equity_dirty = np.zeros(N, np.uint8)
+        self._eq = np.zeros(N * P, np.float32)
+        self.active_players = P
+        self._first = True
+        self.s = PokerStruct()
+        for k, v in dict(n_games=N, n_players=P, active_players=P, max_players=max_players,
+                         starting_bbs=starting_bbs, max_bbs=max_bbs, K=K, alpha=alpha, w1=w1, w2=w2).items():
+            setattr(self.s, k, v)
+        self._sync()
+        self.obs = np.zeros((N, self.obs_size), np.float32)
+        self.rewards = np.zeros(N, np.float32)
+
+    @property
+    def equities(self):
+        return self._eq[: self.n_games * self.active_players].reshape(self.n_games, self.active_players)
+
+    def _sync(self):
+        for n in ("decks", "board", "hands", "is_done", "equity_dirty") + INT_FIELDS_N + INT_FIELDS_NP:
+            setattr(self.s, n, getattr(self, n).ctypes.data)
+        self.s.equities = self._eq.ctypes.data
+        self.s.hand_ranks = self.hand_ranks.ctypes.data
+        self.s.n_hand_ranks = self.hand_ranks.size
+        self.s.active_players = self.active_players
+
+    def tape_decks(self, seed, env_base, hand):
+        d = np.zeros(52, np.int32)
+        for g in range(self.n_games):
+            self.L.oracle_poker_tape_deck(C.c_uint64(seed), C.c_uint64(env_base + g), C.c_uint32(hand), p(d))
+            self.decks[g] = d
+
+    def reset(self, decks=None, active_players=None, rotation=0):
+        if decks is not None:
+            self.decks[...] = decks
+        self.active_players = active_players or self.n_players
+        self._sync()
+        self.L.oracle_poker_reset(C.byref(self.s), C.c_int(self.active_players), C.c_int(self._first),
+                                  C.c_int(rotation))
+        self._first = False
+        self.L.oracle_poker_get_obs(C.byref(self.s), p(self.obs))
+        return self.obs
+
+    def step(self, actions, use_cached_equities=False):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        self._sync()
+        self.L.oracle_poker_step(C.byref(self.s), p(a), p(self.obs), p(self.rewards), C.c_int(use_cached_equities))
+        return self.obs, self.rewards, self.is_done.astype(bool)
+
+    def call(self, name, *args):
+        self._sync()
+        getattr(self.L, "oracle_poker_" + name)(C.byref(self.s), *args)
