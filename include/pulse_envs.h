@@ -1,0 +1,126 @@
+/* libpulse_envs -- C ABI of the B200-native batched env-step engine.
+ *
+ * The reference (cerredz/Pulselib) has no FFI: its env step is Python (torch eager / numba).  The
+ * boundary this library sits behind is therefore the Python gym.Env class contract; each entry
+ * point below names the reference method it replaces.  pulselib_b200/envs/ binds these with ctypes
+ * (see INTEGRATION.md for the stub a Pulselib maintainer would add).
+ *
+ * Conventions for every call:
+ *   - returns 0 on success, a negative PULSE_E* code for bad arguments, or a positive cudaError_t;
+ *     pulse_last_error() then holds a thread-local message;
+ *   - never allocates, frees or retains caller buffers; never synchronises the stream;
+ *   - unless a parameter says "host", pointers are device pointers the caller keeps alive until the
+ *     stream has run the call; `stream` is a cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream);
+ *   - the caller's current CUDA device must be the one owning the buffers;
+ *   - thread-compatible: concurrent calls on different envs/streams are fine.
+ */
+#ifndef PULSE_ENVS_H
+#define PULSE_ENVS_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* pulse_stream_t; /* == cudaStream_t */
+
+#define PULSE_OK 0
+#define PULSE_EINVAL (-1)
+#define PULSE_ENOTREADY (-2)
+#define PULSE_EUNSUPPORTED (-3)
+
+int pulse_version(void);
+const char* pulse_last_error(void);
+
+/* ---- chance tape ------------------------------------------------------------------------------
+ * Philox-4x32-10, counter {env_id lo, env_id hi, draw counter, stream tag}, key = seed.  Host
+ * helper so callers can materialise the draws the kernels consume. */
+int pulse_tape_block(uint64_t seed, uint64_t env_id, uint32_t stream_tag, uint32_t counter, uint32_t* host_out4);
+
+/* ---- HandRanks table (replaces the HandRanks.dat download, PokerGPU.py:47-58) ------------------ */
+size_t pulse_handranks_entries(void);                                   /* 32,487,834 */
+int pulse_handranks_generate(int32_t* host_out, size_t n_entries);      /* host, ~6 s */
+int pulse_handranks_walk(const int32_t* host_table, const int32_t* host_cards, int n_cards);
+int pulse_eval_cards(const int32_t* host_cards, int n_cards);           /* computed evaluator, host */
+/* computed evaluator on the device: cards int32 [n, n_cards] (5..7), out int32 [n] */
+int pulse_poker_eval_batch(const int32_t* cards, int n_cards, int32_t* out, int n, pulse_stream_t stream);
+
+/* ---- Particle2D (environments/Particle2D/Particle2D.py:15-30) --------------------------------- */
+int pulse_particle2d_reset(float* state /*[N,4]*/, int32_t* steps, uint8_t* terminated, float* obs_out /*[N,4]*/,
+                           uint64_t seed, uint64_t env_base, uint32_t episode, int n_envs, pulse_stream_t stream);
+int pulse_particle2d_step(float* state /*[N,4]*/, const float* action /*[N,2]*/, int32_t* steps,
+                          float* obs_out /*[N,4]*/, float* reward_out, uint8_t* terminated_out,
+                          uint8_t* truncated_out_or_null, float dt, int max_steps, int n_envs,
+                          pulse_stream_t stream);
+
+/* ---- PokerGPU, reference-shaped layout (environments/Poker/PokerGPU.py) ----------------------- */
+/* One device pointer per tensor attribute of the reference env, same shapes and dtypes (int32,
+ * row-major; is_done / equity_dirty are torch.bool = 1 byte). */
+typedef struct PulsePokerState {
+  int32_t* decks;             /* [N,52] 1..52                        PokerGPU.py:86-92  */
+  int32_t* deck_positions;    /* [N]                                 :93  */
+  int32_t* board;             /* [N,5], -1 = not dealt               :95  */
+  int32_t* pots;              /* [N]                                 :96  */
+  int32_t* stages;            /* [N] 0..5                            :97  */
+  int32_t* stacks;            /* [N,P]                               :101-110 */
+  int32_t* hands;             /* [N,P,2]                             :112-114 */
+  int32_t* current_round_bet; /* [N,P]                               :116 */
+  int32_t* total_invested;    /* [N,P]                               :117 */
+  int32_t* status;            /* [N,P] 0 ACTIVE 1 FOLDED 2 ALLIN 3 SITOUT  :118-119 */
+  int32_t* button;            /* [N]                                 :121 */
+  int32_t* sb;                /* [N]                                 :123-128 */
+  int32_t* bb;                /* [N] */
+  int32_t* idx;               /* [N] seat to act                     :130-133 */
+  int32_t* highest;           /* [N]                                 :134 */
+  int32_t* agg;               /* [N]                                 :135 */
+  int32_t* acted;             /* [N]                                 :136 */
+  int32_t* last_raise_size;   /* [N]                                 :81  */
+  int32_t* prev_invested;     /* [N]                                 :151 */
+  uint8_t* is_done;           /* [N]                                 :137 */
+  uint8_t* equity_dirty;      /* [N]                                 :145 */
+  float* equities;            /* [N,AP]                              :144 */
+  const int32_t* hand_ranks;  /* HandRanks table on the device       :47-58 */
+  int64_t n_hand_ranks;
+} PulsePokerState;
+
+typedef struct PulsePokerConfig {
+  int32_t n_games, n_players, active_players, max_players;
+  int32_t starting_bbs, max_bbs;
+  int32_t K, alpha;
+  float w1, w2;
+} PulsePokerConfig;
+
+/* reset (PokerGPU.py:73-157).  prefixed_decks_or_null: int32 [N,52] copied into st->decks; NULL
+ * draws each deck from the chance tape (seed, env_base + table, hand_counter).  first_reset != 0:
+ * stacks = starting_bbs and button = 0; otherwise busted/oversized stacks are refilled, rolled by
+ * `rotation` and the button advances.  Writes the first observation [N, 13+3(M-1)]. */
+int pulse_poker_reset(const PulsePokerState* st, const PulsePokerConfig* cfg, const int32_t* prefixed_decks_or_null,
+                      uint64_t seed, uint64_t env_base, uint32_t hand_counter, int rotation, int first_reset,
+                      float* obs_out, pulse_stream_t stream);
+
+/* Phases of a step, in the reference's order (PokerGPU.py:527-633). */
+#define PULSE_POKER_EQUITIES 1        /* calculate_equities           :455-525 */
+#define PULSE_POKER_EXECUTE 2         /* execute_actions              :230-303 */
+#define PULSE_POKER_ADVANCE 4         /* next actor + street change   :547-616 */
+#define PULSE_POKER_FOLD_WINNERS 8    /* resolve_fold_winners         :331-338 */
+#define PULSE_POKER_SHOWDOWN 16       /* resolve_terminated_games     :380-453 */
+#define PULSE_POKER_CLEAR_DONE 32     /*                              :625-628 */
+#define PULSE_POKER_REWARD 64         /* poker_reward_gpu             :305-329 */
+#define PULSE_POKER_OBS 128           /* get_obs                      :159-179 */
+#define PULSE_POKER_STEP 255
+#define PULSE_POKER_NEWLY_IS_DONE 256 /* resolve_* called directly: is_done is the mask */
+#define PULSE_POKER_RAW_REWARD 512    /* reward for actor_idx[], not masked by legality */
+
+/* step (PokerGPU.py:527-633) = one fused launch with phases = PULSE_POKER_STEP.  The reference's
+ * internal methods are the same kernel with a single phase bit.  actions int64 [N]; done_out may
+ * alias st->is_done (the reference rebinds is_done to a new tensor each step, :623).  Any of
+ * obs_out / reward_out may be NULL when its phase is not requested. */
+int pulse_poker_step(const PulsePokerState* st, const PulsePokerConfig* cfg, const int64_t* actions,
+                     const int32_t* actor_idx_or_null, uint32_t phases, float* obs_out, float* reward_out,
+                     uint8_t* done_out, pulse_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -10,10 +10,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define PULSE_OK 0
-#define PULSE_EINVAL (-1)
-#define PULSE_ENOTREADY (-2)
-#define PULSE_EUNSUPPORTED (-3)
+#include "pulse_envs.h"
 
 // stream tags of the chance tape
 #define PULSE_STREAM_POKER_DECK 1u
@@ -36,6 +33,43 @@ int pulse_check_launch(const char* what);
   } while (0)
 
 struct PulseU4 { uint32_t x, y, z, w; };
+
+struct PulseI2 { int32_t x, y; };
+__host__ __device__ __forceinline__ PulseI2 pulse_ld_int2(const int32_t* p) {  // 8-byte aligned pair
+#ifdef __CUDA_ARCH__
+  int2 v = *reinterpret_cast<const int2*>(p);
+  PulseI2 r; r.x = v.x; r.y = v.y; return r;
+#else
+  PulseI2 r; r.x = p[0]; r.y = p[1]; return r;
+#endif
+}
+
+// Per-env logic is written as __host__ __device__ functions so that tests/hostemu can compile the
+// very same code for the CPU and check it against the oracle without a GPU.  The product library
+// only ever launches the __global__ wrappers.
+#define PULSE_HD __host__ __device__ __forceinline__
+#ifdef __CUDA_ARCH__
+#define PULSE_POPC(x) __popc(x)
+#define PULSE_FFS(x) __ffs(x)
+#define PULSE_FMUL(a, b) __fmul_rn(a, b)
+#define PULSE_FADD(a, b) __fadd_rn(a, b)
+#define PULSE_FSUB(a, b) __fsub_rn(a, b)
+#define PULSE_FDIV(a, b) __fdiv_rn(a, b)
+#define PULSE_FSQRT(a) __fsqrt_rn(a)
+#define PULSE_F2I_RZ(a) __float2int_rz(a)
+#define PULSE_LDG(p) __ldg(p)
+#else
+#include <math.h>
+#define PULSE_POPC(x) __builtin_popcount(x)
+#define PULSE_FFS(x) __builtin_ffs(x)
+#define PULSE_FMUL(a, b) ((a) * (b))
+#define PULSE_FADD(a, b) ((a) + (b))
+#define PULSE_FSUB(a, b) ((a) - (b))
+#define PULSE_FDIV(a, b) ((a) / (b))
+#define PULSE_FSQRT(a) sqrtf(a)
+#define PULSE_F2I_RZ(a) ((int)(a))
+#define PULSE_LDG(p) (*(p))
+#endif
 
 __host__ __device__ __forceinline__ uint32_t pulse_mulhi32(uint32_t a, uint32_t b) {
 #ifdef __CUDA_ARCH__

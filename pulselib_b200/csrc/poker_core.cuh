@@ -1,0 +1,289 @@
+// PokerGPU per-table step logic, shared by the reference-shaped ("compat") kernels and the packed
+// throughput kernels.  One thread owns one table; the whole table lives in registers between one
+// load and one store.  Semantics follow /root/reference/environments/Poker/PokerGPU.py:527-633
+// (SURVEY.md Appendix A); line cites are to that file.
+#pragma once
+#include "common.cuh"
+#include "poker_eval.cuh"
+#include <limits.h>
+
+enum { PK_ACTIVE = 0, PK_FOLDED = 1, PK_ALLIN = 2, PK_SITOUT = 3 };  // :11
+
+// phases of a step; the fused kernel runs PK_PH_STEP, the sub-step entry points run one bit
+enum {
+  PK_PH_EQUITY = 1, PK_PH_EXECUTE = 2, PK_PH_ADVANCE = 4, PK_PH_FOLDWIN = 8, PK_PH_SHOWDOWN = 16,
+  PK_PH_CLEAR = 32, PK_PH_REWARD = 64, PK_PH_OBS = 128, PK_PH_STEP = 255,
+  PK_PH_NEWLY_IS_DONE = 256,  // resolve_* called on their own: is_done is the "newly done" mask (:620)
+  PK_PH_RAW_REWARD = 512      // poker_reward_gpu on its own: no legality masking, actor given
+};
+
+struct PokerParams {
+  float w1, w2;
+  int K, alpha;
+  int P, AP, M;  // n_players, active_players, max_players
+};
+
+template <int MAXP>
+struct PokerTable {
+  int32_t stack[MAXP], crb[MAXP], inv[MAXP];
+  int32_t hole0[MAXP], hole1[MAXP];
+  uint32_t st;  // status bit-planes: bit s = low bit of seat s, bit 16+s = high bit
+  int32_t pot, highest, last_raise;
+  int32_t board[5];  // -1 = not dealt
+  int32_t stage, idx, agg, acted, button, deck_pos;
+  bool done, dirty;
+};
+
+template <int MAXP>
+PULSE_HD int32_t pk_sel(const int32_t (&a)[MAXP], int i) {
+  int32_t v = a[0];
+#pragma unroll
+  for (int s = 1; s < MAXP; ++s) if (i == s) v = a[s];
+  return v;
+}
+template <int MAXP>
+PULSE_HD void pk_put(int32_t (&a)[MAXP], int i, int32_t v) {
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) if (i == s) a[s] = v;
+}
+
+PULSE_HD int pk_status(uint32_t st, int s) { return ((st >> s) & 1u) | (((st >> (16 + s)) & 1u) << 1); }
+PULSE_HD uint32_t pk_set_status(uint32_t st, int s, int v) {
+  uint32_t lo = 1u << s, hi = 1u << (16 + s);
+  st &= ~(lo | hi);
+  if (v & 1) st |= lo;
+  if (v & 2) st |= hi;
+  return st;
+}
+PULSE_HD uint32_t pk_seatmask(int n) { return (1u << n) - 1u; }
+PULSE_HD uint32_t pk_active_mask(uint32_t st, int n) { return ~(st | (st >> 16)) & pk_seatmask(n); }
+PULSE_HD uint32_t pk_allin_mask(uint32_t st, int n) { return (st >> 16) & ~st & pk_seatmask(n); }
+PULSE_HD uint32_t pk_live_mask(uint32_t st, int n) { return ~st & pk_seatmask(n); }  // ACTIVE|ALLIN: low bit clear
+
+// first ACTIVE seat scanning (from+1 .. from+AP) % AP, or -1 (:554-561, :215-228)
+PULSE_HD int pk_next_active(uint32_t st, int from, int AP) {
+  uint32_t a = pk_active_mask(st, AP);
+  if (!a) return -1;
+  uint32_t above = a & ~((2u << from) - 1u);
+  return PULSE_FFS(above ? above : a) - 1;
+}
+
+// The reference's hand-strength proxy for one seat (:455-525).  stage 3: 7-card value; stage 2:
+// 6-card value; stage 1: HR[HR[p5]] where HR[p5] is the 5-card value, i.e. one real lookup into the
+// low part of the table (only its first 36,875 entries are ever touched).
+PULSE_HD float pk_equity(int stage, int h0, int h1, const int32_t (&board)[5],
+                                           const int32_t* __restrict__ hand_ranks, long long n_hr) {
+  if (stage < 1 || stage > 3) return 0.5f;  // :461
+  uint32_t m[4] = {0, 0, 0, 0};
+  pe_add_card(h0, m); pe_add_card(h1, m);
+  pe_add_card(board[0], m); pe_add_card(board[1], m); pe_add_card(board[2], m);
+  if (stage >= 2) pe_add_card(board[3], m);
+  if (stage >= 3) pe_add_card(board[4], m);
+  int v = pe_eval_suits(m[0], m[1], m[2], m[3]);
+  float lo = 4109.0f, den = 32765.0f;  // :17-18, :65
+  if (stage == 1) {
+    v = (v >= 0 && v < n_hr) ? PULSE_LDG(hand_ranks + v) : 0;  // :521
+    lo = 74359.0f; den = 749420.0f;                        // :15-16, :66
+  }
+  float e = PULSE_FDIV(PULSE_FSUB((float)v, lo), den);
+  return fminf(fmaxf(e, 0.0f), 1.0f);
+}
+
+// execute_actions for the seat to act (:230-303)
+template <int MAXP>
+PULSE_HD void pk_execute(PokerTable<MAXP>& t, long long a) {
+  const int idx = t.idx;
+  int stat = pk_status(t.st, idx);
+  if (stat != PK_ACTIVE || t.done) return;  // :233
+  if (a < 0) return;                        // matches no mask in the reference
+  int stack = pk_sel(t.stack, idx), crb = pk_sel(t.crb, idx), inv = pk_sel(t.inv, idx);
+  int call_cost = t.highest - crb;  // :232
+  if (a == 0) {                     // :236-238
+    t.st = pk_set_status(t.st, idx, PK_FOLDED);
+    t.acted += 1;
+    return;
+  }
+  int bet;
+  bool is_raise = false;
+  if (a == 1) {  // :241-252
+    bet = call_cost < stack ? call_cost : stack;
+  } else {       // :255-303
+    int raise_amt = 0;
+    if (a == 2) raise_amt = t.last_raise;  // :259
+    else if (a == 12) raise_amt = stack;   // :264
+    else if (a <= 11) {
+      const float fr[9] = {0.25f, 0.33f, 0.50f, 0.75f, 1.00f, 1.50f, 2.00f, 3.00f, 4.00f};  // :39
+      float f = fr[0];
+#pragma unroll
+      for (int k = 1; k < 9; ++k) if (a - 3 == k) f = fr[k];
+      raise_amt = PULSE_F2I_RZ(PULSE_FMUL((float)t.pot, f));  // :270 one fp32 multiply, truncation
+    }
+    bet = (call_cost + raise_amt) < stack ? (call_cost + raise_amt) : stack;  // :272-273
+    is_raise = bet > call_cost;               // :274-275
+  }
+  stack -= bet; crb += bet; inv += bet; t.pot += bet;
+  if (stack == 0) t.st = pk_set_status(t.st, idx, PK_ALLIN);
+  pk_put(t.stack, idx, stack); pk_put(t.crb, idx, crb); pk_put(t.inv, idx, inv);
+  if (is_raise) {  // :288-301
+    int size = crb - t.highest;
+    t.highest = crb;
+    if (size >= t.last_raise) { t.agg = idx; t.acted = 0; t.last_raise = size; }
+  }
+  t.acted += 1;  // :252, :303
+}
+
+// next actor, round close, street transition (:547-616).  Deck::card(pos) returns the card at a
+// deck position of this table.
+template <int MAXP, class Deck>
+PULSE_HD void pk_advance(PokerTable<MAXP>& t, const PokerParams& pr, const Deck& deck) {
+  const int P = pr.P, AP = pr.AP;
+  int truly_active = PULSE_POPC(pk_active_mask(t.st, P));      // :547
+  bool all_acted = t.acted >= truly_active;                // :549
+  bool round_over = t.done || truly_active == 0;           // :552-553
+  int nxt = pk_next_active(t.st, t.idx, AP);               // :554-561
+  if (!round_over)                                         // :562-569
+    round_over = nxt < 0 || (all_acted && t.idx == t.agg) || (all_acted && nxt == t.agg);
+  if (!round_over && nxt >= 0) t.idx = nxt;                // :571-573
+  int lc = PULSE_POPC(pk_live_mask(t.st, P));                  // :576
+  bool early = lc <= 1 && round_over;                      // :577
+  if (early) t.done = true;                                // :578
+  if (round_over && !early && !t.done) {                   // :580
+    t.last_raise = 1;                                      // :581
+    t.stage += 1;                                          // :584
+    t.highest = 0;                                         // :585
+    t.agg = (t.button + 1) % AP;                           // :586
+    t.acted = 0;                                           // :587
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) t.crb[s] = 0;           // :588
+    int first = pk_next_active(t.st, t.button, AP);        // :589
+    if (first >= 0) t.idx = first;
+    if (t.stage > 3) { t.done = true; t.stage = 4; }       // :595-598
+    else if (t.stage == 1) {                               // :601-604
+      t.deck_pos += 1;
+      t.board[0] = deck.card(t.deck_pos); t.board[1] = deck.card(t.deck_pos + 1); t.board[2] = deck.card(t.deck_pos + 2);
+      t.deck_pos += 3; t.dirty = true;
+    } else if (t.stage == 2) {                             // :607-610
+      t.deck_pos += 1; t.board[3] = deck.card(t.deck_pos); t.deck_pos += 1; t.dirty = true;
+    } else {                                               // :613-616
+      t.deck_pos += 1; t.board[4] = deck.card(t.deck_pos); t.deck_pos += 1; t.dirty = true;
+    }
+  }
+}
+
+// resolve_fold_winners (:331-338): exactly one live seat takes the pot
+template <int MAXP>
+PULSE_HD void pk_fold_winner(PokerTable<MAXP>& t, const PokerParams& pr) {
+  uint32_t live = pk_live_mask(t.st, pr.P);
+  if (PULSE_POPC(live) != 1) return;
+  int w = PULSE_FFS(live) - 1;
+  pk_put(t.stack, w, pk_sel(t.stack, w) + t.pot);
+  t.pot = 0;
+}
+
+// resolve_terminated_games + _award_showdown_side_pots (:380-453, :340-378)
+template <int MAXP, class Deck>
+PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck& deck) {
+  const int P = pr.P, AP = pr.AP;
+  if (!(t.stage < 5)) return;                               // :386
+  uint32_t live = pk_live_mask(t.st, P);
+  if (!(PULSE_POPC(live) > 1)) return;                          // :390
+  if (t.stage == 0) {                                       // :397-405
+    t.deck_pos += 1;
+    t.board[0] = deck.card(t.deck_pos); t.board[1] = deck.card(t.deck_pos + 1); t.board[2] = deck.card(t.deck_pos + 2);
+    t.deck_pos += 3;
+  }
+  if (t.stage <= 1) { t.deck_pos += 1; t.board[3] = deck.card(t.deck_pos); t.deck_pos += 1; }  // :407-411
+  if (t.stage <= 2) { t.deck_pos += 1; t.board[4] = deck.card(t.deck_pos); t.deck_pos += 1; }  // :416-419
+  uint32_t bm[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int i = 0; i < 5; ++i) pe_add_card(t.board[i], bm);
+  int32_t rank[MAXP];
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {                          // :427-450
+    rank[s] = INT_MIN;
+    if (s < AP && ((live >> s) & 1u)) {
+      uint32_t m[4] = {bm[0], bm[1], bm[2], bm[3]};
+      pe_add_card(t.hole0[s], m); pe_add_card(t.hole1[s], m);
+      rank[s] = pe_eval_suits(m[0], m[1], m[2], m[3]);
+    }
+  }
+  // side pots: one layer per distinct investment level, ascending (:346-378).  Iterating seats as
+  // "level = inv[k]" and skipping levels already handled equals the reference's sorted layers:
+  // duplicate levels have size 0 there.
+  int32_t prev_level = 0;
+  for (int layer = 0; layer < AP; ++layer) {
+    int32_t level = INT_MAX;  // smallest investment above prev_level
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s)
+      if (s < AP && t.inv[s] > prev_level && t.inv[s] < level) level = t.inv[s];
+    if (level == INT_MAX) break;
+    int contributors = 0, winners = 0, first = -1;
+    int32_t best = INT_MIN;
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s)
+      if (s < AP && t.inv[s] >= level) {
+        contributors++;
+        if (((live >> s) & 1u) && rank[s] > best) best = rank[s];
+      }
+#pragma unroll
+    for (int s = MAXP - 1; s >= 0; --s)
+      if (s < AP && t.inv[s] >= level && ((live >> s) & 1u) && rank[s] == best) { winners++; first = s; }
+    int32_t pot = (level - prev_level) * contributors;      // :359-360
+    if (winners > 0) {                                      // :362
+      int32_t share = pot / winners, rem = pot - share * winners;
+#pragma unroll
+      for (int s = 0; s < MAXP; ++s)
+        if (s < AP && t.inv[s] >= level && ((live >> s) & 1u) && rank[s] == best)
+          t.stack[s] += share + (s == first ? rem : 0);     // :374-378
+    }
+    prev_level = level;
+  }
+  t.pot = 0; t.stage = 5;                                   // :452-453
+}
+
+// poker_reward_gpu (:305-329), fp32 with one rounding per op like the eager reference
+template <int MAXP>
+PULSE_HD float pk_reward(const PokerTable<MAXP>& t, const PokerParams& pr, long long a,
+                                           float e, int prev_inv) {
+  float cnt = (float)PULSE_POPC(pk_live_mask(t.st, pr.P));       // :309
+  float fair = PULSE_FDIV(1.0f, fmaxf(cnt, 1.0f));            // :310
+  int cc = t.highest - prev_inv; if (cc < 0) cc = 0;                     // :311
+  float pot = (float)t.pot;
+  float m = PULSE_FMUL(e, pot);                               // :315
+  float o = PULSE_FDIV((float)cc, PULSE_FADD((float)(t.pot + cc), 1e-6f));  // :316
+  float s = 0.0f;
+  if (a == 1) s = PULSE_FMUL(PULSE_FSUB(e, o), pot);           // :326
+  else if (a == 0) s = PULSE_FMUL(PULSE_FSUB(o, e), pot);      // :327
+  else if (a >= 2) s = PULSE_FMUL(PULSE_FSUB(e, fair), pot);   // :328
+  float x = PULSE_FDIV(PULSE_FADD(PULSE_FMUL(pr.w1, m), PULSE_FMUL(pr.w2, s)), (float)pr.K);
+  return PULSE_FMUL((float)pr.alpha, tanhf(x));               // :329
+}
+
+// get_obs row (:159-179); o must hold 13 + 3*(M-1) floats
+template <int MAXP>
+PULSE_HD void pk_obs(const PokerTable<MAXP>& t, const PokerParams& pr, float* o) {
+  const int AP = pr.AP, W = 13 + 3 * (pr.M - 1);
+  const int idx = t.idx;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) o[i] = (float)t.board[i];
+  o[5] = (float)pk_sel(t.hole0, idx);
+  o[6] = (float)pk_sel(t.hole1, idx);
+  o[7] = (float)t.stage;
+  int rel = (idx - t.button) % AP;
+  if (rel < 0) rel += AP;
+  o[8] = (float)rel;
+  o[9] = (float)t.pot;
+  o[10] = (float)(t.highest - pk_sel(t.crb, idx));
+  o[11] = (float)pk_sel(t.stack, idx);
+  o[12] = (float)pk_status(t.st, idx);
+  int seat = idx;
+  for (int k = 1; k < pr.M; ++k) {
+    float a = 0.0f, b = 0.0f, c = 0.0f;
+    if (k < AP) {
+      seat = seat + 1 == AP ? 0 : seat + 1;
+      a = (float)pk_sel(t.stack, seat); b = (float)pk_status(t.st, seat); c = (float)pk_sel(t.crb, seat);
+    }
+    int base = 13 + 3 * (k - 1);
+    if (base + 2 < W) { o[base] = a; o[base + 1] = b; o[base + 2] = c; }
+  }
+}
