@@ -92,9 +92,9 @@ typedef struct PulsePokerConfig {
 } PulsePokerConfig;
 
 /* reset (PokerGPU.py:73-157).  prefixed_decks_or_null: int32 [N,52] copied into st->decks; NULL
- * draws each deck from the chance tape (seed, env_base + table, hand_counter).  first_reset != 0:
- * stacks = starting_bbs and button = 0; otherwise busted/oversized stacks are refilled, rolled by
- * `rotation` and the button advances.  Writes the first observation [N, 13+3(M-1)]. */
+ * draws each deck from the chance tape (seed, env_base + table, hand_counter).  first_reset bit 0: stacks = starting_bbs
+ * (else busted/oversized stacks are refilled and rolled by `rotation`); bit 1: button = 0 (else it
+ * advances modulo the table size).  The first reset of an env passes 3.  Writes the first observation [N, 13+3(M-1)]. */
 int pulse_poker_reset(const PulsePokerState* st, const PulsePokerConfig* cfg, const int32_t* prefixed_decks_or_null,
                       uint64_t seed, uint64_t env_base, uint32_t hand_counter, int rotation, int first_reset,
                       float* obs_out, pulse_stream_t stream);

@@ -137,7 +137,7 @@ PULSE_HD void compat_reset_one(const PulsePokerState& S, const PokerParams& pr, 
 #pragma unroll
   for (int s = 0; s < MAXP; ++s) {
     old[s] = starting_bbs;
-    if (s < P && !first_reset) {
+    if (s < P && !(first_reset & 1)) {
       int v = S.stacks[(size_t)g * P + s];
       old[s] = (v == 0 || v > max_bbs) ? starting_bbs : v;  // :105-108
     }
@@ -147,7 +147,7 @@ PULSE_HD void compat_reset_one(const PulsePokerState& S, const PokerParams& pr, 
   for (int s = 0; s < MAXP; ++s) {
     int src = s - rotation;  // torch.roll: new[(j + r) % P] = old[j]  (:109-110)
     src %= P; if (src < 0) src += P;
-    t.stack[s] = (s < P) ? pk_sel(old, first_reset ? s : src) : 0;
+    t.stack[s] = (s < P) ? pk_sel(old, (first_reset & 1) ? s : src) : 0;
     t.crb[s] = 0; t.inv[s] = 0;
     bool dealt = s < AP;
     t.hole0[s] = dealt ? deck[2 * s] : -1;                  // :112-114
@@ -155,7 +155,7 @@ PULSE_HD void compat_reset_one(const PulsePokerState& S, const PokerParams& pr, 
     if (s < P) st = pk_set_status(st, s, dealt ? PK_ACTIVE : PK_SITOUT);  // :118-119
   }
   t.st = st;
-  int button = first_reset ? 0 : (S.button[g] + 1) % AP;    // :121
+  int button = (first_reset & 2) ? 0 : (S.button[g] + 1) % AP;    // :121
   int sb, bb;
   if (AP == 2) { sb = button; bb = (button + 1) % AP; }     // :123-125
   else { sb = (button + 1) % AP; bb = (button + 2) % AP; }  // :127-128

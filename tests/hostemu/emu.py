@@ -1,0 +1,92 @@
+"""TEST INFRASTRUCTURE ONLY: numpy-backed driver of the host-compiled kernel bodies (libhostemu.so)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import build as _build
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(str(_build.build()))
+    return _LIB
+
+
+def p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+class StateStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "decks", "deck_positions", "board", "pots", "stages", "stacks", "hands", "current_round_bet",
+        "total_invested", "status", "button", "sb", "bb", "idx", "highest", "agg", "acted", "last_raise_size",
+        "prev_invested", "is_done", "equity_dirty", "equities", "hand_ranks")] + [("n_hand_ranks", C.c_int64)]
+
+
+class ConfigStruct(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("n_games", "n_players", "active_players", "max_players", "starting_bbs",
+                                         "max_bbs", "K", "alpha")] + [("w1", C.c_float), ("w2", C.c_float)]
+
+
+N_FIELDS = ("deck_positions", "pots", "stages", "button", "sb", "bb", "idx", "highest", "agg", "acted",
+            "last_raise_size", "prev_invested")
+NP_FIELDS = ("stacks", "current_round_bet", "total_invested", "status")
+
+
+class EmuPoker:
+    def __init__(self, hand_ranks, n_players=6, max_players=10, n_games=100, starting_bbs=100, max_bbs=1000,
+                 w1=.5, w2=.5, K=20, alpha=300):
+        N, P = n_games, n_players
+        self.n_games, self.n_players, self.max_players = N, P, max_players
+        self.obs_size = 13 + (max_players - 1) * 3
+        self.hand_ranks = np.ascontiguousarray(hand_ranks, dtype=np.int32)
+        self.decks = np.zeros((N, 52), np.int32)
+        self.board = np.full((N, 5), -1, np.int32)
+        self.hands = np.full((N, P, 2), -1, np.int32)
+        for f in N_FIELDS:
+            setattr(self, f, np.zeros(N, np.int32))
+        for f in NP_FIELDS:
+            setattr(self, f, np.zeros((N, P), np.int32))
+        self.is_done = np.zeros(N, np.uint8)
+        self.equity_dirty = np.zeros(N, np.uint8)
+        self._eq = np.zeros(N * P, np.float32)
+        self.active_players = P
+        self._first = True
+        self.cfg = ConfigStruct(N, P, P, max_players, starting_bbs, max_bbs, K, alpha, w1, w2)
+        self.obs = np.zeros((N, self.obs_size), np.float32)
+        self.rewards = np.zeros(N, np.float32)
+
+    @property
+    def equities(self):
+        return self._eq[: self.n_games * self.active_players].reshape(self.n_games, self.active_players)
+
+    def _state(self):
+        s = StateStruct()
+        for n in ("decks", "board", "hands", "is_done", "equity_dirty") + N_FIELDS + NP_FIELDS:
+            setattr(s, n, getattr(self, n).ctypes.data)
+        s.equities = self._eq.ctypes.data
+        s.hand_ranks = self.hand_ranks.ctypes.data
+        s.n_hand_ranks = self.hand_ranks.size
+        self.cfg.active_players = self.active_players
+        return s
+
+    def reset(self, decks=None, active_players=None, rotation=0, seed=0, env_base=0, hand=0):
+        self.active_players = active_players or self.n_players
+        s = self._state()
+        d = None if decks is None else np.ascontiguousarray(decks, dtype=np.int32)
+        lib().emu_poker_reset(C.byref(s), C.byref(self.cfg), p(d), C.c_uint64(seed), C.c_uint64(env_base),
+                              C.c_uint32(hand), C.c_int(rotation), C.c_int(3 if self._first else 0), p(self.obs))
+        self._first = False
+        return self.obs
+
+    def step(self, actions, phases=255, actor_idx=None):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        s = self._state()
+        lib().emu_poker_step(C.byref(s), C.byref(self.cfg), p(a), p(actor_idx), C.c_uint32(phases), p(self.obs),
+                             p(self.rewards), p(self.is_done))
+        return self.obs, self.rewards, self.is_done.astype(bool)
