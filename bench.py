@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""Headline benchmark: env-steps/s of the PokerGPU heads-up NLHE table step (BASELINE.json configs[2]:
+4M parallel tables, uniform random actions over 0..12, full showdown evaluation), weak-scaled over N
+GPUs with 4M tables per GPU and no data-path collective (tables are independent).
+
+A "step" is one `env.step(actions)` over the whole batch.  Hands follow the reference's convention
+(scripts/Poker/trainGPU.py:79-108): whole-batch reset, then HAND_LEN steps, every table counted at
+every step; the reset launches sit inside the timed region.  One JSON line is printed by rank 0.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload poker_hu|poker_6max]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+HAND_LEN = 16          # steps per whole-batch hand (max observed heads-up hand is 14)
+SEED = 20260401        # scripts/Poker/trainGPU_performance.py:52
+CFG = dict(starting_bbs=100, max_bbs=1000, w1=.5, w2=.3, K=100, alpha=50)  # config/pokerGPU.yaml:26-33
+WORKLOADS = {
+    "poker_hu": dict(n_players=2, max_players=2, tables=4_194_304, algo_bytes=201, hand_len=16),
+    "poker_6max": dict(n_players=6, max_players=6, tables=4_194_304, algo_bytes=401, hand_len=24),
+}
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks and throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_baseline(wl, min_seconds=10.0, tables=1 << 20):
+    """The oracle port of the reference step (oracle/oracle_poker.c, OpenMP over tables) timed on this
+    box's host cores on a bounded sample of the same workload: `tables` tables, whole hands of
+    hand_len steps, until min_seconds of stepping have elapsed."""
+    import numpy as np
+    from oracle import pyoracle
+    from pulselib_b200 import handranks
+
+    hr = handranks.load_table()
+    P, M, L = wl["n_players"], wl["max_players"], wl["hand_len"]
+    orc = pyoracle.OraclePoker(hr, n_players=P, max_players=M, n_games=tables, **CFG)
+    rng = np.random.default_rng(SEED)
+    acts = rng.integers(0, 13, (L, tables)).astype(np.int64)
+    steps, spent, hands = 0, 0.0, 0
+    while spent < min_seconds:
+        orc.tape_decks(SEED, 0, hands)
+        t0 = time.perf_counter()
+        orc.reset(None)
+        orc._sync()
+        for i in range(L):
+            orc.step_fast(acts[i])
+        spent += time.perf_counter() - t0
+        steps += L * tables
+        hands += 1
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    return {"value": steps / spent, "unit": "env-steps/s", "cores": cores, "kind": "port",
+            "sample": f"{tables} tables x {hands} hands x {L} steps (reset + step, obs built), oracle/oracle_poker.c "
+                      f"with OpenMP on {cores} threads; the reference itself is torch-eager Python and cannot "
+                      f"travel to this box"}, spent, steps
+
+
+def run_reference(args, wl, name):
+    """--impl reference: the reference's own CPU path for this step.  The reference is Python
+    (torch eager), absent on the GPU box, so the oracle port stands in (kind = "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    per_step = max(1.0, 20.0 / max(1, args.steps + args.warmup))
+    base, spent, steps = cpu_baseline(wl, min_seconds=min(60.0, per_step * (args.steps + args.warmup)))
+    line = {"impl": "reference", "metric": "env-steps/sec (PokerGPU NLHE)", "value": base["value"],
+            "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * spent / max(1, steps) * wl["tables"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": f"{name}: PokerGPU n_players={wl['n_players']}, {wl['tables']} tables/GPU, "
+                                   f"uniform random actions 0..12, hands of {wl['hand_len']} steps"},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_gpu(args, wl, name):
+    import torch
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the env-step engine has no CPU fallback")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+    N, L = int(args.tables or wl["tables"]), wl["hand_len"]
+    P, M = wl["n_players"], wl["max_players"]
+    env = PokerGPUPacked(dev, n_players=P, max_players=M, n_games=N, seed=SEED, env_base=rank * N, **CFG)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(SEED + rank)
+    actions = torch.randint(0, 13, (L, N), dtype=torch.int64, device=dev, generator=gen)
+    obs = torch.empty((N, env.obs_size), dtype=torch.float32, device=dev)
+    rew = torch.empty(N, dtype=torch.float32, device=dev)
+    done = torch.empty(N, dtype=torch.bool, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    launches = [0]
+
+    def run_steps(k, start, pairs=None):
+        for i in range(k):
+            j = (start + i) % L
+            if j == 0:
+                env.reset()
+                launches[0] += 1
+            if pairs is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+            env.step_into(actions[j], obs, rew, done)
+            launches[0] += 1
+            if pairs is not None:
+                e1.record(stream)
+                pairs.append((e0, e1))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # live-step fraction of the workload (untimed): tables not yet done when each step begins
+    env.reset()
+    live = 0.0
+    for j in range(L):
+        live += 1.0 if j == 0 else float((~done).float().mean())
+        env.step_into(actions[j], obs, rew, done)
+    live_fraction = live / L
+
+    run_steps(args.warmup, 0)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches[0] = 0
+    pairs = []
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record(stream)
+    run_steps(args.steps, args.warmup, pairs)
+    t1.record(stream)
+    barrier()
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+    ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
+    kern_ms = torch.tensor([sum(a.elapsed_time(b) for a, b in pairs) / max(1, len(pairs))], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(kern_ms, op=dist.ReduceOp.MAX)
+    total_ms, kernel_ms = float(ms.item()), float(kern_ms.item())
+    n_launch = launches[0]
+
+    # end to end through the public API with HOST buffers: pinned actions -> device, env.step(),
+    # obs/reward/done -> pinned host, every step, `chunks` independent envs on their own streams so
+    # the PCIe copies of one chunk overlap the step of another.
+    chunks = max(1, args.e2e_chunks)
+    Nc = N // chunks
+    e2e_steps = min(args.steps, 2 * L)
+    envs = [PokerGPUPacked(dev, n_players=P, max_players=M, n_games=Nc, seed=SEED, env_base=rank * N + c * Nc, **CFG)
+            for c in range(chunks)]
+    streams = [torch.cuda.Stream(dev) for _ in range(chunks)]
+    h_act = torch.randint(0, 13, (L, chunks, Nc), dtype=torch.int64).pin_memory()
+    h_obs = torch.empty((chunks, Nc, env.obs_size), dtype=torch.float32).pin_memory()
+    h_rew = torch.empty((chunks, Nc), dtype=torch.float32).pin_memory()
+    h_done = torch.empty((chunks, Nc), dtype=torch.bool).pin_memory()
+    d_act = [torch.empty(Nc, dtype=torch.int64, device=dev) for _ in range(chunks)]
+
+    def e2e_steps_run(k, start):
+        for i in range(k):
+            j = (start + i) % L
+            for c in range(chunks):
+                with torch.cuda.stream(streams[c]):
+                    if j == 0:
+                        envs[c].reset()
+                    d_act[c].copy_(h_act[j, c], non_blocking=True)
+                    o, r, d, _, _ = envs[c].step(d_act[c])
+                    h_obs[c].copy_(o, non_blocking=True)
+                    h_rew[c].copy_(r, non_blocking=True)
+                    h_done[c].copy_(d, non_blocking=True)
+
+    e2e_steps_run(3, 0)
+    barrier()
+    w0 = time.perf_counter()
+    e2e_steps_run(e2e_steps, 0)
+    for s in streams:
+        s.synchronize()
+    e2e_ms = torch.tensor([(time.perf_counter() - w0) * 1e3], dtype=torch.float64, device=dev)
+    barrier()
+    if dist is not None:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_value = world * Nc * chunks * e2e_steps / (float(e2e_ms.item()) * 1e-3)
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        A = wl["algo_bytes"]
+        achieved = A * N / (kernel_ms * 1e-3) / 1e9
+        traffic = None
+        tf = ROOT / "profiles" / "traffic.json"
+        if tf.exists():
+            traffic = json.loads(tf.read_text()).get(name)
+        base, _, _ = cpu_baseline(wl, min_seconds=args.cpu_seconds) if world == 1 and args.cpu_seconds > 0 else (None, 0, 0)
+        line = {
+            "metric": "env-steps/sec (PokerGPU NLHE)", "value": world * N * args.steps / (total_ms * 1e-3),
+            "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int32", "data": "synthetic",
+            "config": {"workload": f"{name}: PokerGPU n_players={P}, {N} tables/GPU, uniform random actions 0..12, "
+                                   f"whole-batch reset every {L} steps inside the timed region (reference step "
+                                   f"convention: every table counted every step)",
+                       "tables_per_gpu": N, "hand_len": L, "layout": "packed", "parallelism": f"env-sharded x{world}",
+                       "l2": "inputs larger than L2 (state+obs+actions per step > 126 MB)",
+                       "live_step_fraction": round(live_fraction, 4)},
+            "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": N * 8,
+                    "d2h_bytes_per_step": N * (4 * env.obs_size + 4 + 1), "steps": e2e_steps, "chunks": chunks,
+                    "timing": "wall clock around the host loop, all streams synchronised"},
+            "gpu_launches": n_launch,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "kernel": "poker_packed_step_kernel", "kernel_ms": kernel_ms,
+                         "algorithmic_bytes_per_table_step": A, "peak_source": peak_src},
+            "clocks": sampler.summary(),
+        }
+        if base is not None:
+            line["cpu_baseline"] = base
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="poker_hu", choices=sorted(WORKLOADS))
+    ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")
+    ap.add_argument("--e2e-chunks", type=int, default=4)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU-baseline sample length (0 = skip)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl, args.workload)
+    else:
+        run_gpu(args, wl, args.workload)
+
+
+if __name__ == "__main__":
+    main()

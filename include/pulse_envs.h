@@ -120,6 +120,33 @@ int pulse_poker_step(const PulsePokerState* st, const PulsePokerConfig* cfg, con
                      const int32_t* actor_idx_or_null, uint32_t phases, float* obs_out, float* reward_out,
                      uint8_t* done_out, pulse_stream_t stream);
 
+/* ---- PokerGPU, packed layout (throughput path; layout in pulselib_b200/csrc/poker_packed_body.cuh) */
+typedef struct PulsePokerPacked {
+  uint32_t* tbl;             /* [N][4] meta | status planes | pot | highest */
+  uint32_t* tbl2;            /* [N][2] last_raise_size | five board cards x 6 bits */
+  int32_t* stack;            /* [P][N] */
+  int32_t* crb;              /* [P][N] current_round_bet */
+  int32_t* inv;              /* [P][N] total_invested */
+  uint16_t* hole;            /* [P][N] card0 | card1 << 6 */
+  uint32_t* hand_ctr;        /* [N] hands dealt (needed for auto_reset), may be NULL otherwise */
+  const int32_t* hand_ranks; /* HandRanks table (only its first 36,875 entries are read) */
+  int64_t n_hand_ranks;
+} PulsePokerPacked;
+
+/* Same contracts as pulse_poker_reset / pulse_poker_step.  auto_reset != 0 (engine extension): a
+ * table already done when the step begins is dealt its next hand from the chance tape instead of
+ * idling; that step returns reward 0, done 0 and the new hand's first observation. */
+int pulse_poker_packed_reset(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
+                             const int32_t* prefixed_decks_or_null, uint64_t seed, uint64_t env_base,
+                             uint32_t hand_counter, int rotation, int first_reset, float* obs_out_or_null,
+                             pulse_stream_t stream);
+int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int64_t* actions,
+                            float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset, uint64_t seed,
+                            uint64_t env_base, pulse_stream_t stream);
+/* packed -> reference-shaped tensors (decks, sb/bb, equities, prev_invested are not represented) */
+int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                       pulse_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -387,3 +387,19 @@ void oracle_poker_step(OraclePoker* s, const int64_t* actions, float* obs, float
   }
   if (obs) oracle_poker_get_obs(s, obs);                        /* :633 */
 }
+
+/* fills s->decks from the chance tape for every table (OpenMP) */
+void oracle_poker_fill_tape_decks(OraclePoker* s, uint64_t seed, uint64_t env_base, uint32_t hand) {
+#pragma omp parallel for schedule(static)
+  for (int g = 0; g < s->n_games; ++g) oracle_poker_tape_deck(seed, env_base + (uint64_t)g, hand, s->decks + (size_t)g * 52);
+}
+
+/* actions from the chance tape: uniform over 0..n_actions-1, stream ACTION, counter = step */
+void oracle_tape_actions(uint64_t seed, uint64_t env_base, uint32_t step, int n_actions, int64_t* out, int n) {
+#pragma omp parallel for schedule(static)
+  for (int g = 0; g < n; ++g) {
+    uint32_t blk[4];
+    oracle_tape(seed, env_base + (uint64_t)g, ORACLE_STREAM_ACTION, step, blk);
+    out[g] = (int64_t)oracle_mulhi32(blk[0], (uint32_t)n_actions);
+  }
+}

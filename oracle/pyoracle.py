@@ -94,10 +94,8 @@ class OraclePoker:
         self.s.active_players = self.active_players
 
     def tape_decks(self, seed, env_base, hand):
-        d = np.zeros(52, np.int32)
-        for g in range(self.n_games):
-            self.L.oracle_poker_tape_deck(C.c_uint64(seed), C.c_uint64(env_base + g), C.c_uint32(hand), p(d))
-            self.decks[g] = d
+        self._sync()
+        self.L.oracle_poker_fill_tape_decks(C.byref(self.s), C.c_uint64(seed), C.c_uint64(env_base), C.c_uint32(hand))
 
     def reset(self, decks=None, active_players=None, rotation=0):
         if decks is not None:
@@ -115,6 +113,10 @@ class OraclePoker:
         self._sync()
         self.L.oracle_poker_step(C.byref(self.s), p(a), p(self.obs), p(self.rewards), C.c_int(use_cached_equities))
         return self.obs, self.rewards, self.is_done.astype(bool)
+
+    def step_fast(self, actions_i64):
+        """step without re-syncing pointers or building obs (CPU-baseline timing loop)."""
+        self.L.oracle_poker_step(C.byref(self.s), p(actions_i64), p(self.obs), p(self.rewards), C.c_int(0))
 
     def call(self, name, *args):
         self._sync()

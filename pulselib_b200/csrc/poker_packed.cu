@@ -1,0 +1,137 @@
+// Packed-layout PokerGPU kernels and their C ABI (include/pulse_envs.h).  Layout and rationale:
+// poker_packed_body.cuh.  HBM-bound: see DESIGN.md for bytes per table-step.
+#include "poker_packed_body.cuh"
+
+namespace {
+
+constexpr int kBlock = 128;
+
+// Each thread builds its observation row in registers/local memory, the block stages the rows in
+// shared memory (row stride W+1 words: conflict-free) and then writes the block's contiguous
+// [kBlock, W] slab with fully coalesced 128 B lines.
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock)
+poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
+                         float* __restrict__ obs_out, float* __restrict__ reward_out,
+                         uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
+                         int starting_bbs, int max_bbs, long long n) {
+  extern __shared__ float smem[];
+  const int W = 13 + 3 * (pr.M - 1);
+  for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
+    const long long g = base + threadIdx.x;
+    float row[13 + 3 * 15];
+    if (g < n)
+      packed_step_one<MAXP>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base, starting_bbs,
+                            max_bbs, g, n);
+    float* mine = smem + threadIdx.x * (W + 1);
+    if (g < n)
+      for (int i = 0; i < W; ++i) mine[i] = row[i];
+    __syncthreads();
+    const long long rows = (n - base) < kBlock ? (n - base) : kBlock;
+    const int total = (int)rows * W;
+    float* dst = obs_out + base * W;
+    const int dq = kBlock / W, dr = kBlock - dq * W;
+    int r = threadIdx.x / W, c = threadIdx.x - r * W;
+    for (int e = threadIdx.x; e < total; e += kBlock) {
+      dst[e] = smem[r * (W + 1) + c];
+      r += dq; c += dr;
+      if (c >= W) { c -= W; ++r; }
+    }
+    __syncthreads();
+  }
+}
+
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock)
+poker_packed_reset_kernel(PulsePokerPacked S, PokerParams pr, const int32_t* __restrict__ prefixed, uint64_t seed,
+                          uint64_t env_base, uint32_t hand, int rotation, int first_reset, int starting_bbs,
+                          int max_bbs, float* __restrict__ obs_out, long long n) {
+  const int W = 13 + 3 * (pr.M - 1);
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
+    float row[13 + 3 * 15];
+    packed_reset_one<MAXP>(S, pr, prefixed, seed, env_base, hand, rotation, first_reset, starting_bbs, max_bbs,
+                           obs_out ? row : nullptr, g, n);
+    if (obs_out)
+      for (int i = 0; i < W; ++i) obs_out[g * W + i] = row[i];
+  }
+}
+
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock)
+poker_packed_unpack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr, long long n) {
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock)
+    packed_unpack_one<MAXP>(S, C, pr, g, n);
+}
+
+int check_cfg(const void* st, const PulsePokerConfig* cfg) {
+  if (!st || !cfg) { pulse_set_error("null state/config"); return PULSE_EINVAL; }
+  if (cfg->n_players < 2 || cfg->n_players > 10) { pulse_set_error("n_players must be in 2..10"); return PULSE_EINVAL; }
+  if (cfg->active_players < 2 || cfg->active_players > cfg->n_players) { pulse_set_error("active_players must be in 2..n_players"); return PULSE_EINVAL; }
+  if (cfg->max_players < cfg->active_players || cfg->max_players > 16) { pulse_set_error("max_players must be in active_players..16"); return PULSE_EINVAL; }
+  if (cfg->n_games < 0) { pulse_set_error("n_games < 0"); return PULSE_EINVAL; }
+  return PULSE_OK;
+}
+
+PokerParams make_params(const PulsePokerConfig* c) {
+  PokerParams p; p.w1 = c->w1; p.w2 = c->w2; p.K = c->K; p.alpha = c->alpha;
+  p.P = c->n_players; p.AP = c->active_players; p.M = c->max_players;
+  return p;
+}
+
+}  // namespace
+
+#define PKP_DISPATCH(P, CALL)                            \
+  do {                                                   \
+    if ((P) <= 2) { constexpr int MP = 2; CALL; }        \
+    else if ((P) <= 4) { constexpr int MP = 4; CALL; }   \
+    else if ((P) <= 6) { constexpr int MP = 6; CALL; }   \
+    else { constexpr int MP = 10; CALL; }                \
+  } while (0)
+
+extern "C" {
+
+int pulse_poker_packed_reset(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int32_t* prefixed,
+                             uint64_t seed, uint64_t env_base, uint32_t hand_counter, int rotation, int first_reset,
+                             float* obs_out, cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  if (cfg->n_games == 0) return PULSE_OK;
+  PokerParams pr = make_params(cfg);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_reset_kernel<MP><<<grid, kBlock, 0, stream>>>(
+                         *st, pr, prefixed, seed, env_base, hand_counter, rotation, first_reset, cfg->starting_bbs,
+                         cfg->max_bbs, obs_out, (long long)cfg->n_games)));
+  return pulse_check_launch("pulse_poker_packed_reset");
+}
+
+int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int64_t* actions,
+                            float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset, uint64_t seed,
+                            uint64_t env_base, cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  if (cfg->n_games == 0) return PULSE_OK;
+  PULSE_REQUIRE(actions && obs_out && reward_out && done_out, "null buffer");
+  PULSE_REQUIRE(!auto_reset || st->hand_ctr, "auto_reset needs hand_ctr");
+  PokerParams pr = make_params(cfg);
+  const int W = 13 + 3 * (pr.M - 1);
+  const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_step_kernel<MP><<<grid, kBlock, smem, stream>>>(
+                         *st, pr, actions, obs_out, reward_out, done_out, auto_reset, seed, env_base,
+                         cfg->starting_bbs, cfg->max_bbs, (long long)cfg->n_games)));
+  return pulse_check_launch("pulse_poker_packed_step");
+}
+
+int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                       cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  PULSE_REQUIRE(compat != nullptr, "compat state is null");
+  if (cfg->n_games == 0) return PULSE_OK;
+  PokerParams pr = make_params(cfg);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_unpack_kernel<MP><<<grid, kBlock, 0, stream>>>(*st, *compat, pr,
+                                                                                  (long long)cfg->n_games)));
+  return pulse_check_launch("pulse_poker_unpack");
+}
+}

@@ -1,0 +1,284 @@
+// Packed PokerGPU layout: the throughput path.  Same per-table logic as the reference-shaped
+// kernels (poker_core.cuh), different HBM layout:
+//
+//   tbl   uint4 [N]    x = meta  (stage:3 | idx:4 | agg:4 | button:4 | acted:5 | done:1)
+//                      y = status bit-planes (bit s = low bit of seat s, bit 16+s = high bit)
+//                      z = pot, w = highest
+//   tbl2  uint2 [N]    x = last_raise_size, y = the hand's five board cards, 6 bits each
+//   stack/crb/inv  int32 [P][N]   seat-major, so lane i reads element i of every seat row
+//   hole  uint16 [P][N]           card0 | card1 << 6
+//   hand_ctr uint32 [N]           hands dealt to this table (tape counter for auto-reset)
+//
+// One thread owns one table: a 16 B + 8 B vector load plus 3 coalesced 4 B loads per seat bring the
+// whole table into registers; only words that changed are stored.  The deck itself is never kept:
+// hole cards and the full board are fixed by the deal (burn/flop/turn/river sit at deck positions
+// 2AP+1..2AP+7 whatever the betting does, PokerGPU.py:394-419, :601-616), so reset stores the five
+// board cards and `stage` says how many are visible.  Heads-up state is 52 B per table against the
+// 62 B the SURVEY's accounting assumes.  Equities are not stored either: the reward needs only the
+// actor's, which is recomputed from (stage, board, hole) -- identical to the cached value because
+// the reference refreshes its cache whenever stage or board change (PokerGPU.py:604-616, :542).
+#pragma once
+#include "poker_core.cuh"
+
+struct PackedDeck {
+  uint32_t fb;   // five board cards, 6 bits each
+  int base;      // 2 * active_players: first deck position after the hole cards
+  PULSE_HD int card(int pos) const {
+    int off = pos - base;  // 1,2,3 flop; 5 turn; 7 river
+    int i = off <= 3 ? off - 1 : (off == 5 ? 3 : 4);
+    return (int)((fb >> (6 * i)) & 63u);
+  }
+};
+
+PULSE_HD uint32_t pkp_meta(int stage, int idx, int agg, int button, int acted, bool done) {
+  if (acted > 31) acted = 31;  // only ever compared with the number of ACTIVE seats (<= 10)
+  return (uint32_t)stage | ((uint32_t)idx << 3) | ((uint32_t)agg << 7) | ((uint32_t)button << 11) |
+         ((uint32_t)acted << 15) | ((uint32_t)done << 20);
+}
+
+struct PulseU4x { uint32_t x, y, z, w; };
+struct PulseU2x { uint32_t x, y; };
+
+PULSE_HD PulseU4x pkp_ld4(const uint32_t* p) {
+#ifdef __CUDA_ARCH__
+  uint4 v = *reinterpret_cast<const uint4*>(p);
+  PulseU4x r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r;
+#else
+  PulseU4x r; r.x = p[0]; r.y = p[1]; r.z = p[2]; r.w = p[3]; return r;
+#endif
+}
+PULSE_HD void pkp_st4(uint32_t* p, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+#ifdef __CUDA_ARCH__
+  *reinterpret_cast<uint4*>(p) = make_uint4(x, y, z, w);
+#else
+  p[0] = x; p[1] = y; p[2] = z; p[3] = w;
+#endif
+}
+PULSE_HD PulseU2x pkp_ld2(const uint32_t* p) {
+#ifdef __CUDA_ARCH__
+  uint2 v = *reinterpret_cast<const uint2*>(p);
+  PulseU2x r; r.x = v.x; r.y = v.y; return r;
+#else
+  PulseU2x r; r.x = p[0]; r.y = p[1]; return r;
+#endif
+}
+PULSE_HD void pkp_st2(uint32_t* p, uint32_t x, uint32_t y) {
+#ifdef __CUDA_ARCH__
+  *reinterpret_cast<uint2*>(p) = make_uint2(x, y);
+#else
+  p[0] = x; p[1] = y;
+#endif
+}
+
+template <int MAXP>
+PULSE_HD void packed_load(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPacked& S, long long g, long long n,
+                          int AP) {
+  PulseU4x a = pkp_ld4(S.tbl + 4 * g);
+  PulseU2x b = pkp_ld2(S.tbl2 + 2 * g);
+  t.stage = a.x & 7; t.idx = (a.x >> 3) & 15; t.agg = (a.x >> 7) & 15; t.button = (a.x >> 11) & 15;
+  t.acted = (a.x >> 15) & 31; t.done = (a.x >> 20) & 1; t.dirty = false;
+  t.st = a.y; t.pot = (int32_t)a.z; t.highest = (int32_t)a.w; t.last_raise = (int32_t)b.x;
+  fb = b.y;
+  const int vis = t.stage == 0 ? 0 : t.stage == 1 ? 3 : t.stage == 2 ? 4 : 5;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) t.board[i] = i < vis ? (int)((fb >> (6 * i)) & 63u) : -1;
+  t.deck_pos = 2 * AP + (t.stage == 0 ? 0 : t.stage == 1 ? 4 : t.stage == 2 ? 6 : 8);
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {
+    t.stack[s] = t.crb[s] = t.inv[s] = 0; t.hole0[s] = t.hole1[s] = -1;
+    if (s < AP) {
+      long long o = (long long)s * n + g;
+      t.stack[s] = S.stack[o]; t.crb[s] = S.crb[o]; t.inv[s] = S.inv[o];
+      uint32_t h = S.hole[o];
+      t.hole0[s] = (int)(h & 63u); t.hole1[s] = (int)((h >> 6) & 63u);
+    }
+  }
+}
+
+template <int MAXP>
+PULSE_HD void packed_store(const PokerTable<MAXP>& t, const PokerTable<MAXP>& o, const PulsePokerPacked& S,
+                           long long g, long long n, int AP) {
+  uint32_t m1 = pkp_meta(t.stage, t.idx, t.agg, t.button, t.acted, t.done);
+  uint32_t m0 = pkp_meta(o.stage, o.idx, o.agg, o.button, o.acted, o.done);
+  if (m1 != m0 || t.st != o.st || t.pot != o.pot || t.highest != o.highest)
+    pkp_st4(S.tbl + 4 * g, m1, t.st, (uint32_t)t.pot, (uint32_t)t.highest);
+  if (t.last_raise != o.last_raise) S.tbl2[2 * g] = (uint32_t)t.last_raise;
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s)
+    if (s < AP) {
+      long long off = (long long)s * n + g;
+      if (t.stack[s] != o.stack[s]) S.stack[off] = t.stack[s];
+      if (t.crb[s] != o.crb[s]) S.crb[off] = t.crb[s];
+      if (t.inv[s] != o.inv[s]) S.inv[off] = t.inv[s];
+    }
+}
+
+// Deals a new hand to one table (PokerGPU.py:73-157 for a single row).  Cards come from
+// `prefixed` (int32 [N,52]) or from the chance tape; only the first 2AP+8 deck positions matter.
+// keep_stacks == 0 fills every stack with starting_bbs; otherwise busted / oversized stacks are
+// refilled and rolled by `rotation`.
+template <int MAXP>
+PULSE_HD void packed_deal(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPacked& S, const PokerParams& pr,
+                          const int32_t* __restrict__ prefixed, uint64_t seed, uint64_t env_id, uint32_t hand,
+                          int rotation, int keep_stacks, int button, int starting_bbs, int max_bbs, long long g,
+                          long long n) {
+  const int P = pr.P, AP = pr.AP;
+  const int need = 2 * AP + 8;
+  uint8_t d[52];
+  if (prefixed) {
+    for (int i = 0; i < need; ++i) d[i] = (uint8_t)prefixed[g * 52 + i];
+  } else {
+    for (int i = 0; i < 52; ++i) d[i] = (uint8_t)(i + 1);
+    PulseU4 blk;
+    blk.x = blk.y = blk.z = blk.w = 0;
+    for (int i = 0; i < need; ++i) {  // forward Fisher-Yates fixes position i at iteration i
+      if ((i & 3) == 0) blk = pulse_tape(seed, env_id, PULSE_STREAM_POKER_DECK, hand * 16u + (uint32_t)(i >> 2));
+      uint32_t u = (i & 3) == 0 ? blk.x : (i & 3) == 1 ? blk.y : (i & 3) == 2 ? blk.z : blk.w;
+      int j = i + (int)pulse_mulhi32(u, (uint32_t)(52 - i));
+      uint8_t tmp = d[i]; d[i] = d[j]; d[j] = tmp;
+    }
+  }
+  int32_t old[MAXP];
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {
+    old[s] = starting_bbs;
+    if (s < P && keep_stacks) {
+      int v = S.stack[(long long)s * n + g];
+      old[s] = (v == 0 || v > max_bbs) ? starting_bbs : v;  // :105-108
+    }
+  }
+  uint32_t st = 0xFFFFFFFFu;
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {
+    int src = (s - rotation) % P;  // torch.roll (:109-110)
+    if (src < 0) src += P;
+    t.stack[s] = s < P ? pk_sel(old, keep_stacks ? src : s) : 0;
+    t.crb[s] = 0; t.inv[s] = 0;
+    const bool dealt = s < AP;
+    t.hole0[s] = dealt ? d[2 * s] : -1;
+    t.hole1[s] = dealt ? d[2 * s + 1] : -1;
+    if (s < P) st = pk_set_status(st, s, dealt ? PK_ACTIVE : PK_SITOUT);
+  }
+  t.st = st;
+  const int bb = AP == 2 ? (button + 1) % AP : (button + 2) % AP;  // :123-128
+  int bstack = pk_sel(t.stack, bb) - 1;                            // post_blinds :188-199
+  pk_put(t.stack, bb, bstack); pk_put(t.crb, bb, 1); pk_put(t.inv, bb, 1);
+  if (bstack == 0) t.st = pk_set_status(t.st, bb, PK_ALLIN);
+  t.pot = 1; t.highest = 1; t.last_raise = 1;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) t.board[i] = -1;
+  t.stage = 0; t.idx = AP == 2 ? button : (bb + 1) % AP;           // :130-133
+  t.agg = bb; t.acted = 0; t.button = button; t.deck_pos = 2 * AP; t.done = false; t.dirty = false;
+  const int b0 = 2 * AP;
+  fb = (uint32_t)d[b0 + 1] | ((uint32_t)d[b0 + 2] << 6) | ((uint32_t)d[b0 + 3] << 12) |
+       ((uint32_t)d[b0 + 5] << 18) | ((uint32_t)d[b0 + 7] << 24);
+}
+
+// unconditional store of a freshly dealt table
+template <int MAXP>
+PULSE_HD void packed_store_all(const PokerTable<MAXP>& t, uint32_t fb, const PulsePokerPacked& S, long long g,
+                               long long n, int P) {
+  pkp_st4(S.tbl + 4 * g, pkp_meta(t.stage, t.idx, t.agg, t.button, t.acted, t.done), t.st, (uint32_t)t.pot,
+          (uint32_t)t.highest);
+  pkp_st2(S.tbl2 + 2 * g, (uint32_t)t.last_raise, fb);
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s)
+    if (s < P) {
+      long long off = (long long)s * n + g;
+      S.stack[off] = t.stack[s]; S.crb[off] = t.crb[s]; S.inv[off] = t.inv[s];
+      S.hole[off] = (uint16_t)((t.hole0[s] & 63) | ((t.hole1[s] & 63) << 6));
+    }
+}
+
+// One step of one table in the packed layout (PokerGPU.py:527-633).  auto_reset: a table that was
+// already done when the step began is dealt a new hand instead (engine extension):
+// the action is ignored, reward 0, done 0 and the observation is the new hand's first one.
+template <int MAXP>
+PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, const int64_t* __restrict__ actions,
+                              float* __restrict__ obs_row, float* __restrict__ reward_out,
+                              uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
+                              int starting_bbs, int max_bbs, long long g, long long n) {
+  const int P = pr.P, AP = pr.AP;
+  PokerTable<MAXP> t;
+  uint32_t fb;
+  packed_load(t, fb, S, g, n, AP);
+  if (auto_reset && t.done) {
+    uint32_t hand = S.hand_ctr[g] + 1u;
+    S.hand_ctr[g] = hand;
+    packed_deal(t, fb, S, pr, nullptr, seed, env_base + (uint64_t)g, hand, 0, 1, (t.button + 1) % AP,
+                starting_bbs, max_bbs, g, n);
+    packed_store_all(t, fb, S, g, n, P);
+    reward_out[g] = 0.0f;
+    done_out[g] = 0;
+    pk_obs(t, pr, obs_row);
+    return;
+  }
+  const PokerTable<MAXP> t0 = t;
+  const PackedDeck deck{fb, 2 * AP};
+  const long long a = actions[g];
+  const bool prev_done = t.done;
+  const int actor = t.idx;                                           // :531
+  const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537
+  const int prev_inv = pk_sel(t.crb, actor);                         // :539
+  float e = 0.5f;
+  if (legal)  // the reward is zeroed otherwise (:632), so the equity is only needed for legal actors
+    e = pk_equity(t.stage, pk_sel(t.hole0, actor), pk_sel(t.hole1, actor), t.board, S.hand_ranks, S.n_hand_ranks);
+  pk_execute(t, a);                                                  // :546
+  pk_advance(t, pr, deck);                                           // :547-616
+  if (t.done && !prev_done) {                                        // :619-622
+    pk_fold_winner(t, pr);
+    pk_showdown(t, pr, deck);
+  }
+  if (t.done) {                                                      // :625-628
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) { t.crb[s] = 0; t.inv[s] = 0; }
+    t.highest = 0;
+  }
+  reward_out[g] = legal ? pk_reward(t, pr, a, e, prev_inv) : 0.0f;   // :631-632
+  done_out[g] = t.done;
+  packed_store(t, t0, S, g, n, AP);
+  pk_obs(t, pr, obs_row);                                            // :633
+}
+
+template <int MAXP>
+PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr, const int32_t* __restrict__ prefixed,
+                               uint64_t seed, uint64_t env_base, uint32_t hand, int rotation, int first_reset,
+                               int starting_bbs, int max_bbs, float* __restrict__ obs_row, long long g, long long n) {
+  PokerTable<MAXP> t;
+  uint32_t fb;
+  int button = 0;
+  if (!(first_reset & 2)) button = (int)(((S.tbl[4 * g] >> 11) & 15u) + 1u) % pr.AP;  // :121
+  packed_deal(t, fb, S, pr, prefixed, seed, env_base + (uint64_t)g, hand, rotation, !(first_reset & 1), button,
+              starting_bbs, max_bbs, g, n);
+  packed_store_all(t, fb, S, g, n, pr.P);
+  if (S.hand_ctr) S.hand_ctr[g] = hand;
+  if (obs_row) pk_obs(t, pr, obs_row);
+}
+
+// packed -> reference-shaped tensors (for inspection and parity checks); decks, sb/bb, equities and
+// prev_invested are not represented in the packed layout and are left untouched.
+template <int MAXP>
+PULSE_HD void packed_unpack_one(const PulsePokerPacked& S, const PulsePokerState& C, const PokerParams& pr,
+                                long long g, long long n) {
+  const int P = pr.P, AP = pr.AP;
+  PokerTable<MAXP> t;
+  uint32_t fb;
+  packed_load(t, fb, S, g, n, AP);
+  if (t.stage == 5) {
+#pragma unroll
+    for (int i = 0; i < 5; ++i) t.board[i] = (int)((fb >> (6 * i)) & 63u);
+  }
+  for (int s = 0; s < P; ++s) {
+    long long off = g * P + s;
+    C.stacks[off] = s < AP ? pk_sel(t.stack, s) : S.stack[(long long)s * n + g];
+    C.current_round_bet[off] = pk_sel(t.crb, s);
+    C.total_invested[off] = pk_sel(t.inv, s);
+    C.status[off] = s < P ? pk_status(t.st, s) : PK_SITOUT;
+    C.hands[2 * off] = pk_sel(t.hole0, s);
+    C.hands[2 * off + 1] = pk_sel(t.hole1, s);
+  }
+  for (int i = 0; i < 5; ++i) C.board[g * 5 + i] = t.board[i];
+  C.pots[g] = t.pot; C.stages[g] = t.stage; C.highest[g] = t.highest; C.last_raise_size[g] = t.last_raise;
+  C.idx[g] = t.idx; C.agg[g] = t.agg; C.acted[g] = t.acted; C.button[g] = t.button;
+  C.deck_positions[g] = t.deck_pos; C.is_done[g] = t.done;
+}

@@ -1,0 +1,182 @@
+"""PokerGPU on the packed HBM layout: same rules, same reset/step API and return tuples as
+`pulselib_b200.envs.poker.PokerGPU` (the drop-in for /root/reference/environments/Poker/PokerGPU.py),
+but the per-table state is kept in the 52 B (heads-up) packed structure-of-arrays form described in
+csrc/poker_packed_body.cuh instead of one int32 tensor per field.  This is the throughput path:
+training loops that only consume (obs, reward, done, info) can use it unchanged; code that reaches
+into env.stacks / env.status etc. gets read-only snapshots through `unpack()` / attribute access.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from .. import _lib
+from .._lib import c_i, c_u32, c_u64, ptr
+from ..gym_compat import gym, spaces
+from .poker import _Config, _State, _STATE_FIELDS, device_hand_ranks
+
+
+class _Packed(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "hand_ctr", "hand_ranks")] + \
+               [("n_hand_ranks", C.c_int64)]
+
+
+_SNAPSHOT = ("stacks", "status", "idx", "agg", "acted", "highest", "last_raise_size", "current_round_bet",
+             "total_invested", "pots", "stages", "board", "hands", "deck_positions", "button", "is_done")
+
+
+class PokerGPUPacked(gym.Env):
+    metadata = {"render.modes": ["human"]}
+    NUM_ACTIONS = 13
+    ACTIVE, FOLDED, ALLIN, SITOUT = 0, 1, 2, 3
+
+    def __init__(self, device, agents=None, n_players=6, max_players=10, n_games=100, starting_bbs=100, max_bbs=1000,
+                 w1=.5, w2=.5, K=20, alpha=300, seed=0, env_base=0, auto_reset=False):
+        super().__init__()
+        self.device = dev = _lib.require_cuda(device)
+        self._lib = _lib.load()
+        if not 2 <= int(n_players) <= 10:
+            raise ValueError("n_players must be in 2..10")
+        if int(max_players) < int(n_players) or int(max_players) > 16:
+            raise ValueError("max_players must be in n_players..16")
+        self.agents = agents
+        self.n_players, self.n_games, self.max_players = int(n_players), int(n_games), int(max_players)
+        self.starting_bbs, self.max_bbs = int(starting_bbs), int(max_bbs)
+        self.w1, self.w2, self.K, self.alpha = float(w1), float(w2), int(K), int(alpha)
+        self.auto_reset = bool(auto_reset)
+        self.seed_value, self.env_base, self._hand_counter = int(seed), int(env_base), 0
+        self.action_space = spaces.Discrete(self.NUM_ACTIONS)
+        self.obs_size = 13 + (self.max_players - 1) * 3
+        self.observation_space = spaces.Box(low=0, high=10000, shape=(self.obs_size,), dtype=np.float32)
+        self.active_players = self.n_players
+        N, P = self.n_games, self.n_players
+        self.hand_ranks = device_hand_ranks(dev)
+        self._tbl = torch.zeros((N, 4), dtype=torch.int32, device=dev)
+        self._tbl2 = torch.zeros((N, 2), dtype=torch.int32, device=dev)
+        self._stack = torch.zeros((P, N), dtype=torch.int32, device=dev)
+        self._crb = torch.zeros((P, N), dtype=torch.int32, device=dev)
+        self._inv = torch.zeros((P, N), dtype=torch.int32, device=dev)
+        self._hole = torch.zeros((P, N), dtype=torch.int16, device=dev)
+        self._hand_ctr = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.obs = torch.zeros((N, self.obs_size), dtype=torch.float32, device=dev)
+        self.is_truncated = torch.zeros(N, dtype=torch.bool, device=dev)
+        self._first = True
+        self._packed = _Packed(self._tbl.data_ptr(), self._tbl2.data_ptr(), self._stack.data_ptr(),
+                               self._crb.data_ptr(), self._inv.data_ptr(), self._hole.data_ptr(),
+                               self._hand_ctr.data_ptr(), self.hand_ranks.data_ptr(), self.hand_ranks.numel())
+
+    def set_agents(self, agents):
+        self.agents = agents
+
+    def _config(self):
+        return _Config(self.n_games, self.n_players, int(self.active_players), self.max_players, self.starting_bbs,
+                       self.max_bbs, self.K, self.alpha, self.w1, self.w2)
+
+    def state_bytes_per_table(self) -> int:
+        return 24 + 14 * self.n_players
+
+    def reset(self, seed=None, options=None, rotation=0):
+        if seed is not None:
+            self.seed_value, self._hand_counter = int(seed), 0
+        options = options or {}
+        N, P, dev = self.n_games, self.n_players, self.device
+        if options.get("active_players", False):
+            candidate = torch.randint(2, P + 1, (1,), device=dev).item()
+        else:
+            candidate = P
+        self.active_players = int(min(max(candidate, options.get("q_agent_seat", 0) + 1), P))
+        prefixed = options.get("prefixed_decks")
+        if prefixed is not None:
+            prefixed = torch.as_tensor(prefixed, dtype=torch.int32, device=dev)
+            if tuple(prefixed.shape) != (N, 52):
+                raise ValueError(f"prefixed_decks must have shape {(N, 52)}, got {tuple(prefixed.shape)}")
+            prefixed = prefixed.contiguous()
+        rot = 0 if self._first else int(options.get("rotation", rotation))
+        cfg = self._config()
+        with _lib.device_guard(dev):
+            _lib.check(self._lib.pulse_poker_packed_reset(
+                C.byref(self._packed), C.byref(cfg), ptr(prefixed), c_u64(self.seed_value), c_u64(self.env_base),
+                c_u32(self._hand_counter), c_i(rot), c_i(3 if self._first else 0), ptr(self.obs),
+                _lib.cuda_stream(dev)), "pulse_poker_packed_reset")
+        self._first = False
+        self._hand_counter += 1
+        return self.obs, self.get_info()
+
+    def step_into(self, actions, obs, rewards, done):
+        """step() writing into caller-provided tensors (no allocation; used by rollout loops)."""
+        cfg = self._config()
+        with _lib.device_guard(self.device):
+            _lib.check(self._lib.pulse_poker_packed_step(
+                C.byref(self._packed), C.byref(cfg), ptr(actions), ptr(obs), ptr(rewards), ptr(done),
+                c_i(1 if self.auto_reset else 0), c_u64(self.seed_value), c_u64(self.env_base),
+                _lib.cuda_stream(self.device)), "pulse_poker_packed_step")
+
+    def step(self, actions):
+        a = torch.as_tensor(actions, device=self.device)
+        if a.dtype != torch.int64 or not a.is_contiguous():
+            a = a.to(torch.int64).contiguous()
+        if tuple(a.shape) != (self.n_games,):
+            raise ValueError(f"actions must have shape {(self.n_games,)}, got {tuple(a.shape)}")
+        rewards = torch.empty(self.n_games, dtype=torch.float32, device=self.device)
+        done = torch.empty(self.n_games, dtype=torch.bool, device=self.device)
+        self.step_into(a, self.obs, rewards, done)
+        self._done = done
+        return self.obs, rewards, done, self.is_truncated, self.get_info()
+
+    def get_info(self):
+        # seat_idx / stacks are what build_actions and the trainers read (environments/Poker/utils.py:108-123)
+        return {"active_players": self.active_players, "stacks": _Lazy(self, "stacks"), "seat_idx": _Lazy(self, "idx")}
+
+    def unpack(self) -> dict:
+        """Reference-shaped int32 snapshot of the packed state (one kernel launch)."""
+        N, P, dev = self.n_games, self.n_players, self.device
+        i32 = dict(dtype=torch.int32, device=dev)
+        out = {n: torch.zeros(N, **i32) for n in ("deck_positions", "pots", "stages", "button", "sb", "bb", "idx",
+                                                  "highest", "agg", "acted", "last_raise_size", "prev_invested")}
+        out.update({n: torch.zeros((N, P), **i32) for n in ("stacks", "current_round_bet", "total_invested", "status")})
+        out["decks"] = torch.zeros((1,), **i32)
+        out["board"] = torch.zeros((N, 5), **i32)
+        out["hands"] = torch.zeros((N, P, 2), **i32)
+        out["is_done"] = torch.zeros(N, dtype=torch.bool, device=dev)
+        out["equity_dirty"] = torch.zeros(1, dtype=torch.bool, device=dev)
+        out["equities"] = torch.zeros(1, dtype=torch.float32, device=dev)
+        s = _State()
+        for name in _STATE_FIELDS:
+            setattr(s, name, (self.hand_ranks if name == "hand_ranks" else out[name]).data_ptr())
+        s.n_hand_ranks = self.hand_ranks.numel()
+        cfg = self._config()
+        with _lib.device_guard(dev):
+            _lib.check(self._lib.pulse_poker_unpack(C.byref(self._packed), C.byref(s), C.byref(cfg),
+                                                    _lib.cuda_stream(dev)), "pulse_poker_unpack")
+        return {k: out[k] for k in _SNAPSHOT}
+
+    def __getattr__(self, name):
+        if name in _SNAPSHOT:
+            return self.unpack()[name]
+        raise AttributeError(name)
+
+    def close(self):
+        return None
+
+
+class _Lazy:
+    """info['stacks'] / info['seat_idx'] materialised only if the caller actually reads them."""
+
+    def __init__(self, env, field):
+        self._env, self._field = env, field
+
+    def _get(self):
+        return getattr(self._env, self._field)
+
+    def __getattr__(self, name):
+        return getattr(self._get(), name)
+
+    def __getitem__(self, i):
+        return self._get()[i]
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        args = tuple(a._get() if isinstance(a, _Lazy) else a for a in args)
+        return func(*args, **(kwargs or {}))

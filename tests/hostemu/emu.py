@@ -90,3 +90,58 @@ class EmuPoker:
         lib().emu_poker_step(C.byref(s), C.byref(self.cfg), p(a), p(actor_idx), C.c_uint32(phases), p(self.obs),
                              p(self.rewards), p(self.is_done))
         return self.obs, self.rewards, self.is_done.astype(bool)
+
+
+class PackedStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "hand_ctr", "hand_ranks")] + \
+               [("n_hand_ranks", C.c_int64)]
+
+
+class EmuPokerPacked(EmuPoker):
+    """Packed-layout kernel bodies on the host; the reference-shaped arrays are refreshed by unpack
+    after every call so the same comparison helpers apply."""
+
+    def __init__(self, hand_ranks, auto_reset=False, seed=0, env_base=0, **kw):
+        super().__init__(hand_ranks, **kw)
+        N, P = self.n_games, self.n_players
+        self.tbl = np.zeros((N, 4), np.uint32)
+        self.tbl2 = np.zeros((N, 2), np.uint32)
+        self.pstack = np.zeros((P, N), np.int32)
+        self.pcrb = np.zeros((P, N), np.int32)
+        self.pinv = np.zeros((P, N), np.int32)
+        self.phole = np.zeros((P, N), np.uint16)
+        self.hand_ctr = np.zeros(N, np.uint32)
+        self.auto_reset, self.seed, self.env_base = auto_reset, seed, env_base
+
+    def _packed(self):
+        s = PackedStruct()
+        s.tbl, s.tbl2 = self.tbl.ctypes.data, self.tbl2.ctypes.data
+        s.stack, s.crb, s.inv, s.hole = (a.ctypes.data for a in (self.pstack, self.pcrb, self.pinv, self.phole))
+        s.hand_ctr = self.hand_ctr.ctypes.data
+        s.hand_ranks, s.n_hand_ranks = self.hand_ranks.ctypes.data, self.hand_ranks.size
+        return s
+
+    def _unpack(self):
+        s, c = self._packed(), self._state()
+        lib().emu_poker_unpack(C.byref(s), C.byref(c), C.byref(self.cfg))
+
+    def reset(self, decks=None, active_players=None, rotation=0, seed=None, env_base=None, hand=0):
+        self.active_players = active_players or self.n_players
+        self.cfg.active_players = self.active_players
+        s = self._packed()
+        d = None if decks is None else np.ascontiguousarray(decks, dtype=np.int32)
+        lib().emu_poker_packed_reset(C.byref(s), C.byref(self.cfg), p(d),
+                                     C.c_uint64(self.seed if seed is None else seed),
+                                     C.c_uint64(self.env_base if env_base is None else env_base), C.c_uint32(hand),
+                                     C.c_int(rotation), C.c_int(3 if self._first else 0), p(self.obs))
+        self._first = False
+        self._unpack()
+        return self.obs
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        s = self._packed()
+        lib().emu_poker_packed_step(C.byref(s), C.byref(self.cfg), p(a), p(self.obs), p(self.rewards), p(self.is_done),
+                                    C.c_int(self.auto_reset), C.c_uint64(self.seed), C.c_uint64(self.env_base))
+        self._unpack()
+        return self.obs, self.rewards, self.is_done.astype(bool)

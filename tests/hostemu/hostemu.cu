@@ -3,6 +3,7 @@
 // so the CPU test suite can check the kernel logic against the oracle without a GPU.  Not part of
 // libpulse_envs.so and never used by the product.
 #include "poker_compat_body.cuh"
+#include "poker_packed_body.cuh"
 
 void pulse_set_error(const char*, ...) {}
 int pulse_check_launch(const char*) { return 0; }
@@ -35,6 +36,34 @@ int emu_poker_step(const PulsePokerState* st, const PulsePokerConfig* cfg, const
   PokerParams pr = mk(cfg);
   for (int g = 0; g < cfg->n_games; ++g)
     EMU_DISPATCH(pr.P, (compat_step_one<MP>(*st, pr, actions, actor_idx, phases, obs_out, reward_out, done_out, g)));
+  return 0;
+}
+
+int emu_poker_packed_reset(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int32_t* prefixed,
+                           uint64_t seed, uint64_t env_base, uint32_t hand, int rotation, int first_reset,
+                           float* obs_out) {
+  PokerParams pr = mk(cfg);
+  const int W = 13 + 3 * (pr.M - 1);
+  for (long long g = 0; g < cfg->n_games; ++g)
+    EMU_DISPATCH(pr.P, (packed_reset_one<MP>(*st, pr, prefixed, seed, env_base, hand, rotation, first_reset,
+                                             cfg->starting_bbs, cfg->max_bbs, obs_out ? obs_out + g * W : nullptr, g,
+                                             (long long)cfg->n_games)));
+  return 0;
+}
+int emu_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int64_t* actions,
+                          float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset, uint64_t seed,
+                          uint64_t env_base) {
+  PokerParams pr = mk(cfg);
+  const int W = 13 + 3 * (pr.M - 1);
+  for (long long g = 0; g < cfg->n_games; ++g)
+    EMU_DISPATCH(pr.P, (packed_step_one<MP>(*st, pr, actions, obs_out + g * W, reward_out, done_out, auto_reset, seed,
+                                            env_base, cfg->starting_bbs, cfg->max_bbs, g, (long long)cfg->n_games)));
+  return 0;
+}
+int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg) {
+  PokerParams pr = mk(cfg);
+  for (long long g = 0; g < cfg->n_games; ++g)
+    EMU_DISPATCH(pr.P, (packed_unpack_one<MP>(*st, *compat, pr, g, (long long)cfg->n_games)));
   return 0;
 }
 }
