@@ -49,6 +49,24 @@ class ClockSampler(threading.Thread):
         self.index, self.samples, self.stop_flag = index, [], threading.Event()
 
     def run(self):
+        try:  # NVML in-process: ~10 ms period instead of one nvidia-smi process per sample
+            import pynvml
+
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            R = pynvml
+            while not self.stop_flag.is_set():
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                flags = [bool(r & R.nvmlClocksThrottleReasonHwSlowdown), bool(r & R.nvmlClocksThrottleReasonHwThermalSlowdown),
+                         bool(r & R.nvmlClocksThrottleReasonSwThermalSlowdown), bool(r & R.nvmlClocksThrottleReasonSwPowerCap)]
+                self.samples.append([str(sm), str(mx)] + ["Active" if f else "Not Active" for f in flags])
+                self.stop_flag.wait(0.01)
+            return
+        except Exception:
+            pass
         while not self.stop_flag.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
@@ -280,8 +298,8 @@ def run_gpu(args, wl, name):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
-    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=1024)
+    ap.add_argument("--warmup", type=int, default=32)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="poker_hu", choices=sorted(WORKLOADS))
     ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")

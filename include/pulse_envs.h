@@ -128,6 +128,7 @@ typedef struct PulsePokerPacked {
   int32_t* crb;              /* [P][N] current_round_bet */
   int32_t* inv;              /* [P][N] total_invested */
   uint16_t* hole;            /* [P][N] card0 | card1 << 6 */
+  uint64_t* ev;              /* [P][N] per-deal hand values: 7-card | 6-card << 16 | HR[5-card] << 32 */
   uint32_t* hand_ctr;        /* [N] hands dealt (needed for auto_reset), may be NULL otherwise */
   const int32_t* hand_ranks; /* HandRanks table (only its first 36,875 entries are read) */
   int64_t n_hand_ranks;

@@ -74,12 +74,11 @@ PULSE_HD int pk_next_active(uint32_t st, int from, int AP) {
 PULSE_HD float pk_equity(int stage, int h0, int h1, const int32_t (&board)[5],
                                            const int32_t* __restrict__ hand_ranks, long long n_hr) {
   if (stage < 1 || stage > 3) return 0.5f;  // :461
-  uint32_t m[4] = {0, 0, 0, 0};
-  pe_add_card(h0, m); pe_add_card(h1, m);
-  pe_add_card(board[0], m); pe_add_card(board[1], m); pe_add_card(board[2], m);
-  if (stage >= 2) pe_add_card(board[3], m);
-  if (stage >= 3) pe_add_card(board[4], m);
-  int v = pe_eval_suits(m[0], m[1], m[2], m[3]);
+  uint64_t m = pe_add_card64(h1, pe_add_card64(h0, 0));
+  m = pe_add_card64(board[2], pe_add_card64(board[1], pe_add_card64(board[0], m)));
+  if (stage >= 2) m = pe_add_card64(board[3], m);
+  if (stage >= 3) m = pe_add_card64(board[4], m);
+  int v = pe_eval_mask64(m);
   float lo = 4109.0f, den = 32765.0f;  // :17-18, :65
   if (stage == 1) {
     v = (v >= 0 && v < n_hr) ? PULSE_LDG(hand_ranks + v) : 0;  // :521
@@ -151,7 +150,7 @@ PULSE_HD void pk_advance(PokerTable<MAXP>& t, const PokerParams& pr, const Deck&
     t.last_raise = 1;                                      // :581
     t.stage += 1;                                          // :584
     t.highest = 0;                                         // :585
-    t.agg = (t.button + 1) % AP;                           // :586
+    t.agg = t.button + 1 < AP ? t.button + 1 : (t.button + 1) % AP;  // :586
     t.acted = 0;                                           // :587
 #pragma unroll
     for (int s = 0; s < MAXP; ++s) t.crb[s] = 0;           // :588
@@ -181,8 +180,21 @@ PULSE_HD void pk_fold_winner(PokerTable<MAXP>& t, const PokerParams& pr) {
 }
 
 // resolve_terminated_games + _award_showdown_side_pots (:380-453, :340-378)
-template <int MAXP, class Deck>
-PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck& deck) {
+// Ranker::rank(t, s) gives the showdown value of live seat s once the board is complete.
+struct PokerCardRanker {  // evaluates the seat's two hole cards + the five board cards
+  template <int MAXP>
+  PULSE_HD int32_t rank(const PokerTable<MAXP>& t, int s) const {
+    uint64_t m = 0;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) m = pe_add_card64(t.board[i], m);
+    m = pe_add_card64(pk_sel(t.hole0, s), m);
+    m = pe_add_card64(pk_sel(t.hole1, s), m);
+    return pe_eval_mask64(m);
+  }
+};
+
+template <int MAXP, class Deck, class Ranker>
+PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck& deck, const Ranker& ranker) {
   const int P = pr.P, AP = pr.AP;
   if (!(t.stage < 5)) return;                               // :386
   uint32_t live = pk_live_mask(t.st, P);
@@ -194,18 +206,11 @@ PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck
   }
   if (t.stage <= 1) { t.deck_pos += 1; t.board[3] = deck.card(t.deck_pos); t.deck_pos += 1; }  // :407-411
   if (t.stage <= 2) { t.deck_pos += 1; t.board[4] = deck.card(t.deck_pos); t.deck_pos += 1; }  // :416-419
-  uint32_t bm[4] = {0, 0, 0, 0};
-#pragma unroll
-  for (int i = 0; i < 5; ++i) pe_add_card(t.board[i], bm);
   int32_t rank[MAXP];
 #pragma unroll
   for (int s = 0; s < MAXP; ++s) {                          // :427-450
     rank[s] = INT_MIN;
-    if (s < AP && ((live >> s) & 1u)) {
-      uint32_t m[4] = {bm[0], bm[1], bm[2], bm[3]};
-      pe_add_card(t.hole0[s], m); pe_add_card(t.hole1[s], m);
-      rank[s] = pe_eval_suits(m[0], m[1], m[2], m[3]);
-    }
+    if (s < AP && ((live >> s) & 1u)) rank[s] = ranker.rank(t, s);
   }
   // side pots: one layer per distinct investment level, ascending (:346-378).  Iterating seats as
   // "level = inv[k]" and skipping levels already handled equals the reference's sorted layers:
@@ -230,7 +235,8 @@ PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck
       if (s < AP && t.inv[s] >= level && ((live >> s) & 1u) && rank[s] == best) { winners++; first = s; }
     int32_t pot = (level - prev_level) * contributors;      // :359-360
     if (winners > 0) {                                      // :362
-      int32_t share = pot / winners, rem = pot - share * winners;
+      int32_t share = winners == 1 ? pot : winners == 2 ? (pot >> 1) : pot / winners;  // pot >= 0
+      int32_t rem = pot - share * winners;
 #pragma unroll
       for (int s = 0; s < MAXP; ++s)
         if (s < AP && t.inv[s] >= level && ((live >> s) & 1u) && rank[s] == best)
@@ -269,8 +275,9 @@ PULSE_HD void pk_obs(const PokerTable<MAXP>& t, const PokerParams& pr, float* o)
   o[5] = (float)pk_sel(t.hole0, idx);
   o[6] = (float)pk_sel(t.hole1, idx);
   o[7] = (float)t.stage;
-  int rel = (idx - t.button) % AP;
+  int rel = idx - t.button;  // (idx - button) % AP, python modulo; both are seats in [0, AP)
   if (rel < 0) rel += AP;
+  if (rel >= AP) rel %= AP;
   o[8] = (float)rel;
   o[9] = (float)t.pot;
   o[10] = (float)(t.highest - pk_sel(t.crb, idx));

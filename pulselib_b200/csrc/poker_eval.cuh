@@ -128,3 +128,15 @@ __host__ __device__ __forceinline__ void pe_add_card(int card, uint32_t m[4]) {
   unsigned c = (unsigned)(card - 1);
   if (c < 52u) m[c & 3u] |= 1u << (c >> 2);
 }
+
+// Same evaluation from one 64-bit word holding the four suit masks in 16-bit lanes
+// (bit 16*suit + rank): adding a card is one shift and one OR.
+__host__ __device__ __forceinline__ uint64_t pe_add_card64(int card, uint64_t m) {
+  unsigned c = (unsigned)(card - 1);
+  if (c < 52u) m |= 1ull << (((c & 3u) << 4) | (c >> 2));
+  return m;
+}
+__host__ __device__ __forceinline__ int pe_eval_mask64(uint64_t m) {
+  return pe_eval_suits((uint32_t)m & 0xFFFFu, (uint32_t)(m >> 16) & 0xFFFFu, (uint32_t)(m >> 32) & 0xFFFFu,
+                       (uint32_t)(m >> 48));
+}

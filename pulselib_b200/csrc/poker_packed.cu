@@ -6,36 +6,62 @@ namespace {
 
 constexpr int kBlock = 128;
 
-// Each thread builds its observation row in registers/local memory, the block stages the rows in
-// shared memory (row stride W+1 words: conflict-free) and then writes the block's contiguous
-// [kBlock, W] slab with fully coalesced 128 B lines.
-template <int MAXP>
+// Observation write-out.  Each thread builds its row in registers; the block stages the rows in
+// shared memory and then writes its contiguous [kBlock, W] slab of obs with fully coalesced 16 B
+// stores (a thread writing its own 64-160 B row straight to global would touch 32 different lines
+// per store instruction).  MT > 0: max_players is the compile-time constant MT, W % 4 == 0, rows
+// are staged as float4 with an odd row stride (in 16 B units) so both sides are conflict-free.
+// MT == 0: any max_players, scalar staging with row stride W + 1.
+template <int MAXP, int MT>
 __global__ void __launch_bounds__(kBlock)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
                          float* __restrict__ obs_out, float* __restrict__ reward_out,
                          uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
                          int starting_bbs, int max_bbs, long long n) {
-  extern __shared__ float smem[];
+  extern __shared__ float4 smem4[];
+  if (MT > 0) pr.M = MT;
+  constexpr int WT = MT > 0 ? 13 + 3 * (MT - 1) : 13 + 3 * 15;  // row buffer size
   const int W = 13 + 3 * (pr.M - 1);
   for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
     const long long g = base + threadIdx.x;
-    float row[13 + 3 * 15];
+    float row[WT];
     if (g < n)
       packed_step_one<MAXP>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base, starting_bbs,
                             max_bbs, g, n);
-    float* mine = smem + threadIdx.x * (W + 1);
-    if (g < n)
-      for (int i = 0; i < W; ++i) mine[i] = row[i];
-    __syncthreads();
     const long long rows = (n - base) < kBlock ? (n - base) : kBlock;
-    const int total = (int)rows * W;
-    float* dst = obs_out + base * W;
-    const int dq = kBlock / W, dr = kBlock - dq * W;
-    int r = threadIdx.x / W, c = threadIdx.x - r * W;
-    for (int e = threadIdx.x; e < total; e += kBlock) {
-      dst[e] = smem[r * (W + 1) + c];
-      r += dq; c += dr;
-      if (c >= W) { c -= W; ++r; }
+    if (MT > 0) {
+      constexpr int W4 = WT / 4, S4 = W4 | 1;
+      if (g < n) {
+#pragma unroll
+        for (int c = 0; c < W4; ++c)
+          smem4[threadIdx.x * S4 + c] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+      }
+      __syncthreads();
+      float4* dst = reinterpret_cast<float4*>(obs_out + base * WT);
+      const int total = (int)rows * W4;
+#pragma unroll
+      for (int it = 0; it < W4; ++it) {
+        const int q = threadIdx.x + it * kBlock;
+        if (q < total) {
+          const int r = q / W4, c = q - r * W4;
+          dst[q] = smem4[r * S4 + c];
+        }
+      }
+    } else {
+      float* smem = reinterpret_cast<float*>(smem4);
+      float* mine = smem + threadIdx.x * (W + 1);
+      if (g < n)
+        for (int i = 0; i < W; ++i) mine[i] = row[i];
+      __syncthreads();
+      const int total = (int)rows * W;
+      float* dst = obs_out + base * W;
+      const int dq = kBlock / W, dr = kBlock - dq * W;
+      int r = threadIdx.x / W, c = threadIdx.x - r * W;
+      for (int e = threadIdx.x; e < total; e += kBlock) {
+        dst[e] = smem[r * (W + 1) + c];
+        r += dq; c += dr;
+        if (c >= W) { c -= W; ++r; }
+      }
     }
     __syncthreads();
   }
@@ -114,11 +140,23 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   PULSE_REQUIRE(!auto_reset || st->hand_ctr, "auto_reset needs hand_ctr");
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
-  const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
-  PKP_DISPATCH(pr.P, (poker_packed_step_kernel<MP><<<grid, kBlock, smem, stream>>>(
-                         *st, pr, actions, obs_out, reward_out, done_out, auto_reset, seed, env_base,
-                         cfg->starting_bbs, cfg->max_bbs, (long long)cfg->n_games)));
+#define PKP_STEP(MP, MT, SMEM)                                                                              \
+  poker_packed_step_kernel<MP, MT><<<grid, kBlock, SMEM, stream>>>(*st, pr, actions, obs_out, reward_out, \
+                                                                   done_out, auto_reset, seed, env_base,    \
+                                                                   cfg->starting_bbs, cfg->max_bbs,         \
+                                                                   (long long)cfg->n_games)
+#define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
+  const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
+  if (pr.P <= 2 && pr.M == 2 && aligned) PKP_STEP(2, 2, PKP_SMEM4(2));
+  else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) PKP_STEP(6, 6, PKP_SMEM4(6));
+  else if (pr.P > 6 && pr.M == 10 && aligned) PKP_STEP(10, 10, PKP_SMEM4(10));
+  else {
+    const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
+    PKP_DISPATCH(pr.P, (PKP_STEP(MP, 0, smem)));
+  }
+#undef PKP_STEP
+#undef PKP_SMEM4
   return pulse_check_launch("pulse_poker_packed_step");
 }
 

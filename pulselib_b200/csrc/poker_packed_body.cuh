@@ -7,6 +7,9 @@
 //   tbl2  uint2 [N]    x = last_raise_size, y = the hand's five board cards, 6 bits each
 //   stack/crb/inv  int32 [P][N]   seat-major, so lane i reads element i of every seat row
 //   hole  uint16 [P][N]           card0 | card1 << 6
+//   ev    uint64 [P][N]           the seat's hand values for this deal, computed once by reset:
+//                                 bits 0-15 seven-card value (river equity and showdown rank),
+//                                 16-31 six-card value (turn), 32-52 HR[five-card value] (flop)
 //   hand_ctr uint32 [N]           hands dealt to this table (tape counter for auto-reset)
 //
 // One thread owns one table: a 16 B + 8 B vector load plus 3 coalesced 4 B loads per seat bring the
@@ -14,9 +17,12 @@
 // hole cards and the full board are fixed by the deal (burn/flop/turn/river sit at deck positions
 // 2AP+1..2AP+7 whatever the betting does, PokerGPU.py:394-419, :601-616), so reset stores the five
 // board cards and `stage` says how many are visible.  Heads-up state is 52 B per table against the
-// 62 B the SURVEY's accounting assumes.  Equities are not stored either: the reward needs only the
-// actor's, which is recomputed from (stage, board, hole) -- identical to the cached value because
-// the reference refreshes its cache whenever stage or board change (PokerGPU.py:604-616, :542).
+// 62 B the SURVEY's accounting assumes.  Because the whole board is known at the deal, so is every
+// hand value the hand can ever need: reset evaluates each seat's 5-, 6- and 7-card hands once
+// (uniformly across the warp) and step only reads `ev` -- one 8 B word for the actor when a reward
+// needs its equity, one per live seat at showdown.  This equals the reference's cached equities
+// because it refreshes its cache whenever stage or board change (PokerGPU.py:604-616, :542), and it
+// takes the evaluator (the most divergent code) out of the per-step kernel.
 #pragma once
 #include "poker_core.cuh"
 
@@ -172,7 +178,32 @@ PULSE_HD void packed_deal(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
   const int b0 = 2 * AP;
   fb = (uint32_t)d[b0 + 1] | ((uint32_t)d[b0 + 2] << 6) | ((uint32_t)d[b0 + 3] << 12) |
        ((uint32_t)d[b0 + 5] << 18) | ((uint32_t)d[b0 + 7] << 24);
+  // hand values of every dealt seat on the flop, turn and river boards of this deal
+  const uint64_t flop = pe_add_card64(d[b0 + 3], pe_add_card64(d[b0 + 2], pe_add_card64(d[b0 + 1], 0)));
+  const uint64_t turn = pe_add_card64(d[b0 + 5], flop), river = pe_add_card64(d[b0 + 7], turn);
+  for (int s = 0; s < AP; ++s) {
+    const uint64_t h = pe_add_card64(d[2 * s + 1], pe_add_card64(d[2 * s], 0));
+    const int v5 = pe_eval_mask64(h | flop), v6 = pe_eval_mask64(h | turn), v7 = pe_eval_mask64(h | river);
+    const int f = (v5 >= 0 && v5 < S.n_hand_ranks) ? PULSE_LDG(S.hand_ranks + v5) : 0;  // HR[HR[p5]] (:521)
+    S.ev[(long long)s * n + g] = (uint64_t)(uint32_t)v7 | ((uint64_t)(uint32_t)v6 << 16) | ((uint64_t)(uint32_t)f << 32);
+  }
 }
+
+// equity of seat `s` at `stage` from the stored hand values (PokerGPU.py:455-525)
+PULSE_HD float pkp_equity(const PulsePokerPacked& S, int stage, int s, long long g, long long n) {
+  if (stage < 1 || stage > 3) return 0.5f;  // :461
+  const uint64_t ev = S.ev[(long long)s * n + g];
+  const int v = stage == 3 ? (int)(ev & 0xFFFFu) : stage == 2 ? (int)((ev >> 16) & 0xFFFFu) : (int)(ev >> 32);
+  const float lo = stage == 1 ? 74359.0f : 4109.0f, den = stage == 1 ? 749420.0f : 32765.0f;  // :15-18, :65-66
+  const float e = PULSE_FDIV(PULSE_FSUB((float)v, lo), den);
+  return fminf(fmaxf(e, 0.0f), 1.0f);
+}
+
+struct PackedEvRanker {  // showdown rank = the stored seven-card value
+  const uint64_t* ev; long long g, n;
+  template <int MAXP>
+  PULSE_HD int32_t rank(const PokerTable<MAXP>&, int s) const { return (int32_t)(ev[(long long)s * n + g] & 0xFFFFu); }
+};
 
 // unconditional store of a freshly dealt table
 template <int MAXP>
@@ -205,7 +236,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   if (auto_reset && t.done) {
     uint32_t hand = S.hand_ctr[g] + 1u;
     S.hand_ctr[g] = hand;
-    packed_deal(t, fb, S, pr, nullptr, seed, env_base + (uint64_t)g, hand, 0, 1, (t.button + 1) % AP,
+    packed_deal(t, fb, S, pr, nullptr, seed, env_base + (uint64_t)g, hand, 0, 1, t.button + 1 < AP ? t.button + 1 : (t.button + 1) % AP,
                 starting_bbs, max_bbs, g, n);
     packed_store_all(t, fb, S, g, n, P);
     reward_out[g] = 0.0f;
@@ -222,12 +253,12 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   const int prev_inv = pk_sel(t.crb, actor);                         // :539
   float e = 0.5f;
   if (legal)  // the reward is zeroed otherwise (:632), so the equity is only needed for legal actors
-    e = pk_equity(t.stage, pk_sel(t.hole0, actor), pk_sel(t.hole1, actor), t.board, S.hand_ranks, S.n_hand_ranks);
+    e = pkp_equity(S, t.stage, actor, g, n);
   pk_execute(t, a);                                                  // :546
   pk_advance(t, pr, deck);                                           // :547-616
   if (t.done && !prev_done) {                                        // :619-622
     pk_fold_winner(t, pr);
-    pk_showdown(t, pr, deck);
+    pk_showdown(t, pr, deck, PackedEvRanker{S.ev, g, n});
   }
   if (t.done) {                                                      // :625-628
 #pragma unroll

@@ -19,7 +19,7 @@ from .poker import _Config, _State, _STATE_FIELDS, device_hand_ranks
 
 
 class _Packed(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "hand_ctr", "hand_ranks")] + \
+    _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "ev", "hand_ctr", "hand_ranks")] + \
                [("n_hand_ranks", C.c_int64)]
 
 
@@ -60,11 +60,12 @@ class PokerGPUPacked(gym.Env):
         self._inv = torch.zeros((P, N), dtype=torch.int32, device=dev)
         self._hole = torch.zeros((P, N), dtype=torch.int16, device=dev)
         self._hand_ctr = torch.zeros(N, dtype=torch.int32, device=dev)
+        self._ev = torch.zeros((P, N), dtype=torch.int64, device=dev)
         self.obs = torch.zeros((N, self.obs_size), dtype=torch.float32, device=dev)
         self.is_truncated = torch.zeros(N, dtype=torch.bool, device=dev)
         self._first = True
         self._packed = _Packed(self._tbl.data_ptr(), self._tbl2.data_ptr(), self._stack.data_ptr(),
-                               self._crb.data_ptr(), self._inv.data_ptr(), self._hole.data_ptr(),
+                               self._crb.data_ptr(), self._inv.data_ptr(), self._hole.data_ptr(), self._ev.data_ptr(),
                                self._hand_ctr.data_ptr(), self.hand_ranks.data_ptr(), self.hand_ranks.numel())
 
     def set_agents(self, agents):
@@ -75,7 +76,7 @@ class PokerGPUPacked(gym.Env):
                        self.max_bbs, self.K, self.alpha, self.w1, self.w2)
 
     def state_bytes_per_table(self) -> int:
-        return 24 + 14 * self.n_players
+        return 24 + 22 * self.n_players  # 14 B/seat touched every step + 8 B/seat of per-deal hand values
 
     def reset(self, seed=None, options=None, rotation=0):
         if seed is not None:

@@ -93,7 +93,7 @@ class EmuPoker:
 
 
 class PackedStruct(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "hand_ctr", "hand_ranks")] + \
+    _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "ev", "hand_ctr", "hand_ranks")] + \
                [("n_hand_ranks", C.c_int64)]
 
 
@@ -111,6 +111,7 @@ class EmuPokerPacked(EmuPoker):
         self.pinv = np.zeros((P, N), np.int32)
         self.phole = np.zeros((P, N), np.uint16)
         self.hand_ctr = np.zeros(N, np.uint32)
+        self.pev = np.zeros((P, N), np.uint64)
         self.auto_reset, self.seed, self.env_base = auto_reset, seed, env_base
 
     def _packed(self):
@@ -118,6 +119,7 @@ class EmuPokerPacked(EmuPoker):
         s.tbl, s.tbl2 = self.tbl.ctypes.data, self.tbl2.ctypes.data
         s.stack, s.crb, s.inv, s.hole = (a.ctypes.data for a in (self.pstack, self.pcrb, self.pinv, self.phole))
         s.hand_ctr = self.hand_ctr.ctypes.data
+        s.ev = self.pev.ctypes.data
         s.hand_ranks, s.n_hand_ranks = self.hand_ranks.ctypes.data, self.hand_ranks.size
         return s
 

@@ -61,7 +61,7 @@ def compare_state(a, b, tag, fields=INT_N + INT_NP + ("board", "hands")):
             raise AssertionError(f"{tag}: field {f} differs at {bad}: {x[bad]} vs {y[bad]}")
 
 
-def replay_golden(name, engine, alpha_override=None):
+def replay_golden(name, engine, check_equities=True):
     """Replays a golden file through `engine`; asserts bit-exact ints/obs/equities, reward within tolerance."""
     z = np.load(GOLDEN / f"{name}.npz")
     P, M, N, hands, steps = z["meta"]
@@ -80,7 +80,8 @@ def replay_golden(name, engine, alpha_override=None):
                     raise AssertionError(f"{tag}: {f} at {bad}: got {got[bad]} want {z[f][h, t][bad]}")
             np.testing.assert_array_equal(to_np(done).astype(bool), z["is_done"][h, t], err_msg=tag + " done")
             np.testing.assert_array_equal(to_np(obs), z["obs"][h, t], err_msg=tag + " obs")
-            np.testing.assert_array_equal(to_np(engine.equities), z["equities_pad"][h, t][:, :ap], err_msg=tag + " equities")
+            if check_equities:
+                np.testing.assert_array_equal(to_np(engine.equities), z["equities_pad"][h, t][:, :ap], err_msg=tag + " equities")
             np.testing.assert_allclose(to_np(rew), z["rewards"][h, t], rtol=REWARD_RTOL, atol=reward_atol(alpha),
                                        err_msg=tag + " reward")
 
@@ -93,7 +94,7 @@ def golden_kwargs(name):
                 w1=float(z["w"][0]), w2=float(z["w"][1]))
 
 
-def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, alpha=50, tape=None):
+def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, alpha=50, check_equities=True):
     """Runs engines a and b on the same decks/actions; all integer state must match exactly."""
     for h in range(hands):
         ap = int(rng.integers(2, P + 1)) if vary_ap else P
@@ -111,7 +112,8 @@ def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, 
             compare_state(a, b, tag)
             np.testing.assert_array_equal(to_np(da).astype(bool), to_np(db).astype(bool), err_msg=tag + " done")
             np.testing.assert_array_equal(to_np(oa), to_np(ob), err_msg=tag + " obs")
-            np.testing.assert_array_equal(to_np(a.equities), to_np(b.equities), err_msg=tag + " equities")
+            if check_equities:
+                np.testing.assert_array_equal(to_np(a.equities), to_np(b.equities), err_msg=tag + " equities")
             np.testing.assert_allclose(to_np(ra), to_np(rb), rtol=REWARD_RTOL, atol=reward_atol(alpha), err_msg=tag + " reward")
             if to_np(da).all():
                 break

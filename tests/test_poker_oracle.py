@@ -7,7 +7,7 @@ import pytest
 
 from oracle import pyoracle
 from tests import poker_util as pu
-from tests.hostemu.emu import EmuPoker
+from tests.hostemu.emu import EmuPoker, EmuPokerPacked
 
 GOLDEN_CASES = ["poker_hu", "poker_6max", "poker_10max_varap"]
 
@@ -59,3 +59,17 @@ def test_reference_live_if_available(hr_table):
             return obs, rew, done
 
     pu.random_rollout_compare(RefAdapter(ref), orc, np.random.default_rng(5), 6, 400, 3, 40, rot=1)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_packed_kernel_body_hostbuild_matches_reference_golden(name, hr_table):
+    pu.replay_golden(name, EmuPokerPacked(hr_table, **pu.golden_kwargs(name)), check_equities=False)
+
+
+@pytest.mark.parametrize("P,M,N,vary,rot", [(2, 2, 3000, False, 0), (6, 6, 1500, False, 1), (10, 10, 800, True, 3),
+                                              (3, 10, 800, True, 2)])
+def test_packed_kernel_body_hostbuild_matches_oracle_random(P, M, N, vary, rot, hr_table):
+    kw = dict(n_players=P, max_players=M, n_games=N, starting_bbs=50, max_bbs=200, w1=.5, w2=.3, K=100, alpha=50)
+    rng = np.random.default_rng(P * 10 + M)
+    pu.random_rollout_compare(EmuPokerPacked(hr_table, **kw), pyoracle.OraclePoker(hr_table, **kw), rng, P, N, 5, 45,
+                              vary_ap=vary, rot=rot, check_equities=False)
