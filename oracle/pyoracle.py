@@ -121,3 +121,113 @@ class OraclePoker:
     def call(self, name, *args):
         self._sync()
         getattr(self.L, "oracle_poker_" + name)(C.byref(self.s), *args)
+
+
+# ---- Blackjack -----------------------------------------------------------------------------------
+BJ_FIELDS = ("decks", "deck_positions", "terminated", "players_cards", "players_card_idx", "player_card_sums",
+             "has_ace", "dealer_cards", "dealer_card_idx", "dealer_upcard", "dealer_card_sums", "dealer_has_ace",
+             "rewards", "obs")
+BJ_U8 = ("terminated", "has_ace", "dealer_has_ace")
+
+
+class BlackjackStruct(C.Structure):
+    _fields_ = [("n", C.c_int32)] + [(n, C.c_void_p) for n in BJ_FIELDS]
+
+
+class OracleBlackjack:
+    """Reference-shaped BlackJack on numpy arrays, stepped by oracle_blackjack.c."""
+
+    def __init__(self, batch_size):
+        self.L = lib()
+        N = self.batch_size = int(batch_size)
+        shapes = dict(decks=(N, 52), players_cards=(N, 20), dealer_cards=(N, 20), obs=(N, 3))
+        self.s = BlackjackStruct()
+        self.s.n = N
+        for f in BJ_FIELDS:
+            arr = np.zeros(shapes.get(f, (N,)), np.uint8 if f in BJ_U8 else np.int32)
+            setattr(self, f, arr)
+            setattr(self.s, f, arr.ctypes.data)
+
+    def tape_decks(self, seed, env_base, episode):
+        self.L.oracle_blackjack_tape_decks(C.c_uint64(seed), C.c_uint64(env_base), C.c_uint32(episode),
+                                           C.c_int(self.batch_size), p(self.decks))
+        return self.decks
+
+    def reset(self, decks=None):
+        if decks is not None:
+            self.decks[...] = decks
+        self.L.oracle_blackjack_reset(C.byref(self.s))
+        return self.obs
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        self.L.oracle_blackjack_step(C.byref(self.s), p(a))
+        return self.obs, self.rewards, self.terminated.astype(bool)
+
+
+# ---- 2048 / TFE ----------------------------------------------------------------------------------
+STREAM_TFE_SPAWN, STREAM_TFE_RESET = 3, 4
+
+
+class OracleTFE:
+    """Batch of reference-rule 2048 boards (int32 tile values), stepped by oracle_tfe.c."""
+
+    def __init__(self, n_envs, side=4):
+        self.L = lib()
+        self.n_envs, self.side = int(n_envs), int(side)
+        self.boards = np.zeros((self.n_envs, side, side), np.int32)
+        self.scores = np.zeros(self.n_envs, np.int64)
+        self.rewards = np.zeros(self.n_envs, np.int32)
+        self.done = np.zeros(self.n_envs, np.uint8)
+
+    def tape(self, seed, env_base, stream, counter, words):
+        out = np.zeros((self.n_envs, words), np.uint32)
+        self.L.oracle_tfe_tape_chance(C.c_uint64(seed), C.c_uint64(env_base), C.c_uint32(stream), C.c_uint32(counter),
+                                      C.c_int(self.n_envs), C.c_int(words), p(out))
+        return out
+
+    def reset(self, chance4):
+        c = np.ascontiguousarray(chance4, dtype=np.uint32)
+        self.L.oracle_tfe_reset(p(self.boards), p(c), p(self.scores), p(self.done), C.c_int(self.n_envs), C.c_int(self.side))
+        return self.boards
+
+    def step(self, actions, chance2, auto_reset=False, reset_chance4=None):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        c = np.ascontiguousarray(chance2, dtype=np.uint32)
+        rc = np.ascontiguousarray(reset_chance4, dtype=np.uint32) if reset_chance4 is not None else None
+        self.L.oracle_tfe_step(p(self.boards), p(a), p(c), p(self.scores), p(self.rewards), p(self.done),
+                               C.c_int(self.n_envs), C.c_int(self.side), C.c_int(bool(auto_reset)), p(rc))
+        return self.boards, self.rewards, self.done.astype(bool)
+
+
+# ---- Tetris --------------------------------------------------------------------------------------
+class OracleTetris:
+    """The Tetris spec (oracle_tetris.c): rows uint16 [N,20], bit x of rows[y] = cell (x, y), row 0 bottom."""
+
+    def __init__(self, n_envs):
+        self.L = lib()
+        self.n_envs = int(n_envs)
+        self.rows = np.zeros((self.n_envs, 20), np.uint16)
+        self.piece = np.zeros(self.n_envs, np.uint8)
+        self.lines = np.zeros(self.n_envs, np.int32)
+        self.done = np.zeros(self.n_envs, np.uint8)
+        self.rewards = np.zeros(self.n_envs, np.int32)
+
+    def tape_pieces(self, seed, env_base, counter, word):
+        out = np.zeros(self.n_envs, np.uint8)
+        self.L.oracle_tetris_tape_pieces(C.c_uint64(seed), C.c_uint64(env_base), C.c_uint32(counter), C.c_int(word),
+                                         C.c_int(self.n_envs), p(out))
+        return out
+
+    def reset(self, first_piece):
+        fp = np.ascontiguousarray(first_piece, dtype=np.uint8)
+        self.L.oracle_tetris_reset(p(self.rows), p(self.piece), p(self.lines), p(self.done), p(fp), C.c_int(self.n_envs))
+        return self.rows
+
+    def step(self, actions, next_piece, auto_reset=False, reset_piece=None):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        nx = np.ascontiguousarray(next_piece, dtype=np.uint8)
+        rp = np.ascontiguousarray(reset_piece, dtype=np.uint8) if reset_piece is not None else nx
+        self.L.oracle_tetris_step(p(self.rows), p(self.piece), p(self.lines), p(self.done), p(a), p(nx), p(rp),
+                                  p(self.rewards), C.c_int(bool(auto_reset)), C.c_int(self.n_envs))
+        return self.rows, self.rewards, self.done.astype(bool)

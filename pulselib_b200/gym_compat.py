@@ -49,8 +49,16 @@ except Exception:  # ModuleNotFoundError in this image
             if shape is None:
                 shape = np.shape(low)
             super().__init__(tuple(shape), dtype)
-            self.low = np.broadcast_to(np.asarray(low, dtype=dtype), self.shape)
-            self.high = np.broadcast_to(np.asarray(high, dtype=dtype), self.shape)
+            self.low = np.broadcast_to(self._bound(low, dtype), self.shape)
+            self.high = np.broadcast_to(self._bound(high, dtype), self.shape)
+
+        @staticmethod
+        def _bound(v, dtype):
+            v = np.asarray(v, dtype=np.float64)
+            if np.issubdtype(np.dtype(dtype), np.integer):  # gymnasium clips infinite bounds of integer boxes
+                info = np.iinfo(dtype)
+                v = np.clip(v, info.min, info.max)
+            return v.astype(dtype)
 
         def sample(self):
             lo = np.where(np.isfinite(self.low), self.low, -1e6)
