@@ -54,6 +54,76 @@ int pulse_particle2d_step(float* state /*[N,4]*/, const float* action /*[N,2]*/,
                           uint8_t* truncated_out_or_null, float dt, int max_steps, int n_envs,
                           pulse_stream_t stream);
 
+/* ---- 2048 / TFE (environments/2048/TFE.py:17-189), batched --------------------------------------
+ * boards uint64 [N]: tile exponents, 4 bits per cell, cell (r, c) at bits 16 r + 4 c (side 2..4,
+ * square).  score int64 [N] = TFE.total_score.  obs (optional) int32 [N, side, side] tile values, the
+ * reference's board representation (:121).  Chance: add_tile_numba's two RNG draws (:31-33) are two
+ * 32-bit words per spawn, idx = mulhi32(u0, n_empty), four = u1 > floor(0.9 * 2^32); injected as
+ * chance2 uint32 [N,2] (reset: chance4 uint32 [N,4] = two spawns) or, when NULL, taken from the tape
+ * at (seed, env_base + i, counter) -- pass a different counter for every reset / step.
+ * reset = TFE.reset (:143-149).  step = TFE.step (:152-189): action 0 left, 1 up, 2 right, 3 down
+ * (uint8 or int64, action_bytes = 1 or 8); reward = floor(log2(step score)) or 0 (:185-187); done =
+ * is_game_over_numba (:48-67).  auto_reset != 0 (engine extension; the reference has no batched
+ * form): a board that is game-over when the step begins is reset instead (reward 0, done 0). */
+int pulse_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_t* chance4_or_null, uint64_t seed,
+                    uint64_t env_base, uint32_t counter, int32_t* obs_out_or_null, int n_envs, int side,
+                    pulse_stream_t stream);
+int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, const uint32_t* chance2_or_null,
+                   const uint32_t* reset_chance4_or_null, uint64_t seed, uint64_t env_base, uint32_t counter,
+                   int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out, uint8_t* done_out,
+                   int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
+int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, int side, pulse_stream_t stream);
+/* int32 tile values -> packed boards; *bad_count_or_null is incremented for every board holding a
+ * value that is not 0 or a power of two in 2..32768 */
+int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, int* bad_count_or_null, int n_envs, int side,
+                   pulse_stream_t stream);
+
+/* ---- Tetris 10x20, batched placement + line clear ------------------------------------------------
+ * The reference ships only empty shells (environments/Tetris/Tetris.py:1-13, TetrisNumba.py:1-16), so
+ * these entry points replace no reference code; the rules are DESIGN.md section 6 / oracle/oracle_tetris.c.
+ * rows uint16 [N,20] row-major, 16-byte aligned (bit x of rows[i][y] = cell (x, y), row 0 bottom; this
+ * tensor is also the observation); piece uint8 [N] current piece 0..6 (I O T S Z J L); lines int32 [N];
+ * done uint8/bool [N].  action in 0..39 = rotation * 10 + column (uint8 or int64).  Chance: the piece
+ * that follows a placement (next_piece uint8 [N]) and the first piece after an auto-reset (reset_piece
+ * uint8 [N]); NULL takes mulhi32(word 0 / word 1, 7) of the tape block at (seed, env_base + i, counter).
+ * reward int32 [N] = rows cleared by this step.  auto_reset != 0: an env that is done when the step
+ * begins is cleared instead of stepped (reward 0, done 0). */
+int pulse_tetris_reset(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* done, const uint8_t* first_piece_or_null,
+                       uint64_t seed, uint64_t env_base, uint32_t counter, int n_envs, pulse_stream_t stream);
+int pulse_tetris_step(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* done, const void* actions,
+                      int action_bytes, const uint8_t* next_piece_or_null, const uint8_t* reset_piece_or_null,
+                      uint64_t seed, uint64_t env_base, uint32_t counter, int auto_reset, int32_t* reward_out,
+                      int n_envs, pulse_stream_t stream);
+
+/* ---- Blackjack (environments/blackjack/blackjack.py:23-186) ------------------------------------
+ * Engine state: st uint32 [N] (packed sums, counters, flags; layout in csrc/blackjack_body.cuh) and
+ * deck uint8 [52][N] (position-major).  obs int32 [N,3] = (player_sum, usable_ace, dealer_upcard)
+ * (:103-108); rewards int32 [N] in {-1,0,1} (:164-177); terminated uint8/bool [N].
+ * reset = BlackJack.reset + deal_starting_cards (:23-101); injected_decks_or_null: uint8 [N,52]
+ * row-major permutations of 0..51, NULL draws them from the chance tape (seed, env_base+i, episode).
+ * step = BlackJack.step (:179-186): action 0 hit, 1 stand, anything else / terminated env: no-op. */
+int pulse_blackjack_reset(uint32_t* st, uint8_t* deck, const uint8_t* injected_decks_or_null, uint64_t seed,
+                          uint64_t env_base, uint32_t episode, int32_t* obs_out, int32_t* rewards_out,
+                          uint8_t* terminated_out, int n_envs, pulse_stream_t stream);
+int pulse_blackjack_step(uint32_t* st, const uint8_t* deck, const int64_t* actions, int32_t* obs_out,
+                         int32_t* rewards_out, uint8_t* terminated_out, int n_envs, pulse_stream_t stream);
+/* engine state -> the reference's tensor attributes (blackjack.py:24-44), for inspection / parity */
+typedef struct PulseBlackjackCompat {
+  int64_t* decks;             /* [N,52] */
+  int32_t* deck_positions;    /* [N] */
+  int32_t* players_cards;     /* [N,20] */
+  int32_t* players_card_idx;  /* [N] */
+  int32_t* player_card_sums;  /* [N] */
+  uint8_t* has_ace;           /* [N] */
+  int32_t* dealer_cards;      /* [N,20] */
+  int32_t* dealer_card_idx;   /* [N] */
+  int32_t* dealer_upcard;     /* [N] */
+  int32_t* dealer_card_sums;  /* [N] */
+  uint8_t* dealer_has_ace;    /* [N] */
+} PulseBlackjackCompat;
+int pulse_blackjack_unpack(const uint32_t* st, const uint8_t* deck, const PulseBlackjackCompat* out, int n_envs,
+                           pulse_stream_t stream);
+
 /* ---- PokerGPU, reference-shaped layout (environments/Poker/PokerGPU.py) ----------------------- */
 /* One device pointer per tensor attribute of the reference env, same shapes and dtypes (int32,
  * row-major; is_done / equity_dirty are torch.bool = 1 byte). */
