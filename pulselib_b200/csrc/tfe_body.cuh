@@ -86,7 +86,7 @@ template <int SIDE>
 PULSE_HD bool tfe_game_over(uint64_t b) {
   const uint64_t cells = tfe_cell_mask<SIDE>();
   if (tfe_zero_nibbles(b, cells)) return false;                         // an empty cell
-  const uint64_t hpairs = cells & (cells >> 4);                         // cells with a right neighbour
+  const uint64_t hpairs = cells & (cells >> 4) & 0x0FFF0FFF0FFF0FFFULL;  // cells with a right neighbour in the same row
   if (tfe_zero_nibbles(b ^ (b >> 4), hpairs)) return false;             // equal horizontal neighbours
   const uint64_t vpairs = cells & (cells >> 16);                        // cells with a neighbour below
   if (tfe_zero_nibbles(b ^ (b >> 16), vpairs)) return false;            // equal vertical neighbours

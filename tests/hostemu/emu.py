@@ -147,3 +147,100 @@ class EmuPokerPacked(EmuPoker):
                                     C.c_int(self.auto_reset), C.c_uint64(self.seed), C.c_uint64(self.env_base))
         self._unpack()
         return self.obs, self.rewards, self.is_done.astype(bool)
+
+
+# ---- Blackjack / TFE / Tetris bodies -----------------------------------------------------------------
+BJ_COMPAT = (("decks", np.int64, 52), ("deck_positions", np.int32, 0), ("players_cards", np.int32, 20),
+             ("players_card_idx", np.int32, 0), ("player_card_sums", np.int32, 0), ("has_ace", np.uint8, 0),
+             ("dealer_cards", np.int32, 20), ("dealer_card_idx", np.int32, 0), ("dealer_upcard", np.int32, 0),
+             ("dealer_card_sums", np.int32, 0), ("dealer_has_ace", np.uint8, 0))
+
+
+class BjCompatStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n, _, _ in BJ_COMPAT]
+
+
+class EmuBlackjack:
+    def __init__(self, n, seed=0, env_base=0):
+        self.L, self.n, self.seed, self.env_base = lib(), int(n), seed, env_base
+        self.st = np.zeros(n, np.uint32)
+        self.deck = np.zeros((52, n), np.uint8)
+        self.obs = np.zeros((n, 3), np.int32)
+        self.rewards = np.zeros(n, np.int32)
+        self.terminated = np.zeros(n, np.uint8)
+
+    def reset(self, decks=None, episode=0):
+        inj = np.ascontiguousarray(decks, dtype=np.uint8) if decks is not None else None
+        self.L.emu_blackjack_reset(p(self.st), p(self.deck), p(inj), C.c_uint64(self.seed), C.c_uint64(self.env_base),
+                                   C.c_uint32(episode), p(self.obs), p(self.rewards), p(self.terminated), C.c_int(self.n))
+        return self.obs
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        self.L.emu_blackjack_step(p(self.st), p(self.deck), p(a), p(self.obs), p(self.rewards), p(self.terminated),
+                                  C.c_int(self.n))
+        return self.obs, self.rewards, self.terminated.astype(bool)
+
+    def unpack(self):
+        out, s = {}, BjCompatStruct()
+        for name, dt, w in BJ_COMPAT:
+            out[name] = np.zeros((self.n, w) if w else (self.n,), dt)
+            setattr(s, name, out[name].ctypes.data)
+        self.L.emu_blackjack_unpack(p(self.st), p(self.deck), C.byref(s), C.c_int(self.n))
+        return out
+
+
+class EmuTFE:
+    def __init__(self, n, side=4, seed=0, env_base=0):
+        self.L, self.n, self.side, self.seed, self.env_base = lib(), int(n), int(side), seed, env_base
+        self.packed = np.zeros(n, np.uint64)
+        self.boards = np.zeros((n, side, side), np.int32)
+        self.scores = np.zeros(n, np.int64)
+        self.rewards = np.zeros(n, np.int32)
+        self.done = np.zeros(n, np.uint8)
+
+    def reset(self, chance4=None, counter=0):
+        c = np.ascontiguousarray(chance4, dtype=np.uint32) if chance4 is not None else None
+        self.L.emu_tfe_reset(p(self.packed), p(self.scores), p(self.done), p(c), C.c_uint64(self.seed),
+                             C.c_uint64(self.env_base), C.c_uint32(counter), p(self.boards), C.c_int(self.n), C.c_int(self.side))
+        return self.boards
+
+    def set_boards(self, values):
+        v = np.ascontiguousarray(values, dtype=np.int32)
+        bad = self.L.emu_tfe_pack(p(v), p(self.packed), C.c_int(self.n), C.c_int(self.side))
+        assert bad == 0
+
+    def step(self, actions, chance2=None, auto_reset=False, reset_chance4=None, counter=0):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        c = np.ascontiguousarray(chance2, dtype=np.uint32) if chance2 is not None else None
+        rc = np.ascontiguousarray(reset_chance4, dtype=np.uint32) if reset_chance4 is not None else None
+        self.L.emu_tfe_step(p(self.packed), p(a), p(c), p(rc), C.c_uint64(self.seed), C.c_uint64(self.env_base),
+                            C.c_uint32(counter), C.c_int(bool(auto_reset)), p(self.boards), p(self.rewards), p(self.done),
+                            p(self.scores), C.c_int(self.n), C.c_int(self.side))
+        return self.boards, self.rewards, self.done.astype(bool)
+
+
+class EmuTetris:
+    def __init__(self, n, seed=0, env_base=0):
+        self.L, self.n, self.seed, self.env_base = lib(), int(n), seed, env_base
+        self.rows = np.zeros((n, 20), np.uint16)
+        self.piece = np.zeros(n, np.uint8)
+        self.lines = np.zeros(n, np.int32)
+        self.done = np.zeros(n, np.uint8)
+        self.rewards = np.zeros(n, np.int32)
+
+    def reset(self, first_piece):
+        self.rows[...] = 0
+        self.piece[...] = first_piece
+        self.lines[...] = 0
+        self.done[...] = 0
+        return self.rows
+
+    def step(self, actions, next_piece=None, auto_reset=False, reset_piece=None, counter=0):
+        a = np.ascontiguousarray(actions, dtype=np.int64)
+        nx = np.ascontiguousarray(next_piece, dtype=np.uint8) if next_piece is not None else None
+        rp = np.ascontiguousarray(reset_piece, dtype=np.uint8) if reset_piece is not None else None
+        self.L.emu_tetris_step(p(self.rows), p(self.piece), p(self.lines), p(self.done), p(a), p(nx), p(rp),
+                               C.c_uint64(self.seed), C.c_uint64(self.env_base), C.c_uint32(counter),
+                               C.c_int(bool(auto_reset)), p(self.rewards), C.c_int(self.n))
+        return self.rows, self.rewards, self.done.astype(bool)

@@ -4,6 +4,9 @@
 // libpulse_envs.so and never used by the product.
 #include "poker_compat_body.cuh"
 #include "poker_packed_body.cuh"
+#include "blackjack_body.cuh"
+#include "tfe_body.cuh"
+#include "tetris_body.cuh"
 
 void pulse_set_error(const char*, ...) {}
 int pulse_check_launch(const char*) { return 0; }
@@ -64,6 +67,96 @@ int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, 
   PokerParams pr = mk(cfg);
   for (long long g = 0; g < cfg->n_games; ++g)
     EMU_DISPATCH(pr.P, (packed_unpack_one<MP>(*st, *compat, pr, g, (long long)cfg->n_games)));
+  return 0;
+}
+
+// ---- Blackjack ----
+int emu_blackjack_reset(uint32_t* st, uint8_t* deck, const uint8_t* injected, uint64_t seed, uint64_t env_base,
+                        uint32_t episode, int32_t* obs, int32_t* rewards, uint8_t* terminated, int n) {
+  for (long long g = 0; g < n; ++g) bj_reset_one(st, deck, injected, seed, env_base, episode, obs, rewards, terminated, g, n);
+  return 0;
+}
+int emu_blackjack_step(uint32_t* st, const uint8_t* deck, const int64_t* actions, int32_t* obs, int32_t* rewards,
+                       uint8_t* terminated, int n) {
+  for (long long g = 0; g < n; ++g) bj_step_one(st, deck, actions, obs, rewards, terminated, g, n);
+  return 0;
+}
+int emu_blackjack_unpack(const uint32_t* st, const uint8_t* deck, const BjCompat* C, int n) {
+  for (long long g = 0; g < n; ++g) bj_unpack_one(st, deck, *C, g, n);
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- 2048 / TFE ----
+template <int SIDE>
+static void emu_tfe_step_t(uint64_t* boards, const int64_t* actions, const uint32_t* chance, const uint32_t* reset_chance,
+                           uint64_t seed, uint64_t env_base, uint32_t counter, int auto_reset, int32_t* obs,
+                           int32_t* reward, uint8_t* done, int64_t* score, int n) {
+  for (long long g = 0; g < n; ++g) {
+    const uint64_t b = boards[g];
+    const bool was_done = auto_reset && tfe_game_over<SIDE>(b);
+    PulseU4 sp, rc;
+    if (chance) { sp.x = chance[2 * g]; sp.y = chance[2 * g + 1]; sp.z = sp.w = 0; }
+    else sp = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TFE_SPAWN, counter);
+    if (reset_chance) { rc.x = reset_chance[4 * g]; rc.y = reset_chance[4 * g + 1]; rc.z = reset_chance[4 * g + 2]; rc.w = reset_chance[4 * g + 3]; }
+    else rc = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TFE_RESET, counter);
+    int32_t r; bool d;
+    boards[g] = tfe_step_one<SIDE>(b, (int)actions[g], was_done, auto_reset, sp, rc, score[g], r, d);
+    reward[g] = r; done[g] = d;
+    if (obs) tfe_unpack_board<SIDE>(boards[g], obs + g * SIDE * SIDE);
+  }
+}
+template <int SIDE>
+static void emu_tfe_reset_t(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_t* chance, uint64_t seed,
+                            uint64_t env_base, uint32_t counter, int32_t* obs, int n) {
+  for (long long g = 0; g < n; ++g) {
+    PulseU4 c;
+    if (chance) { c.x = chance[4 * g]; c.y = chance[4 * g + 1]; c.z = chance[4 * g + 2]; c.w = chance[4 * g + 3]; }
+    else c = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TFE_RESET, counter);
+    boards[g] = tfe_reset_board<SIDE>(c); score[g] = 0; done[g] = 0;
+    if (obs) tfe_unpack_board<SIDE>(boards[g], obs + g * SIDE * SIDE);
+  }
+}
+extern "C" {
+int emu_tfe_step(uint64_t* boards, const int64_t* actions, const uint32_t* chance, const uint32_t* reset_chance,
+                 uint64_t seed, uint64_t env_base, uint32_t counter, int auto_reset, int32_t* obs, int32_t* reward,
+                 uint8_t* done, int64_t* score, int n, int side) {
+  if (side == 4) emu_tfe_step_t<4>(boards, actions, chance, reset_chance, seed, env_base, counter, auto_reset, obs, reward, done, score, n);
+  else if (side == 3) emu_tfe_step_t<3>(boards, actions, chance, reset_chance, seed, env_base, counter, auto_reset, obs, reward, done, score, n);
+  else emu_tfe_step_t<2>(boards, actions, chance, reset_chance, seed, env_base, counter, auto_reset, obs, reward, done, score, n);
+  return 0;
+}
+int emu_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_t* chance, uint64_t seed, uint64_t env_base,
+                  uint32_t counter, int32_t* obs, int n, int side) {
+  if (side == 4) emu_tfe_reset_t<4>(boards, score, done, chance, seed, env_base, counter, obs, n);
+  else if (side == 3) emu_tfe_reset_t<3>(boards, score, done, chance, seed, env_base, counter, obs, n);
+  else emu_tfe_reset_t<2>(boards, score, done, chance, seed, env_base, counter, obs, n);
+  return 0;
+}
+int emu_tfe_pack(const int32_t* values, uint64_t* boards, int n, int side) {
+  int bad = 0;
+  for (long long g = 0; g < n; ++g) {
+    bool ok = side == 4 ? tfe_pack_board<4>(values + g * 16, boards[g]) : side == 3 ? tfe_pack_board<3>(values + g * 9, boards[g])
+                                                                                    : tfe_pack_board<2>(values + g * 4, boards[g]);
+    bad += !ok;
+  }
+  return bad;
+}
+
+// ---- Tetris ----
+int emu_tetris_step(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* done, const int64_t* actions,
+                    const uint8_t* next_piece, const uint8_t* reset_piece, uint64_t seed, uint64_t env_base,
+                    uint32_t counter, int auto_reset, int32_t* reward, int n) {
+  static const uint32_t shapes[TET_SHAPES] = TET_SHAPE_TABLE;
+  for (long long g = 0; g < n; ++g) {
+    const PulseU4 blk = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TETRIS_PIECE, counter);
+    const int nx = next_piece ? next_piece[g] : (int)pulse_mulhi32(blk.x, 7u);
+    const int rp = reset_piece ? reset_piece[g] : (int)pulse_mulhi32(blk.y, 7u);
+    int pc = piece[g]; int32_t ln = lines[g]; bool dn = done[g]; int32_t r;
+    tet_step_one(rows + g * TET_H, shapes, pc, ln, dn, actions[g], nx, rp, auto_reset, r);
+    piece[g] = (uint8_t)pc; lines[g] = ln; done[g] = dn; reward[g] = r;
+  }
   return 0;
 }
 }
