@@ -138,6 +138,20 @@ def run_reference(args, wl, name):
     print(json.dumps(line))
 
 
+def run_env_reference(args, name):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import bench_envs as be
+
+    base, spent, steps = be.cpu_baseline(name, min_seconds=min(60.0, max(5.0, 2.0 * (args.steps + args.warmup))))
+    print(json.dumps({"impl": "reference", "metric": f"env-steps/sec ({name})", "value": base["value"],
+                      "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                      "dtype": "int32", "data": "synthetic", "config": {"workload": name}, "cpu_baseline": base,
+                      "e2e": {"value": base["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0,
+                              "d2h_bytes_per_step": 0}}))
+
+
 def run_gpu(args, wl, name):
     import torch
 
@@ -290,9 +304,95 @@ def run_gpu(args, wl, name):
         }
         if base is not None:
             line["cpu_baseline"] = base
+        if world == 1 and not args.no_extras:
+            line["workloads"] = extra_workloads(dev, rank)
         print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
+
+
+def run_env_workload(args, name):
+    """--workload tfe_4x4 | tetris | particle2d | blackjack: the same JSON line for another env's step kernel."""
+    import torch
+
+    import bench_envs as be
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the env-step engine has no CPU fallback")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    spec = be.SPECS[name]
+    sampler = ClockSampler(local)
+    sampler.start()
+    m = be.measure(name, dev, rank, world, args.steps, args.warmup, n=args.tables or None, dist=dist)
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+    e = be.e2e(name, dev, rank, min(args.steps, 64), n=args.tables or None, chunks=args.e2e_chunks)
+    t = torch.tensor([m["total_ms"], m["kernel_ms"], e["ms"]], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, kernel_ms, e2e_ms = (float(x) for x in t.tolist())
+    if rank == 0:
+        peak, peak_src = peaks()
+        n, A = m["n"], spec["algo_bytes"]
+        achieved = A * n / (kernel_ms * 1e-3) / 1e9
+        traffic = None
+        tf = ROOT / "profiles" / "traffic.json"
+        if tf.exists():
+            traffic = json.loads(tf.read_text()).get(name)
+        line = {
+            "metric": f"env-steps/sec ({name})", "value": world * n * args.steps / (total_ms * 1e-3),
+            "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if name == "particle2d" else "int32", "data": "synthetic",
+            "config": {"workload": f"{name}: " + spec["desc"].format(n=n), "envs_per_gpu": n, "launch_mode": m["mode"],
+                       "parallelism": f"env-sharded x{world}",
+                       "l2": f"{m['replicas']} independent env batch(es) stepped in rotation so each step's inputs were "
+                             f"evicted since last touched (working set {m['replicas'] * A * n / 1e6:.0f} MB vs 126 MB L2)"},
+            "e2e": {"value": world * e["value"] * (e["ms"] / e2e_ms), "unit": "env-steps/s",
+                    "h2d_bytes_per_step": e["h2d_bytes_per_step"], "d2h_bytes_per_step": e["d2h_bytes_per_step"],
+                    "steps": e["steps"], "chunks": e["chunks"],
+                    "timing": "wall clock around the host loop, all streams synchronised"},
+            "gpu_launches": m["launches"],
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "kernel": spec["kernel"], "kernel_ms": kernel_ms,
+                         "kernel_time": m["kernel_time"], "algorithmic_bytes_per_env_step": A, "peak_source": peak_src},
+            "clocks": sampler.summary(),
+        }
+        if world == 1 and args.cpu_seconds > 0:
+            line["cpu_baseline"] = be.cpu_baseline(name, args.cpu_seconds)[0]
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def extra_workloads(dev, rank, steps=256):
+    """Compact device-timed numbers of the other env kernels for the default line's `workloads` block."""
+    import bench_envs as be
+
+    peak, _ = peaks()
+    out = {}
+    for name in ("tfe_4x4", "tetris", "particle2d", "blackjack"):
+        try:
+            m = be.measure(name, dev, rank, 1, steps, 3)
+            A = be.SPECS[name]["algo_bytes"]
+            ach = A * m["n"] / (m["kernel_ms"] * 1e-3) / 1e9
+            out[name] = {"value": m["value"], "unit": "env-steps/s", "envs": m["n"], "steps": steps,
+                         "ms_per_step": m["total_ms"] / steps, "launch_mode": m["mode"],
+                         "roofline": {"achieved": ach, "frac": ach / peak, "unit": "GB/s",
+                                      "algorithmic_bytes_per_env_step": A, "kernel": be.SPECS[name]["kernel"]}}
+        except Exception as ex:  # an extra must never take the headline down with it
+            out[name] = {"error": f"{type(ex).__name__}: {ex}"}
+    return out
 
 
 def main():
@@ -301,12 +401,20 @@ def main():
     ap.add_argument("--steps", type=int, default=1024)
     ap.add_argument("--warmup", type=int, default=32)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="poker_hu", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="poker_hu",
+                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tetris", "particle2d", "blackjack"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` block of the poker line")
     ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")
     ap.add_argument("--e2e-chunks", type=int, default=4)
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU-baseline sample length (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    if args.workload not in WORKLOADS:
+        if args.impl == "reference":
+            run_env_reference(args, args.workload)
+        else:
+            run_env_workload(args, args.workload)
+        return
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, wl, args.workload)

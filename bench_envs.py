@@ -1,0 +1,274 @@
+"""Throughput of the non-poker env steps (BASELINE.json configs: 2048 1M boards, Tetris 2M envs, Particle2D
+16M envs, Blackjack 4096 envs), used by bench.py for `--workload <name>` and for the compact `workloads`
+block of the default line.  Same rules as bench.py: CUDA events on the launching stream, >= 3 warm-up
+steps, inputs larger than L2 between touches (small configs rotate over several independent env batches),
+one launch per env step, K steps captured per CUDA graph where a step is shorter than the host's
+per-call overhead.
+"""
+from __future__ import annotations
+
+import os
+import time
+
+SEED = 20260401
+L2_BYTES = 126e6
+
+SPECS = {
+    # algo_bytes: SURVEY.md 8(d) "algorithmic bytes per env-step" (fixed there; DESIGN.md 4.x derives them)
+    "tfe_4x4": dict(n=1 << 20, algo_bytes=106, kernel="tfe_step_kernel<4, uint8_t>", graph=32, actions=16,
+                    desc="2048 4x4, {n} boards/GPU, uniform random moves (uint8), spawns from the chance tape, "
+                         "auto-reset on game over, int32 4x4 observation written every step"),
+    "tetris": dict(n=1 << 21, algo_bytes=134, kernel="tetris_step_kernel<uint8_t>", graph=32, actions=16,
+                   desc="Tetris 10x20, {n} envs/GPU, uniform random placements over 40 actions (uint8), pieces from "
+                        "the chance tape, auto-reset on lock-out, rows tensor is the observation"),
+    "particle2d": dict(n=1 << 24, algo_bytes=70, kernel="particle2d_step_kernel", graph=0, actions=4,
+                       desc="Particle2D fp32, {n} envs/GPU, dt=0.1, max_steps=200, uniform actions in [-1,1]^2"),
+    "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_step_kernel", graph=0, actions=8,
+                      desc="Blackjack, {n} envs/GPU (the reference's CPU-sized config), uniform hit/stand, whole-batch "
+                           "reset every 8 steps inside the timed region; working set is L2-resident by construction"),
+}
+
+
+def _make(name, dev, n, rank, e2e=False):
+    """-> (env, actions [L, n, ...] on the device, step(env, a) -> tuple of output tensors)"""
+    import torch
+
+    spec = SPECS[name]
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(SEED + 17 * rank + (1 if e2e else 0))
+    L = spec["actions"]
+    if name == "tfe_4x4":
+        from pulselib_b200.envs.tfe import TFEBatched
+
+        env = TFEBatched(dev, n, side=4, seed=SEED, env_base=rank * n, auto_reset=True, device_counter=True)
+        acts = torch.randint(0, 4, (L, n), dtype=torch.uint8, device=dev, generator=gen)
+
+        def step(e, a):
+            o, r, d, _, _ = e.step(a)
+            return o, r, d
+    elif name == "tetris":
+        from pulselib_b200.envs.tetris import TetrisBatched
+
+        env = TetrisBatched(dev, n, seed=SEED, env_base=rank * n, auto_reset=True, device_counter=True)
+        acts = torch.randint(0, 40, (L, n), dtype=torch.uint8, device=dev, generator=gen)
+
+        def step(e, a):
+            o, r, d, _, _ = e.step(a)
+            return o, r, d
+    elif name == "particle2d":
+        from pulselib_b200.envs.particle2d import Particle2D
+
+        env = Particle2D(dev, n, dt=0.1, max_steps=200, seed=SEED, env_base=rank * n)
+        acts = torch.rand((L, n, 2), dtype=torch.float32, device=dev, generator=gen) * 2 - 1
+
+        def step(e, a):
+            o, r, t, _, _ = e.step(a)
+            return o, r, t
+    elif name == "blackjack":
+        from pulselib_b200.envs.blackjack import BlackJack
+
+        env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
+        acts = torch.randint(0, 2, (L, n), dtype=torch.int64, device=dev, generator=gen)
+        env._bench_k = 0
+
+        def step(e, a):
+            if e._bench_k % 8 == 0:
+                e.reset()
+            e._bench_k += 1
+            o, r, t, _, _ = e.step(a)
+            return o, r, t
+    else:
+        raise KeyError(name)
+    env.reset()
+    return env, acts, step
+
+
+def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
+    """Device-timed throughput of `steps` env steps; returns a dict (value is per GPU)."""
+    import torch
+
+    spec = SPECS[name]
+    n = int(n or spec["n"])
+    per_step_bytes = spec["algo_bytes"] * n
+    replicas = 1 if name == "blackjack" else max(1, int(-(-2.5 * L2_BYTES // per_step_bytes)))
+    made = [_make(name, dev, n, rank * 64 + r) for r in range(replicas)]
+    envs, acts, step = [m[0] for m in made], made[0][1], made[0][2]
+    L = acts.shape[0]
+    stream = torch.cuda.current_stream(dev)
+    launches = 0
+    chunk = spec["graph"]
+    if chunk:
+        chunk = min(chunk, steps)
+        chunk -= chunk % replicas or 0
+        chunk = max(chunk, replicas)
+
+    def eager(k, start, pairs=None):
+        for i in range(k):
+            j = start + i
+            if pairs is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+            step(envs[j % replicas], acts[j % L])
+            if pairs is not None:
+                e1.record(stream)
+                pairs.append((e0, e1))
+
+    graph = None
+    if chunk:
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(stream)
+        with torch.cuda.stream(side):
+            eager(max(warmup, replicas), 0)
+        stream.wait_stream(side)
+        torch.cuda.synchronize(dev)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            eager(chunk, 0)
+        stream = torch.cuda.current_stream(dev)
+        graph.replay()                                   # warm replay
+    else:
+        eager(max(warmup, 3), 0)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    barrier()
+    pairs = []
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record(stream)
+    if graph is not None:
+        reps, rem = divmod(steps, chunk)
+        for _ in range(reps):
+            graph.replay()
+        eager(rem, 0)
+    else:
+        eager(steps, 0, pairs)
+    t1.record(stream)
+    barrier()
+    total_ms = t0.elapsed_time(t1)
+    kernel_ms = (sum(a.elapsed_time(b) for a, b in pairs) / len(pairs)) if pairs else total_ms / steps
+    launches = steps + (steps // 8 + 1 if name == "blackjack" else 0)
+    return dict(n=n, total_ms=total_ms, kernel_ms=kernel_ms, launches=launches, replicas=replicas,
+                mode=f"cuda graph of {chunk} steps" if graph is not None else "eager launches",
+                kernel_time="graph time / steps (includes inter-kernel gaps)" if graph is not None
+                else "CUDA events around each step launch",
+                value=n * steps / (total_ms * 1e-3))
+
+
+def e2e(name, dev, rank, steps, n=None, chunks=4):
+    """Same metric through the public env API with HOST buffers: pinned actions -> device, env.step, outputs
+    -> pinned host, every step; `chunks` independent env batches on their own streams so copies overlap."""
+    import torch
+
+    spec = SPECS[name]
+    n = int(n or spec["n"])
+    chunks = chunks if n >= 1 << 16 else 1
+    nc = n // chunks
+    made = [_make(name, dev, nc, rank * 64 + 32 + c, e2e=True) for c in range(chunks)]
+    step = made[0][2]
+    streams = [torch.cuda.Stream(dev) for _ in range(chunks)]
+    h_act = [m[1].cpu().pin_memory() for m in made]
+    d_act = [torch.empty_like(m[1][0]) for m in made]
+    outs = [step(m[0], m[1][0]) for m in made]
+    h_out = [[torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in out] for out in outs]
+    L = h_act[0].shape[0]
+    torch.cuda.synchronize(dev)
+
+    def run(k):
+        for i in range(k):
+            for c in range(chunks):
+                with torch.cuda.stream(streams[c]):
+                    d_act[c].copy_(h_act[c][i % L], non_blocking=True)
+                    out = step(made[c][0], d_act[c])
+                    for h, o in zip(h_out[c], out):
+                        h.copy_(o, non_blocking=True)
+
+    run(3)
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    run(steps)
+    for s in streams:
+        s.synchronize()
+    ms = (time.perf_counter() - w0) * 1e3
+    h2d = sum(a[0].numel() * a.element_size() for a in h_act)
+    d2h = sum(h.numel() * h.element_size() for hs in h_out for h in hs)
+    return dict(value=nc * chunks * steps / (ms * 1e-3), ms=ms, steps=steps, chunks=chunks, h2d_bytes_per_step=h2d,
+                d2h_bytes_per_step=d2h)
+
+
+def cpu_baseline(name, min_seconds=10.0):
+    """The oracle port of the reference step (oracle/*.c, OpenMP over envs) on this box's host cores, on a
+    bounded sample of the same workload.  Chance words / pieces are pre-generated outside the timed region."""
+    import ctypes as C
+
+    import numpy as np
+    from oracle import pyoracle
+
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    rng = np.random.default_rng(SEED)
+    spent, steps = 0.0, 0
+    if name == "tfe_4x4":
+        n = 1 << 20
+        orc = pyoracle.OracleTFE(n, 4)
+        orc.reset(rng.integers(0, 2**32, (n, 4), dtype=np.uint64).astype(np.uint32))
+        ch = [rng.integers(0, 2**32, (n, 2), dtype=np.uint64).astype(np.uint32) for _ in range(4)]
+        rc = rng.integers(0, 2**32, (n, 4), dtype=np.uint64).astype(np.uint32)
+        acts = rng.integers(0, 4, (8, n)).astype(np.int64)
+        k = 0
+        while spent < min_seconds:
+            t0 = time.perf_counter()
+            orc.step(acts[k % 8], ch[k % 4], auto_reset=True, reset_chance4=rc)
+            spent += time.perf_counter() - t0
+            steps += n; k += 1
+        sample = f"{n} boards x {k} steps, oracle/oracle_tfe.c (int32 4x4 boards, the reference's representation)"
+    elif name == "tetris":
+        n = 1 << 20
+        orc = pyoracle.OracleTetris(n)
+        orc.reset(rng.integers(0, 7, n).astype(np.uint8))
+        pcs = [rng.integers(0, 7, n).astype(np.uint8) for _ in range(4)]
+        acts = rng.integers(0, 40, (8, n)).astype(np.int64)
+        k = 0
+        while spent < min_seconds:
+            t0 = time.perf_counter()
+            orc.step(acts[k % 8], pcs[k % 4], auto_reset=True, reset_piece=pcs[(k + 1) % 4])
+            spent += time.perf_counter() - t0
+            steps += n; k += 1
+        sample = f"{n} envs x {k} steps, oracle/oracle_tetris.c (this repo's spec; the reference has no Tetris logic)"
+    elif name == "particle2d":
+        n = 1 << 22
+        L = pyoracle.lib()
+        state = np.zeros((n, 4), np.float32)
+        state[:, :2] = rng.standard_normal((n, 2)).astype(np.float32) * 5
+        cnt, rew, term = np.zeros(n, np.int32), np.zeros(n, np.float32), np.zeros(n, np.uint8)
+        acts = rng.uniform(-1, 1, (4, n, 2)).astype(np.float32)
+        k = 0
+        while spent < min_seconds:
+            t0 = time.perf_counter()
+            L.oracle_particle2d_step(pyoracle.p(state), pyoracle.p(acts[k % 4]), pyoracle.p(cnt), pyoracle.p(rew),
+                                     pyoracle.p(term), C.c_float(0.1), C.c_int(200), C.c_int(n))
+            spent += time.perf_counter() - t0
+            steps += n; k += 1
+        sample = f"{n} envs x {k} steps, oracle/oracle_core.c::oracle_particle2d_step"
+    elif name == "blackjack":
+        n = 4096
+        orc = pyoracle.OracleBlackjack(n)
+        acts = rng.integers(0, 2, (8, n)).astype(np.int64)
+        decks = np.argsort(rng.random((n, 52)), axis=1).astype(np.int32)
+        k = 0
+        while spent < min(min_seconds, 5.0):
+            t0 = time.perf_counter()
+            if k % 8 == 0:
+                orc.reset(decks)
+            orc.step(acts[k % 8])
+            spent += time.perf_counter() - t0
+            steps += n; k += 1
+        sample = f"{n} envs x {k} steps (reset every 8), oracle/oracle_blackjack.c, below the OpenMP threshold: 1 thread"
+        cores = 1
+    else:
+        raise KeyError(name)
+    return {"value": steps / spent, "unit": "env-steps/s", "cores": cores, "kind": "port",
+            "sample": sample + f", OpenMP on {cores} thread(s); the reference itself is Python (torch eager / numba) "
+                               f"and cannot travel to this box"}, spent, steps

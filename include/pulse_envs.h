@@ -64,14 +64,17 @@ int pulse_particle2d_step(float* state /*[N,4]*/, const float* action /*[N,2]*/,
  * reset = TFE.reset (:143-149).  step = TFE.step (:152-189): action 0 left, 1 up, 2 right, 3 down
  * (uint8 or int64, action_bytes = 1 or 8); reward = floor(log2(step score)) or 0 (:185-187); done =
  * is_game_over_numba (:48-67).  auto_reset != 0 (engine extension; the reference has no batched
- * form): a board that is game-over when the step begins is reset instead (reward 0, done 0). */
+ * form): a board that is game-over when the step begins is reset instead (reward 0, done 0).
+ * counter_dev_or_null: uint32 [2] on the device, zero-initialised by the caller; when given, the tape
+ * counter of this launch is counter + counter_dev[0] and the launch increments counter_dev[0] when it
+ * finishes, so one captured launch can be replayed from a CUDA graph with advancing chance. */
 int pulse_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_t* chance4_or_null, uint64_t seed,
                     uint64_t env_base, uint32_t counter, int32_t* obs_out_or_null, int n_envs, int side,
                     pulse_stream_t stream);
 int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, const uint32_t* chance2_or_null,
                    const uint32_t* reset_chance4_or_null, uint64_t seed, uint64_t env_base, uint32_t counter,
-                   int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out, uint8_t* done_out,
-                   int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
+                   uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
+                   uint8_t* done_out, int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
 int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, int side, pulse_stream_t stream);
 /* int32 tile values -> packed boards; *bad_count_or_null is incremented for every board holding a
  * value that is not 0 or a power of two in 2..32768 */
@@ -87,13 +90,13 @@ int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, int* bad_count_o
  * that follows a placement (next_piece uint8 [N]) and the first piece after an auto-reset (reset_piece
  * uint8 [N]); NULL takes mulhi32(word 0 / word 1, 7) of the tape block at (seed, env_base + i, counter).
  * reward int32 [N] = rows cleared by this step.  auto_reset != 0: an env that is done when the step
- * begins is cleared instead of stepped (reward 0, done 0). */
+ * begins is cleared instead of stepped (reward 0, done 0).  counter_dev_or_null: as for pulse_tfe_step. */
 int pulse_tetris_reset(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* done, const uint8_t* first_piece_or_null,
                        uint64_t seed, uint64_t env_base, uint32_t counter, int n_envs, pulse_stream_t stream);
 int pulse_tetris_step(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* done, const void* actions,
                       int action_bytes, const uint8_t* next_piece_or_null, const uint8_t* reset_piece_or_null,
-                      uint64_t seed, uint64_t env_base, uint32_t counter, int auto_reset, int32_t* reward_out,
-                      int n_envs, pulse_stream_t stream);
+                      uint64_t seed, uint64_t env_base, uint32_t counter, uint32_t* counter_dev_or_null,
+                      int auto_reset, int32_t* reward_out, int n_envs, pulse_stream_t stream);
 
 /* ---- Blackjack (environments/blackjack/blackjack.py:23-186) ------------------------------------
  * Engine state: st uint32 [N] (packed sums, counters, flags; layout in csrc/blackjack_body.cuh) and
@@ -217,6 +220,12 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 /* packed -> reference-shaped tensors (decks, sb/bb, equities, prev_invested are not represented) */
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
                        pulse_stream_t stream);
+
+/* ---- run statistics (the vector that is all-reduced across GPUs) -------------------
+ * stats4 double [4] on the device: += {n, number of done flags set, sum(reward), sum(reward^2)}.
+ * reward: float32 [n] (reward_is_float != 0) or int32 [n]. */
+int pulse_stats_accumulate(const void* reward, int reward_is_float, const uint8_t* done_or_null, double* stats4,
+                           long long n, pulse_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -80,6 +80,7 @@ void oracle_blackjack_reset(OracleBlackjack* s) {
 
 /* step (:179-186): execute_actions, rewards.zero_(), calculate_rewards, get_obs */
 void oracle_blackjack_step(OracleBlackjack* s, const int64_t* actions) {
+#pragma omp parallel for schedule(static) if (s->n > 16384)
   for (int g = 0; g < s->n; ++g) {
     const int32_t* d = s->decks + (size_t)g * 52;
     const int64_t a = actions[g];

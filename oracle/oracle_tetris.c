@@ -59,6 +59,7 @@ void oracle_tetris_reset(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t
 
 void oracle_tetris_step(uint16_t* rows_all, uint8_t* piece, int32_t* lines, uint8_t* done, const int64_t* actions,
                         const uint8_t* next_piece, const uint8_t* reset_piece, int32_t* rewards, int auto_reset, int n) {
+#pragma omp parallel for schedule(static) if (n > 16384)
   for (int g = 0; g < n; ++g) {
     uint16_t* rows = rows_all + (size_t)g * TH;
     rewards[g] = 0;

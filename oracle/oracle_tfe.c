@@ -84,6 +84,7 @@ void oracle_tfe_step(int32_t* boards, const int64_t* actions, const uint32_t* ch
                      int32_t* rewards, uint8_t* done, int n_envs, int side, int auto_reset,
                      const uint32_t* reset_chance) {
   const int n = side;
+#pragma omp parallel for schedule(static) if (n_envs > 16384)
   for (int g = 0; g < n_envs; ++g) {
     int32_t* board = boards + (size_t)g * n * n;
     if (auto_reset && done[g]) {

@@ -101,6 +101,27 @@ __host__ __device__ __forceinline__ PulseU4 pulse_tape(uint64_t seed, uint64_t e
                              (uint32_t)seed, (uint32_t)(seed >> 32));
 }
 
+// Device-resident step counter (so a step launch can be captured once in a CUDA graph and replayed with
+// an advancing chance-tape counter): ctr[0] = steps taken, ctr[1] = ticket of finished blocks.  Every
+// block reads ctr[0] when it starts; the last block to finish bumps it for the next launch.  A block
+// can only be last after every other block has finished, hence after every block has read.
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t pulse_counter_read(uint32_t* ctr) {
+  return ctr ? *reinterpret_cast<volatile uint32_t*>(ctr) : 0u;
+}
+__device__ __forceinline__ void pulse_counter_advance(uint32_t* ctr, uint32_t seen) {
+  if (!ctr) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(ctr + 1, 1u) == gridDim.x - 1) {
+      ctr[1] = 0;
+      *reinterpret_cast<volatile uint32_t*>(ctr) = seen + 1u;
+    }
+  }
+}
+#endif
+
 // Grid sizing: B200 has 148 SMs; grids are a whole number of waves where the problem is big
 // enough, otherwise just enough CTAs to cover it.
 static inline int pulse_grid_for(long long n, int block, int ctas_per_sm = 8) {

@@ -1,6 +1,7 @@
 // Packed-layout PokerGPU kernels and their C ABI (include/pulse_envs.h).  Layout and rationale:
 // poker_packed_body.cuh.  HBM-bound: see DESIGN.md for bytes per table-step.
 #include "poker_packed_body.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -12,8 +13,8 @@ constexpr int kBlock = 128;
 // per store instruction).  MT > 0: max_players is the compile-time constant MT, W % 4 == 0, rows
 // are staged as float4 with an odd row stride (in 16 B units) so both sides are conflict-free.
 // MT == 0: any max_players, scalar staging with row stride W + 1.
-template <int MAXP, int MT>
-__global__ void __launch_bounds__(kBlock)
+template <int MAXP, int MT, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
                          float* __restrict__ obs_out, float* __restrict__ reward_out,
                          uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
@@ -141,11 +142,20 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
-#define PKP_STEP(MP, MT, SMEM)                                                                              \
-  poker_packed_step_kernel<MP, MT><<<grid, kBlock, SMEM, stream>>>(*st, pr, actions, obs_out, reward_out, \
-                                                                   done_out, auto_reset, seed, env_base,    \
-                                                                   cfg->starting_bbs, cfg->max_bbs,         \
-                                                                   (long long)cfg->n_games)
+#define PKP_STEP_B(MP, MT, MINB, SMEM)                                                                            \
+  poker_packed_step_kernel<MP, MT, MINB><<<grid, kBlock, SMEM, stream>>>(*st, pr, actions, obs_out, reward_out, \
+                                                                         done_out, auto_reset, seed, env_base,    \
+                                                                         cfg->starting_bbs, cfg->max_bbs,         \
+                                                                         (long long)cfg->n_games)
+  static const int minb = getenv("PULSE_POKER_MINB") ? atoi(getenv("PULSE_POKER_MINB")) : 6;
+#define PKP_STEP(MP, MT, SMEM)                                    \
+  do {                                                            \
+    if (minb >= 16) PKP_STEP_B(MP, MT, 16, SMEM);                 \
+    else if (minb >= 12) PKP_STEP_B(MP, MT, 12, SMEM);            \
+    else if (minb >= 10) PKP_STEP_B(MP, MT, 10, SMEM);            \
+    else if (minb >= 8) PKP_STEP_B(MP, MT, 8, SMEM);              \
+    else PKP_STEP_B(MP, MT, 6, SMEM);                             \
+  } while (0)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
   if (pr.P <= 2 && pr.M == 2 && aligned) PKP_STEP(2, 2, PKP_SMEM4(2));
@@ -153,9 +163,10 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   else if (pr.P > 6 && pr.M == 10 && aligned) PKP_STEP(10, 10, PKP_SMEM4(10));
   else {
     const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
-    PKP_DISPATCH(pr.P, (PKP_STEP(MP, 0, smem)));
+    PKP_DISPATCH(pr.P, PKP_STEP(MP, 0, smem));
   }
 #undef PKP_STEP
+#undef PKP_STEP_B
 #undef PKP_SMEM4
   return pulse_check_launch("pulse_poker_packed_step");
 }

@@ -30,9 +30,11 @@ __global__ void __launch_bounds__(kBlock)
 tetris_step_kernel(uint16_t* __restrict__ rows, uint8_t* __restrict__ piece, int32_t* __restrict__ lines,
                    uint8_t* __restrict__ done, const ActT* __restrict__ actions, const uint8_t* __restrict__ next_piece,
                    const uint8_t* __restrict__ reset_piece, uint64_t seed, uint64_t env_base, uint32_t counter,
-                   int auto_reset, int32_t* __restrict__ reward_out, long long n) {
+                   uint32_t* counter_dev, int auto_reset, int32_t* __restrict__ reward_out, long long n) {
   __shared__ __align__(16) uint32_t slab[kSlabWords];
   __shared__ uint32_t shapes[TET_SHAPES];
+  const uint32_t dev_ctr = pulse_counter_read(counter_dev);
+  counter += dev_ctr;
   if (threadIdx.x < TET_SHAPES) shapes[threadIdx.x] = c_shapes[threadIdx.x];
   for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
     const int cnt = (int)((n - base) < kBlock ? (n - base) : kBlock);
@@ -65,6 +67,7 @@ tetris_step_kernel(uint16_t* __restrict__ rows, uint8_t* __restrict__ piece, int
     slab_copy(gslab, slab, cnt * TET_H / 2);
     __syncthreads();
   }
+  pulse_counter_advance(counter_dev, dev_ctr);
 }
 
 __global__ void __launch_bounds__(256)
@@ -96,8 +99,8 @@ int pulse_tetris_reset(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* 
 
 int pulse_tetris_step(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* done, const void* actions,
                       int action_bytes, const uint8_t* next_piece_or_null, const uint8_t* reset_piece_or_null,
-                      uint64_t seed, uint64_t env_base, uint32_t counter, int auto_reset, int32_t* reward_out,
-                      int n_envs, cudaStream_t stream) {
+                      uint64_t seed, uint64_t env_base, uint32_t counter, uint32_t* counter_dev_or_null,
+                      int auto_reset, int32_t* reward_out, int n_envs, cudaStream_t stream) {
   PULSE_REQUIRE(n_envs >= 0, "n_envs < 0");
   PULSE_REQUIRE(action_bytes == 1 || action_bytes == 8, "actions must be uint8 or int64");
   if (n_envs == 0) return PULSE_OK;
@@ -107,11 +110,13 @@ int pulse_tetris_step(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* d
   if (action_bytes == 1)
     tetris_step_kernel<uint8_t><<<grid, kBlock, 0, stream>>>(rows, piece, lines, done, (const uint8_t*)actions,
                                                              next_piece_or_null, reset_piece_or_null, seed, env_base,
-                                                             counter, auto_reset, reward_out, (long long)n_envs);
+                                                             counter, counter_dev_or_null, auto_reset, reward_out,
+                                                             (long long)n_envs);
   else
     tetris_step_kernel<int64_t><<<grid, kBlock, 0, stream>>>(rows, piece, lines, done, (const int64_t*)actions,
                                                              next_piece_or_null, reset_piece_or_null, seed, env_base,
-                                                             counter, auto_reset, reward_out, (long long)n_envs);
+                                                             counter, counter_dev_or_null, auto_reset, reward_out,
+                                                             (long long)n_envs);
   return pulse_check_launch("pulse_tetris_step");
 }
 }

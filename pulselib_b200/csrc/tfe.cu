@@ -34,9 +34,12 @@ template <int SIDE, typename ActT>
 __global__ void __launch_bounds__(kBlock)
 tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions, const uint2* __restrict__ chance,
                 const uint4* __restrict__ reset_chance, uint64_t seed, uint64_t env_base, uint32_t counter,
-                int auto_reset, int32_t* __restrict__ obs_out, int32_t* __restrict__ reward_out,
-                uint8_t* __restrict__ done_out, int64_t* __restrict__ score, long long n) {
+                uint32_t* counter_dev, int auto_reset, int32_t* __restrict__ obs_out,
+                int32_t* __restrict__ reward_out, uint8_t* __restrict__ done_out, int64_t* __restrict__ score,
+                long long n) {
   __shared__ int32_t smem[kBlock * (SIDE * SIDE + 1)];
+  const uint32_t dev_ctr = pulse_counter_read(counter_dev);
+  counter += dev_ctr;
   for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
     const long long g = base + threadIdx.x;
     const bool valid = g < n;
@@ -66,6 +69,7 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
     }
     if (obs_out) tfe_write_obs<SIDE>(smem, b, valid, base, n, obs_out);
   }
+  pulse_counter_advance(counter_dev, dev_ctr);
 }
 
 template <int SIDE>
@@ -135,7 +139,7 @@ int pulse_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint3
 
 int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, const uint32_t* chance2_or_null,
                    const uint32_t* reset_chance4_or_null, uint64_t seed, uint64_t env_base, uint32_t counter,
-                   int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out, uint8_t* done_out,
+                   uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out, uint8_t* done_out,
                    int64_t* score_inout, int n_envs, int side, cudaStream_t stream) {
   PULSE_REQUIRE(n_envs >= 0, "n_envs < 0");
   PULSE_REQUIRE(side >= 2 && side <= 4, "side must be 2, 3 or 4");
@@ -146,7 +150,8 @@ int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, cons
 #define TFE_STEP(ACT)                                                                                          \
   TFE_SIDE_DISPATCH(side, (tfe_step_kernel<SD, ACT><<<grid, kBlock, 0, stream>>>(                              \
                               boards, (const ACT*)actions, (const uint2*)chance2_or_null,                      \
-                              (const uint4*)reset_chance4_or_null, seed, env_base, counter, auto_reset,        \
+                              (const uint4*)reset_chance4_or_null, seed, env_base, counter,                    \
+                              counter_dev_or_null, auto_reset,                                                 \
                               obs_out_or_null, reward_out, done_out, score_inout, (long long)n_envs)))
   if (action_bytes == 1) TFE_STEP(uint8_t);
   else TFE_STEP(int64_t);

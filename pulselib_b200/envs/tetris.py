@@ -20,7 +20,7 @@ class TetrisBatched(gym.Env):
     metadata = {"render_modes": ["human"]}
     WIDTH, HEIGHT, NUM_ACTIONS, NUM_PIECES = 10, 20, 40, 7
 
-    def __init__(self, device, n_envs, seed=0, env_base=0, auto_reset=True):
+    def __init__(self, device, n_envs, seed=0, env_base=0, auto_reset=True, device_counter=False):
         super().__init__()
         self.device = _lib.require_cuda(device)
         self._lib = _lib.load()
@@ -37,6 +37,8 @@ class TetrisBatched(gym.Env):
         self.rewards = torch.zeros(n, dtype=torch.int32, device=dev)
         self._t = 0
         self._started = False
+        # device-resident tape counter, advanced by each step launch (CUDA-graph replay; see envs/tfe.py)
+        self._ctr = torch.zeros(2, dtype=torch.int32, device=dev) if device_counter else None
 
     def _pieces(self, p):
         if p is None:
@@ -50,6 +52,9 @@ class TetrisBatched(gym.Env):
         """options["first_piece"]: optional uint8 [N] piece ids 0..6 (I O T S Z J L) instead of the tape."""
         if seed is not None:
             self.seed_value, self._t = int(seed), 0
+        if self._ctr is not None and self._started:     # fold the device counter back into the host one
+            self._t += int(self._ctr[0].item())
+            self._ctr.zero_()
         first = self._pieces((options or {}).get("first_piece"))
         with _lib.device_guard(self.device):
             _lib.check(self._lib.pulse_tetris_reset(
@@ -75,9 +80,10 @@ class TetrisBatched(gym.Env):
             _lib.check(self._lib.pulse_tetris_step(
                 ptr(self.rows), ptr(self.piece), ptr(self.lines), ptr(self.done), ptr(actions),
                 c_i(actions.element_size()), ptr(nx), ptr(rp), c_u64(self.seed_value), c_u64(self.env_base),
-                c_u32(self._t), c_i(self.auto_reset), ptr(self.rewards), c_i(self.n_envs),
+                c_u32(self._t), ptr(self._ctr), c_i(self.auto_reset), ptr(self.rewards), c_i(self.n_envs),
                 _lib.cuda_stream(self.device)), "pulse_tetris_step")
-        self._t += 1
+        if self._ctr is None:
+            self._t += 1
         return self.rows, self.rewards, self.done, False, self.get_info()
 
     def get_obs(self):

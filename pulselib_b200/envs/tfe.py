@@ -23,7 +23,7 @@ from ..gym_compat import gym, spaces
 class TFEBatched(gym.Env):
     metadata = {"render_modes": ["human"]}
 
-    def __init__(self, device, n_envs, side=4, seed=0, env_base=0, auto_reset=True, return_obs=True):
+    def __init__(self, device, n_envs, side=4, seed=0, env_base=0, auto_reset=True, return_obs=True, device_counter=False):
         super().__init__()
         self.device = _lib.require_cuda(device)
         self._lib = _lib.load()
@@ -43,6 +43,9 @@ class TFEBatched(gym.Env):
         self.obs = torch.zeros((n, self.side, self.side), dtype=torch.int32, device=dev) if return_obs else None
         self._t = 0
         self._started = False
+        # device_counter: the tape counter lives on the device and is advanced by each step launch, so a
+        # captured step can be replayed from a CUDA graph (pulselib_b200.graphs) with fresh chance
+        self._ctr = torch.zeros(2, dtype=torch.int32, device=dev) if device_counter else None
 
     def _chance(self, c, words):
         """uint32 draws [N, words] as an int32-typed device tensor (same bits)."""
@@ -61,6 +64,9 @@ class TFEBatched(gym.Env):
         """options["chance"]: optional uint32 [N,4] spawn draws (two spawns) instead of the tape."""
         if seed is not None:
             self.seed_value, self._t = int(seed), 0
+        if self._ctr is not None and self._started:     # fold the device counter back into the host one
+            self._t += int(self._ctr[0].item())
+            self._ctr.zero_()
         chance = self._chance((options or {}).get("chance"), 4)
         with _lib.device_guard(self.device):
             _lib.check(self._lib.pulse_tfe_reset(
@@ -86,10 +92,12 @@ class TFEBatched(gym.Env):
         with _lib.device_guard(self.device):
             _lib.check(self._lib.pulse_tfe_step(
                 ptr(self.boards), ptr(actions), c_i(actions.element_size()), ptr(chance), ptr(reset_chance),
-                c_u64(self.seed_value), c_u64(self.env_base), c_u32(self._t), c_i(self.auto_reset), ptr(self.obs),
+                c_u64(self.seed_value), c_u64(self.env_base), c_u32(self._t), ptr(self._ctr), c_i(self.auto_reset),
+                ptr(self.obs),
                 ptr(self.rewards), ptr(self.done), ptr(self.total_score), c_i(self.n_envs), c_i(self.side),
                 _lib.cuda_stream(self.device)), "pulse_tfe_step")
-        self._t += 1
+        if self._ctr is None:
+            self._t += 1
         return self.get_obs(), self.rewards, self.done, False, self.get_info()
 
     def get_obs(self):

@@ -34,12 +34,12 @@ def test_host_side_argument_validation():
     lib.pulse_last_error.restype = C.c_char_p
     null = C.c_void_p(0)
     # n_envs == 0 is a no-op that needs no device; bad sizes are rejected before any launch
-    assert lib.pulse_tfe_step(null, null, 8, null, null, C.c_uint64(0), C.c_uint64(0), 0, 0, null, null, null, null, 0, 4, null) == 0
-    assert lib.pulse_tfe_step(null, null, 8, null, null, C.c_uint64(0), C.c_uint64(0), 0, 0, null, null, null, null, 1, 5, null) == -1
+    assert lib.pulse_tfe_step(null, null, 8, null, null, C.c_uint64(0), C.c_uint64(0), 0, null, 0, null, null, null, null, 0, 4, null) == 0
+    assert lib.pulse_tfe_step(null, null, 8, null, null, C.c_uint64(0), C.c_uint64(0), 0, null, 0, null, null, null, null, 1, 5, null) == -1
     assert b"side" in lib.pulse_last_error()
-    assert lib.pulse_tfe_step(null, null, 4, null, null, C.c_uint64(0), C.c_uint64(0), 0, 0, null, null, null, null, 1, 4, null) == -1
+    assert lib.pulse_tfe_step(null, null, 4, null, null, C.c_uint64(0), C.c_uint64(0), 0, null, 0, null, null, null, null, 1, 4, null) == -1
     assert lib.pulse_blackjack_step(null, null, null, null, null, null, 3, null) == -1
-    assert lib.pulse_tetris_step(null, null, null, null, null, 8, null, null, C.c_uint64(0), C.c_uint64(0), 0, 0, null, -1, null) == -1
+    assert lib.pulse_tetris_step(null, null, null, null, null, 8, null, null, C.c_uint64(0), C.c_uint64(0), 0, null, 0, null, -1, null) == -1
     assert lib.pulse_particle2d_step(null, null, null, null, null, null, null, C.c_float(0.1), 10, 0, null) == 0
 
 
