@@ -64,22 +64,27 @@ int pulse_particle2d_step(float* state /*[N,4]*/, const float* action /*[N,2]*/,
  * reset = TFE.reset (:143-149).  step = TFE.step (:152-189): action 0 left, 1 up, 2 right, 3 down
  * (uint8 or int64, action_bytes = 1 or 8); reward = floor(log2(step score)) or 0 (:185-187); done =
  * is_game_over_numba (:48-67).  auto_reset != 0 (engine extension; the reference has no batched
- * form): a board that is game-over when the step begins is reset instead (reward 0, done 0).
+ * form): a board whose done flag is set when the step begins (done_inout, as left by the previous
+ * reset / step / pack) is reset instead (reward 0, done 0).  obs must be 16-byte aligned.
  * counter_dev_or_null: uint32 [2] on the device, zero-initialised by the caller; when given, the tape
  * counter of this launch is counter + counter_dev[0] and the launch increments counter_dev[0] when it
  * finishes, so one captured launch can be replayed from a CUDA graph with advancing chance. */
+/* Builds this device's row-move table (192 KB, staged in shared memory by every step launch) if it does
+ * not exist yet: one cudaMalloc and one stream synchronisation, once per device.  pulse_tfe_step does the
+ * same on first use; call this first when the first step would fall inside a stream capture. */
+int pulse_tfe_init(pulse_stream_t stream);
 int pulse_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_t* chance4_or_null, uint64_t seed,
                     uint64_t env_base, uint32_t counter, int32_t* obs_out_or_null, int n_envs, int side,
                     pulse_stream_t stream);
 int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, const uint32_t* chance2_or_null,
                    const uint32_t* reset_chance4_or_null, uint64_t seed, uint64_t env_base, uint32_t counter,
                    uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
-                   uint8_t* done_out, int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
+                   uint8_t* done_inout, int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
 int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, int side, pulse_stream_t stream);
-/* int32 tile values -> packed boards; *bad_count_or_null is incremented for every board holding a
- * value that is not 0 or a power of two in 2..32768 */
-int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, int* bad_count_or_null, int n_envs, int side,
-                   pulse_stream_t stream);
+/* int32 tile values -> packed boards (+ their game-over flags); *bad_count_or_null is incremented for
+ * every board holding a value that is not 0 or a power of two in 2..32768 */
+int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, uint8_t* done_out_or_null, int* bad_count_or_null,
+                   int n_envs, int side, pulse_stream_t stream);
 
 /* ---- Tetris 10x20, batched placement + line clear ------------------------------------------------
  * The reference ships only empty shells (environments/Tetris/Tetris.py:1-13, TetrisNumba.py:1-16), so

@@ -147,9 +147,12 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
                                                                          done_out, auto_reset, seed, env_base,    \
                                                                          cfg->starting_bbs, cfg->max_bbs,         \
                                                                          (long long)cfg->n_games)
-  static const int minb = getenv("PULSE_POKER_MINB") ? atoi(getenv("PULSE_POKER_MINB")) : 6;
+  // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 8 (64) otherwise --
+  // measured on B200 (profiles/r1c_poker_launch_bounds.md); PULSE_POKER_MINB overrides for experiments
+  static const int minb_env = getenv("PULSE_POKER_MINB") ? atoi(getenv("PULSE_POKER_MINB")) : 0;
 #define PKP_STEP(MP, MT, SMEM)                                    \
   do {                                                            \
+    const int minb = minb_env > 0 ? minb_env : ((MP) <= 2 ? 10 : 8); \
     if (minb >= 16) PKP_STEP_B(MP, MT, 16, SMEM);                 \
     else if (minb >= 12) PKP_STEP_B(MP, MT, 12, SMEM);            \
     else if (minb >= 10) PKP_STEP_B(MP, MT, 10, SMEM);            \

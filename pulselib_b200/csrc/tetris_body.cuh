@@ -39,6 +39,15 @@ PULSE_HD bool tet_collides(const uint16_t* rows, uint32_t shape, int h, int x, i
   return hit;
 }
 
+// rows 2i and 2i+1 as one 32-bit word (the rows array is 4-byte aligned)
+PULSE_HD uint32_t tet_row_pair(const uint16_t* rows, int i) {
+#ifdef __CUDA_ARCH__
+  return reinterpret_cast<const uint32_t*>(rows)[i];
+#else
+  return (uint32_t)rows[2 * i] | ((uint32_t)rows[2 * i + 1] << 16);
+#endif
+}
+
 // One step of one env.  rows: this env's 20 rows (shared memory on the device).  A done env ignores the
 // action (reward 0) unless auto_reset, in which case the step that finds it done clears the board,
 // zeroes `lines` and takes `reset_piece`.  Returns true when rows changed.
@@ -47,7 +56,12 @@ PULSE_HD bool tet_step_one(uint16_t* rows, const uint32_t* shapes, int& piece, i
   reward = 0;
   if (done) {
     if (!auto_reset) return false;
+#ifdef __CUDA_ARCH__
+#pragma unroll
+    for (int i = 0; i < TET_H / 2; ++i) reinterpret_cast<uint32_t*>(rows)[i] = 0u;
+#else
     for (int y = 0; y < TET_H; ++y) rows[y] = 0;
+#endif
     piece = reset_piece; lines = 0; done = false;
     return true;
   }
@@ -57,8 +71,18 @@ PULSE_HD bool tet_step_one(uint16_t* rows, const uint32_t* shapes, int& piece, i
   const int w = (shape >> 16) & 7, h = (shape >> 20) & 7;
   int x = a - rot * 10;
   if (x > TET_W - w) x = TET_W - w;
-  int y = TET_H;                                        // entirely above the board
-  while (y > 0 && !tet_collides(rows, shape, h, x, y - 1)) --y;
+  // Hard drop.  Let `top` be the highest row with a filled cell in the piece's columns.  Dropping from
+  // above, the piece is free at y = top + 1, and it cannot rest below top + 2 - h: the column that is
+  // filled at `top` holds a piece cell at offset <= h - 1, which must end up above `top`.  So instead of
+  // stepping down from row 20, find `top` (two rows per word) and test at most h - 1 positions.
+  const uint32_t colmask = ((1u << w) - 1u) << x, colmask2 = colmask | (colmask << 16);
+  int wi = TET_H / 2 - 1;
+  uint32_t pair = 0;
+  while (wi >= 0 && !((pair = tet_row_pair(rows, wi)) & colmask2)) --wi;
+  const int top = wi < 0 ? -1 : ((pair >> 16) & colmask) ? 2 * wi + 1 : 2 * wi;
+  int y = top + 1;
+  const int ymin = top + 2 - h > 0 ? top + 2 - h : 0;
+  while (y > ymin && !tet_collides(rows, shape, h, x, y - 1)) --y;
   if (y + h > TET_H) { done = true; return false; }     // locks out above the board: game over
   int cleared = 0;
 #pragma unroll

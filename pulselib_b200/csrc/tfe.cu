@@ -30,25 +30,79 @@ __device__ __forceinline__ void tfe_write_obs(int32_t* smem, const uint64_t b, c
   __syncthreads();
 }
 
+// ---- step kernel ------------------------------------------------------------------------------------
+// Persistent: one 1024-thread CTA per SM (grid <= 148).  Each CTA stages the 65,536-entry row-move table
+// (uint16 squashed row + uint8 score code = 192 KB) in shared memory once, then its threads walk the boards
+// with a grid stride, prefetching the next board while the current one is processed.  A move is four
+// table lookups instead of four slide-and-merge computations.  Observations leave through a per-warp
+// staging slot: the warp's 32 packed boards go to shared memory and come back out as the warp's contiguous
+// [32, side*side] int32 slab in fully coalesced 16 B stores (side 4) -- no CTA-wide barrier in the loop.
+constexpr int kStepBlock = 1024;
+constexpr int kTableBytes = 65536 * 2 + 65536;                    // result u16 + score code u8
+constexpr int kStepSmem = kTableBytes + kStepBlock * 8;           // + one packed board per thread
+
+template <int SIDE>
+__device__ __forceinline__ void tfe_warp_write_obs(const uint64_t* __restrict__ wboards, const long long wb, const long long n,
+                                                   int32_t* __restrict__ obs_out) {
+  const int lane = threadIdx.x & 31;
+  const int rows = (int)((n - wb) < 32 ? (n - wb) : 32);
+  constexpr int W = SIDE * SIDE;
+  if (SIDE == 4) {
+    int4* dst = reinterpret_cast<int4*>(obs_out + wb * W);
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int q = it * 32 + lane;                               // int4 index = board * 4 + board row
+      if (q < rows * 4) {
+        const uint32_t r16 = (uint32_t)(wboards[q >> 2] >> (16 * (q & 3))) & 0xFFFFu;
+        int4 v;
+        v.x = (int)((1u << (r16 & 15u)) & ~1u); v.y = (int)((1u << ((r16 >> 4) & 15u)) & ~1u);
+        v.z = (int)((1u << ((r16 >> 8) & 15u)) & ~1u); v.w = (int)((1u << (r16 >> 12)) & ~1u);
+        dst[q] = v;
+      }
+    }
+  } else {
+    int32_t* dst = obs_out + wb * W;
+#pragma unroll
+    for (int it = 0; it < W; ++it) {
+      const int q = it * 32 + lane;
+      if (q < rows * W) {
+        const int r = q / W, c = q - r * W;
+        const uint32_t e = (uint32_t)(wboards[r] >> (16 * (c / SIDE) + 4 * (c % SIDE))) & 15u;
+        dst[q] = (int)((1u << e) & ~1u);
+      }
+    }
+  }
+}
+
 template <int SIDE, typename ActT>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kStepBlock, 1)
 tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions, const uint2* __restrict__ chance,
-                const uint4* __restrict__ reset_chance, uint64_t seed, uint64_t env_base, uint32_t counter,
-                uint32_t* counter_dev, int auto_reset, int32_t* __restrict__ obs_out,
-                int32_t* __restrict__ reward_out, uint8_t* __restrict__ done_out, int64_t* __restrict__ score,
-                long long n) {
-  __shared__ int32_t smem[kBlock * (SIDE * SIDE + 1)];
+                const uint4* __restrict__ reset_chance, const uint4* __restrict__ table, uint64_t seed,
+                uint64_t env_base, uint32_t counter, uint32_t* counter_dev, int auto_reset,
+                int32_t* __restrict__ obs_out, int32_t* __restrict__ reward_out, uint8_t* done_out,
+                int64_t* __restrict__ score, long long n) {
+  extern __shared__ uint4 smem_raw[];
   const uint32_t dev_ctr = pulse_counter_read(counter_dev);
   counter += dev_ctr;
-  for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
-    const long long g = base + threadIdx.x;
+  const long long stride = (long long)gridDim.x * kStepBlock;
+  long long g = (long long)blockIdx.x * kStepBlock + threadIdx.x;
+  // first board's inputs are requested before the table copy so their latency hides behind it
+  uint64_t b = 0; int64_t total = 0; int a = 0; bool was_done = false;
+  if (g < n) { b = boards[g]; total = score[g]; a = (int)actions[g]; was_done = auto_reset && done_out[g]; }
+  for (int i = threadIdx.x; i < kTableBytes / 16; i += kStepBlock) smem_raw[i] = table[i];
+  __syncthreads();
+  TfeTableRows rows;
+  rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
+  rows.code = reinterpret_cast<const uint8_t*>(smem_raw) + 65536 * 2;
+  uint64_t* wboards = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes) + (threadIdx.x & ~31);
+  const int lane = threadIdx.x & 31;
+  for (; g - lane < n; g += stride) {                              // warp-uniform trip count
     const bool valid = g < n;
-    uint64_t b = 0;
+    const long long gn = g + stride;
+    uint64_t nb_in = 0; int64_t ntotal = 0; int na = 0; bool ndone = false;
+    if (gn < n) { nb_in = boards[gn]; ntotal = score[gn]; na = (int)actions[gn]; ndone = auto_reset && done_out[gn]; }
+    uint64_t nb = 0;
     if (valid) {
-      b = boards[g];
-      const int a = (int)actions[g];
-      int64_t total = score[g];
-      const bool was_done = auto_reset && tfe_game_over<SIDE>(b);  // done == game_over(board), always
       PulseU4 sp, rc;
       sp.x = sp.y = sp.z = sp.w = 0; rc = sp;
       if (was_done) {
@@ -60,16 +114,31 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
       }
       int32_t reward; bool done;
       const int64_t total0 = total;
-      const uint64_t nb = tfe_step_one<SIDE>(b, a, was_done, auto_reset, sp, rc, total, reward, done);
+      nb = tfe_step_one<SIDE>(b, a, was_done, auto_reset, sp, rc, total, reward, done, rows);
       if (nb != b) boards[g] = nb;
       if (total != total0) score[g] = total;
       reward_out[g] = reward;
       done_out[g] = done;
-      b = nb;
     }
-    if (obs_out) tfe_write_obs<SIDE>(smem, b, valid, base, n, obs_out);
+    if (obs_out) {
+      wboards[lane] = nb;
+      __syncwarp();
+      tfe_warp_write_obs<SIDE>(wboards, g - lane, n, obs_out);
+      __syncwarp();
+    }
+    b = nb_in; total = ntotal; a = na; was_done = ndone;
   }
   pulse_counter_advance(counter_dev, dev_ctr);
+}
+
+// builds the row-move table: result[row] (uint16) then code[row] (uint8), 196,608 bytes
+__global__ void tfe_build_table_kernel(uint16_t* __restrict__ result, uint8_t* __restrict__ code) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < 65536u) {
+    uint32_t sc = 0;
+    result[r] = (uint16_t)tfe_squash_row(r, sc);
+    code[r] = (uint8_t)tfe_score_code(r);
+  }
 }
 
 template <int SIDE>
@@ -105,11 +174,13 @@ tfe_unpack_kernel(const uint64_t* __restrict__ boards, int32_t* __restrict__ val
 
 template <int SIDE>
 __global__ void __launch_bounds__(kBlock)
-tfe_pack_kernel(const int32_t* __restrict__ values, uint64_t* __restrict__ boards, int* __restrict__ bad, long long n) {
+tfe_pack_kernel(const int32_t* __restrict__ values, uint64_t* __restrict__ boards, uint8_t* __restrict__ done,
+                int* __restrict__ bad, long long n) {
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
     uint64_t b;
     if (!tfe_pack_board<SIDE>(values + g * SIDE * SIDE, b) && bad) atomicAdd(bad, 1);
     boards[g] = b;
+    if (done) done[g] = tfe_game_over<SIDE>(b);
   }
 }
 }  // namespace
@@ -121,7 +192,47 @@ tfe_pack_kernel(const int32_t* __restrict__ values, uint64_t* __restrict__ board
     else { constexpr int SD = 2; CALL; }              \
   } while (0)
 
+// ---- per-device row-move table ------------------------------------------------------------------------
+#include <mutex>
+namespace {
+std::mutex g_table_mutex;
+uint4* g_table[64] = {nullptr};
+
+template <int SIDE, typename ActT>
+cudaError_t allow_smem() {
+  return cudaFuncSetAttribute(tfe_step_kernel<SIDE, ActT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
+}
+
+// Builds the table on the current device the first time it is needed (one cudaMalloc, one small kernel,
+// one stream synchronisation -- the only call in the library that may synchronise, and only once).
+int tfe_ensure_table(cudaStream_t stream, const uint4** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) { pulse_set_error("cudaGetDevice failed"); return e ? (int)e : PULSE_EINVAL; }
+  if (!g_table[dev]) {
+    std::lock_guard<std::mutex> lock(g_table_mutex);
+    if (!g_table[dev]) {
+      uint4* t = nullptr;
+      if ((e = cudaMalloc(&t, kTableBytes)) != cudaSuccess) { pulse_set_error("cudaMalloc(row table): %s", cudaGetErrorString(e)); return (int)e; }
+      tfe_build_table_kernel<<<65536 / 256, 256, 0, stream>>>(reinterpret_cast<uint16_t*>(t),
+                                                              reinterpret_cast<uint8_t*>(t) + 65536 * 2);
+      if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) { pulse_set_error("row table build: %s", cudaGetErrorString(e)); cudaFree(t); return (int)e; }
+      allow_smem<4, uint8_t>(); allow_smem<4, int64_t>(); allow_smem<3, uint8_t>(); allow_smem<3, int64_t>();
+      allow_smem<2, uint8_t>(); allow_smem<2, int64_t>();
+      g_table[dev] = t;
+    }
+  }
+  *out = g_table[dev];
+  return PULSE_OK;
+}
+}  // namespace
+
 extern "C" {
+
+int pulse_tfe_init(cudaStream_t stream) {
+  const uint4* t;
+  return tfe_ensure_table(stream, &t);
+}
 
 int pulse_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_t* chance4_or_null, uint64_t seed,
                     uint64_t env_base, uint32_t counter, int32_t* obs_out_or_null, int n_envs, int side,
@@ -139,20 +250,25 @@ int pulse_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint3
 
 int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, const uint32_t* chance2_or_null,
                    const uint32_t* reset_chance4_or_null, uint64_t seed, uint64_t env_base, uint32_t counter,
-                   uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out, uint8_t* done_out,
-                   int64_t* score_inout, int n_envs, int side, cudaStream_t stream) {
+                   uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
+                   uint8_t* done_inout, int64_t* score_inout, int n_envs, int side, cudaStream_t stream) {
   PULSE_REQUIRE(n_envs >= 0, "n_envs < 0");
   PULSE_REQUIRE(side >= 2 && side <= 4, "side must be 2, 3 or 4");
   PULSE_REQUIRE(action_bytes == 1 || action_bytes == 8, "actions must be uint8 or int64");
   if (n_envs == 0) return PULSE_OK;
-  PULSE_REQUIRE(boards && actions && reward_out && done_out && score_inout, "null buffer");
-  const int grid = pulse_grid_for(n_envs, kBlock);
+  PULSE_REQUIRE(boards && actions && reward_out && done_inout && score_inout, "null buffer");
+  PULSE_REQUIRE(!obs_out_or_null || (reinterpret_cast<uintptr_t>(obs_out_or_null) & 15u) == 0, "obs must be 16-byte aligned");
+  const uint4* table = nullptr;
+  int rc = tfe_ensure_table(stream, &table);
+  if (rc) return rc;
+  const long long need = ((long long)n_envs + kStepBlock - 1) / kStepBlock;
+  const int grid = (int)(need < 148 ? need : 148);  // one persistent CTA per SM
 #define TFE_STEP(ACT)                                                                                          \
-  TFE_SIDE_DISPATCH(side, (tfe_step_kernel<SD, ACT><<<grid, kBlock, 0, stream>>>(                              \
+  TFE_SIDE_DISPATCH(side, (tfe_step_kernel<SD, ACT><<<grid, kStepBlock, kStepSmem, stream>>>(                  \
                               boards, (const ACT*)actions, (const uint2*)chance2_or_null,                      \
-                              (const uint4*)reset_chance4_or_null, seed, env_base, counter,                    \
-                              counter_dev_or_null, auto_reset,                                                 \
-                              obs_out_or_null, reward_out, done_out, score_inout, (long long)n_envs)))
+                              (const uint4*)reset_chance4_or_null, table, seed, env_base, counter,             \
+                              counter_dev_or_null, auto_reset, obs_out_or_null, reward_out, done_inout,        \
+                              score_inout, (long long)n_envs)))
   if (action_bytes == 1) TFE_STEP(uint8_t);
   else TFE_STEP(int64_t);
 #undef TFE_STEP
@@ -168,13 +284,13 @@ int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, in
   return pulse_check_launch("pulse_tfe_unpack");
 }
 
-int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, int* bad_count_or_null, int n_envs, int side,
-                   cudaStream_t stream) {
+int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, uint8_t* done_out_or_null, int* bad_count_or_null,
+                   int n_envs, int side, cudaStream_t stream) {
   PULSE_REQUIRE(n_envs >= 0 && side >= 2 && side <= 4, "bad n_envs / side");
   if (n_envs == 0) return PULSE_OK;
   PULSE_REQUIRE(values && boards_out, "null buffer");
   TFE_SIDE_DISPATCH(side, (tfe_pack_kernel<SD><<<pulse_grid_for(n_envs, kBlock), kBlock, 0, stream>>>(
-                              values, boards_out, bad_count_or_null, (long long)n_envs)));
+                              values, boards_out, done_out_or_null, bad_count_or_null, (long long)n_envs)));
   return pulse_check_launch("pulse_tfe_pack");
 }
 }

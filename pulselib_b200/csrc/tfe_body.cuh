@@ -68,17 +68,22 @@ PULSE_HD uint64_t tfe_zero_nibbles(uint64_t x, uint64_t cells) {
 // idx = mulhi32(u0, n_empty) among the empty cells in row-major order, four = u1 > TFE_FOUR_THRESHOLD
 template <int SIDE>
 PULSE_HD uint64_t tfe_add_tile(uint64_t b, uint32_t u0, uint32_t u1) {
-  uint64_t e = tfe_zero_nibbles(b, tfe_cell_mask<SIDE>());
-#ifdef __CUDA_ARCH__
-  const int ne = __popcll(e);
-#else
-  const int ne = __builtin_popcountll(e);
-#endif
+  const uint64_t e = tfe_zero_nibbles(b, tfe_cell_mask<SIDE>());
+  const uint32_t lo = (uint32_t)e, hi = (uint32_t)(e >> 32);
+  const int nlo = PULSE_POPC(lo), ne = nlo + PULSE_POPC(hi);
   if (ne == 0) return b;
   int idx = (int)pulse_mulhi32(u0, (uint32_t)ne);
-  for (; idx > 0; --idx) e &= e - 1;  // drop the idx lowest set bits
-  e &= (~e + 1);                      // isolate the lowest remaining one: 0x1 at the chosen nibble
-  return b | (u1 > TFE_FOUR_THRESHOLD ? e << 1 : e);  // exponent 2 (tile 4) or 1 (tile 2)
+  // position of the idx-th set bit (set bits sit at multiples of 4): halve the window four times
+  int pos = 0;
+  uint32_t w = lo;
+  if (idx >= nlo) { idx -= nlo; w = hi; pos = 32; }
+  int c = PULSE_POPC(w & 0xFFFFu);
+  if (idx >= c) { idx -= c; w >>= 16; pos += 16; }
+  c = PULSE_POPC(w & 0xFFu);
+  if (idx >= c) { idx -= c; w >>= 8; pos += 8; }
+  c = (int)(w & 1u);
+  if (idx >= c) pos += 4;
+  return b | ((uint64_t)(u1 > TFE_FOUR_THRESHOLD ? 2u : 1u) << pos);  // exponent 2 (tile 4) or 1 (tile 2)
 }
 
 // is_game_over_numba (:48-67)
@@ -93,16 +98,44 @@ PULSE_HD bool tfe_game_over(uint64_t b) {
   return true;
 }
 
+// How a 16-bit row is squashed: computed (host and device), or looked up in the 65,536-entry row-move
+// table the step kernel stages in shared memory (tfe.cu).  Both give squash_row_optimized's result; the
+// table is built from tfe_squash_row.
+struct TfeComputedRows {
+  PULSE_HD uint32_t operator()(uint32_t row, uint32_t& score) const { return tfe_squash_row(row, score); }
+};
+// score code of a row: the exponents of its (at most two) merged tiles, 4 bits each, 0 = none
+PULSE_HD uint32_t tfe_score_code(uint32_t row) {
+  uint32_t a0 = row & 15u, a1 = (row >> 4) & 15u, a2 = (row >> 8) & 15u, a3 = (row >> 12) & 15u;
+  if (!a2) { a2 = a3; a3 = 0; }
+  if (!a1) { a1 = a2; a2 = a3; a3 = 0; }
+  if (!a0) { a0 = a1; a1 = a2; a2 = a3; a3 = 0; }
+  uint32_t code = 0;
+  if (a0 && a0 == a1 && a0 < 15u) { code = a0 + 1; a1 = a2; a2 = a3; a3 = 0; }
+  if (a1 && a1 == a2 && a1 < 15u) { code = code ? code | ((a1 + 1) << 4) : a1 + 1; a2 = a3; a3 = 0; }
+  if (a2 && a2 == a3 && a2 < 15u) { code = code ? code | ((a2 + 1) << 4) : a2 + 1; }
+  return code;
+}
+struct TfeTableRows {
+  const uint16_t* result;  // [65536] squashed row
+  const uint8_t* code;     // [65536] tfe_score_code
+  PULSE_HD uint32_t operator()(uint32_t row, uint32_t& score) const {
+    const uint32_t c = code[row];
+    score += ((1u << (c & 15u)) & ~1u) + ((1u << (c >> 4)) & ~1u);  // exponent 0 means "no merge": 1 & ~1 = 0
+    return result[row];
+  }
+};
+
 // the move of TFE.step (:154-178); returns the new board, adds the step's score
-template <int SIDE>
-PULSE_HD uint64_t tfe_move(uint64_t b, int action, uint32_t& score) {
+template <int SIDE, class Rows>
+PULSE_HD uint64_t tfe_move(uint64_t b, int action, uint32_t& score, const Rows& rows) {
   const bool vertical = action & 1, toward_end = (action & 2) != 0;     // 1 up, 3 down; 2 right, 3 down
   if (vertical) b = tfe_transpose(b);
   if (toward_end) b = tfe_reverse_rows<SIDE>(b);
   uint64_t out = 0;
 #pragma unroll
   for (int r = 0; r < SIDE; ++r)
-    out |= (uint64_t)tfe_squash_row((uint32_t)(b >> (16 * r)) & 0xFFFFu, score) << (16 * r);
+    out |= (uint64_t)rows((uint32_t)(b >> (16 * r)) & 0xFFFFu, score) << (16 * r);
   if (toward_end) out = tfe_reverse_rows<SIDE>(out);
   if (vertical) out = tfe_transpose(out);
   return out;
@@ -116,15 +149,15 @@ PULSE_HD uint64_t tfe_reset_board(PulseU4 c) {
 
 // One step of one board (:152-189).  auto_reset (batched-engine extension): a board that was game-over
 // when the step began is reset instead; that step returns reward 0, done 0.
-template <int SIDE>
+template <int SIDE, class Rows>
 PULSE_HD uint64_t tfe_step_one(uint64_t b, int action, bool was_done, int auto_reset, PulseU4 spawn /*x,y*/,
-                               PulseU4 reset_c, int64_t& score_total, int32_t& reward, bool& done) {
+                               PulseU4 reset_c, int64_t& score_total, int32_t& reward, bool& done, const Rows& rows) {
   if (auto_reset && was_done) {
     score_total = 0; reward = 0; done = false;
     return tfe_reset_board<SIDE>(reset_c);
   }
   uint32_t score = 0;
-  b = tfe_move<SIDE>(b, action & 3, score);
+  b = tfe_move<SIDE>(b, action & 3, score, rows);
   b = tfe_add_tile<SIDE>(b, spawn.x, spawn.y);                          // :182 always
   score_total += score;                                                 // :168
 #ifdef __CUDA_ARCH__

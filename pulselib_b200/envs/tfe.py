@@ -46,6 +46,8 @@ class TFEBatched(gym.Env):
         # device_counter: the tape counter lives on the device and is advanced by each step launch, so a
         # captured step can be replayed from a CUDA graph (pulselib_b200.graphs) with fresh chance
         self._ctr = torch.zeros(2, dtype=torch.int32, device=dev) if device_counter else None
+        with _lib.device_guard(dev):  # row-move table of this device (built once)
+            _lib.check(self._lib.pulse_tfe_init(_lib.cuda_stream(dev)), "pulse_tfe_init")
 
     def _chance(self, c, words):
         """uint32 draws [N, words] as an int32-typed device tensor (same bits)."""
@@ -121,7 +123,7 @@ class TFEBatched(gym.Env):
             raise ValueError("values must have shape [n_envs, side, side]")
         bad = torch.zeros(1, dtype=torch.int32, device=self.device)
         with _lib.device_guard(self.device):
-            _lib.check(self._lib.pulse_tfe_pack(ptr(v), ptr(self.boards), ptr(bad), c_i(self.n_envs), c_i(self.side),
+            _lib.check(self._lib.pulse_tfe_pack(ptr(v), ptr(self.boards), ptr(self.done), ptr(bad), c_i(self.n_envs), c_i(self.side),
                                                 _lib.cuda_stream(self.device)), "pulse_tfe_pack")
         if int(bad.item()):
             raise ValueError("board values must be 0 or a power of two in 2..32768")

@@ -102,7 +102,7 @@ static void emu_tfe_step_t(uint64_t* boards, const int64_t* actions, const uint3
     if (reset_chance) { rc.x = reset_chance[4 * g]; rc.y = reset_chance[4 * g + 1]; rc.z = reset_chance[4 * g + 2]; rc.w = reset_chance[4 * g + 3]; }
     else rc = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TFE_RESET, counter);
     int32_t r; bool d;
-    boards[g] = tfe_step_one<SIDE>(b, (int)actions[g], was_done, auto_reset, sp, rc, score[g], r, d);
+    boards[g] = tfe_step_one<SIDE>(b, (int)actions[g], was_done, auto_reset, sp, rc, score[g], r, d, TfeComputedRows());
     reward[g] = r; done[g] = d;
     if (obs) tfe_unpack_board<SIDE>(boards[g], obs + g * SIDE * SIDE);
   }
@@ -133,6 +133,20 @@ int emu_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_
   else if (side == 3) emu_tfe_reset_t<3>(boards, score, done, chance, seed, env_base, counter, obs, n);
   else emu_tfe_reset_t<2>(boards, score, done, chance, seed, env_base, counter, obs, n);
   return 0;
+}
+// the row-move table as the device builds it, exercised through TfeTableRows on every 16-bit row
+int emu_tfe_table_check(void) {
+  static uint16_t res[65536];
+  static uint8_t code[65536];
+  for (uint32_t r = 0; r < 65536; ++r) { uint32_t sc = 0; res[r] = (uint16_t)tfe_squash_row(r, sc); code[r] = (uint8_t)tfe_score_code(r); }
+  TfeTableRows t{res, code};
+  int bad = 0;
+  for (uint32_t r = 0; r < 65536; ++r) {
+    uint32_t s1 = 0, s2 = 0;
+    const uint32_t a = tfe_squash_row(r, s1), b = t(r, s2);
+    bad += (a != b) || (s1 != s2);
+  }
+  return bad;
 }
 int emu_tfe_pack(const int32_t* values, uint64_t* boards, int n, int side) {
   int bad = 0;
