@@ -122,6 +122,35 @@ __device__ __forceinline__ void pulse_counter_advance(uint32_t* ctr, uint32_t se
 }
 #endif
 
+// TMA bulk copy global -> shared, completion on an mbarrier (sm_90+; SASS: UBLKCP).  Used to stage
+// lookup tables: one elected thread issues the copies, nobody spends registers or issue slots on them.
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t pulse_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pulse_mbar_init(uint64_t* bar, uint32_t arrivals) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pulse_smem_u32(bar)), "r"(arrivals) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void pulse_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pulse_smem_u32(bar)), "r"(bytes) : "memory");
+}
+// bytes: multiple of 16; dst and src 16-byte aligned
+__device__ __forceinline__ void pulse_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(pulse_smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(pulse_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void pulse_mbar_wait(uint64_t* bar, uint32_t phase) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "PULSE_MBAR_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra PULSE_MBAR_DONE;\n"
+      "bra PULSE_MBAR_WAIT;\n"
+      "PULSE_MBAR_DONE:\n"
+      "}" ::"r"(pulse_smem_u32(bar)), "r"(phase) : "memory");
+}
+#endif
+
 // Grid sizing: B200 has 148 SMs; grids are a whole number of waves where the problem is big
 // enough, otherwise just enough CTAs to cover it.
 static inline int pulse_grid_for(long long n, int block, int ctas_per_sm = 8) {

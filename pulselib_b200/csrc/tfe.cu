@@ -32,7 +32,8 @@ __device__ __forceinline__ void tfe_write_obs(int32_t* smem, const uint64_t b, c
 
 // ---- step kernel ------------------------------------------------------------------------------------
 // Persistent: one 1024-thread CTA per SM (grid <= 148).  Each CTA stages the 65,536-entry row-move table
-// (uint16 squashed row + uint8 score code = 192 KB) in shared memory once, then its threads walk the boards
+// (uint16 squashed row + uint8 score code = 192 KB) in shared memory once by TMA bulk copy
+// (cp.async.bulk + mbarrier, overlapped with the first board's loads and Philox draw), then its threads walk the boards
 // with a grid stride, prefetching the next board while the current one is processed.  A move is four
 // table lookups instead of four slide-and-merge computations.  Observations leave through a per-warp
 // staging slot: the warp's 32 packed boards go to shared memory and come back out as the warp's contiguous
@@ -89,8 +90,19 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   // first board's inputs are requested before the table copy so their latency hides behind it
   uint64_t b = 0; int64_t total = 0; int a = 0; bool was_done = false;
   if (g < n) { b = boards[g]; total = score[g]; a = (int)actions[g]; was_done = auto_reset && done_out[g]; }
-  for (int i = threadIdx.x; i < kTableBytes / 16; i += kStepBlock) smem_raw[i] = table[i];
+  // table -> shared memory by TMA bulk copies (12 x 16 KB), issued by one thread, landing on an mbarrier
+  __shared__ uint64_t table_bar;
+  if (threadIdx.x == 0) pulse_mbar_init(&table_bar, 1);
   __syncthreads();
+  if (threadIdx.x == 0) {
+    pulse_mbar_expect_tx(&table_bar, kTableBytes);
+    constexpr int kChunk = 16384;
+#pragma unroll 1
+    for (int off = 0; off < kTableBytes; off += kChunk)
+      pulse_bulk_g2s(reinterpret_cast<uint8_t*>(smem_raw) + off, reinterpret_cast<const uint8_t*>(table) + off, kChunk,
+                     &table_bar);
+  }
+  bool table_ready = false;
   TfeTableRows rows;
   rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
   rows.code = reinterpret_cast<const uint8_t*>(smem_raw) + 65536 * 2;
@@ -114,6 +126,7 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
       }
       int32_t reward; bool done;
       const int64_t total0 = total;
+      if (!table_ready) { pulse_mbar_wait(&table_bar, 0); table_ready = true; }  // first board only
       nb = tfe_step_one<SIDE>(b, a, was_done, auto_reset, sp, rc, total, reward, done, rows);
       if (nb != b) boards[g] = nb;
       if (total != total0) score[g] = total;
