@@ -113,7 +113,7 @@ __device__ __forceinline__ void pulse_counter_advance(uint32_t* ctr, uint32_t se
   if (!ctr) return;
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence();
+    // no fence needed: `seen` was consumed (a true dependency) before this point, and the ticket is an atomic
     if (atomicAdd(ctr + 1, 1u) == gridDim.x - 1) {
       ctr[1] = 0;
       *reinterpret_cast<volatile uint32_t*>(ctr) = seen + 1u;
