@@ -97,6 +97,8 @@ def cpu_baseline(wl, min_seconds=10.0, tables=1 << 20):
     from pulselib_b200 import handranks
 
     hr = handranks.load_table()
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = int(pyoracle.lib().oracle_set_threads(avail))   # torchrun exports OMP_NUM_THREADS=1: set it explicitly
     P, M, L = wl["n_players"], wl["max_players"], wl["hand_len"]
     orc = pyoracle.OraclePoker(hr, n_players=P, max_players=M, n_games=tables, **CFG)
     rng = np.random.default_rng(SEED)
@@ -112,7 +114,6 @@ def cpu_baseline(wl, min_seconds=10.0, tables=1 << 20):
         spent += time.perf_counter() - t0
         steps += L * tables
         hands += 1
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     return {"value": steps / spent, "unit": "env-steps/s", "cores": cores, "kind": "port",
             "sample": f"{tables} tables x {hands} hands x {L} steps (reset + step, obs built), oracle/oracle_poker.c "
                       f"with OpenMP on {cores} threads; the reference itself is torch-eager Python and cannot "

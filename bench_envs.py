@@ -207,7 +207,8 @@ def cpu_baseline(name, min_seconds=10.0):
     import numpy as np
     from oracle import pyoracle
 
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = int(pyoracle.lib().oracle_set_threads(avail))   # torchrun exports OMP_NUM_THREADS=1: set it explicitly
     rng = np.random.default_rng(SEED)
     spent, steps = 0.0, 0
     if name == "tfe_4x4":

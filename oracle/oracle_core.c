@@ -181,3 +181,12 @@ void oracle_particle2d_step(float* state, const float* action, int32_t* steps, f
     terminated[i] = (uint8_t)((dist < 0.1f) | (steps[i] >= max_steps));   /* :29 */
   }
 }
+
+/* ---- host threads used by the OpenMP loops (torchrun exports OMP_NUM_THREADS=1; the timed CPU baseline
+ * sets the count explicitly and reports what it really got) ---------------------------------------- */
+#ifdef _OPENMP
+#include <omp.h>
+int oracle_set_threads(int n) { if (n > 0) omp_set_num_threads(n); return omp_get_max_threads(); }
+#else
+int oracle_set_threads(int n) { (void)n; return 1; }
+#endif

@@ -40,11 +40,12 @@ __device__ __forceinline__ void tfe_write_obs(int32_t* smem, const uint64_t b, c
 // [32, side*side] int32 slab in fully coalesced 16 B stores (side 4) -- no CTA-wide barrier in the loop.
 constexpr int kStepBlock = 1024;
 constexpr int kTableBytes = 65536 * 2 + 65536;                    // result u16 + score code u8
-constexpr int kStepSmem = kTableBytes + kStepBlock * 8;           // + one packed board per thread
+constexpr int kLutBytes = 256 * 8;                                // byte (two cells) -> two int32 tile values
+constexpr int kStepSmem = kTableBytes + kStepBlock * 8 + kLutBytes;  // + one packed board per thread + the LUT
 
 template <int SIDE>
-__device__ __forceinline__ void tfe_warp_write_obs(const uint64_t* __restrict__ wboards, const long long wb, const long long n,
-                                                   int32_t* __restrict__ obs_out) {
+__device__ __forceinline__ void tfe_warp_write_obs(const uint64_t* __restrict__ wboards, const uint2* __restrict__ lut,
+                                                   const long long wb, const long long n, int32_t* __restrict__ obs_out) {
   const int lane = threadIdx.x & 31;
   const int rows = (int)((n - wb) < 32 ? (n - wb) : 32);
   constexpr int W = SIDE * SIDE;
@@ -54,11 +55,10 @@ __device__ __forceinline__ void tfe_warp_write_obs(const uint64_t* __restrict__ 
     for (int it = 0; it < 4; ++it) {
       const int q = it * 32 + lane;                               // int4 index = board * 4 + board row
       if (q < rows * 4) {
-        const uint32_t r16 = (uint32_t)(wboards[q >> 2] >> (16 * (q & 3))) & 0xFFFFu;
-        int4 v;
-        v.x = (int)((1u << (r16 & 15u)) & ~1u); v.y = (int)((1u << ((r16 >> 4) & 15u)) & ~1u);
-        v.z = (int)((1u << ((r16 >> 8) & 15u)) & ~1u); v.w = (int)((1u << (r16 >> 12)) & ~1u);
-        dst[q] = v;
+        // one board row = two bytes = two LUT reads (LSU pipe) instead of twelve shift/mask ops (ALU pipe)
+        const uint32_t r16 = (uint32_t)(wboards[q >> 2] >> (16 * (q & 3)));
+        const uint2 a = lut[r16 & 0xFFu], b = lut[__byte_perm(r16, 0, 0x4441)];
+        dst[q] = make_int4((int)a.x, (int)a.y, (int)b.x, (int)b.y);
       }
     }
   } else {
@@ -107,6 +107,10 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
   rows.code = reinterpret_cast<const uint8_t*>(smem_raw) + 65536 * 2;
   uint64_t* wboards = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes) + (threadIdx.x & ~31);
+  uint2* lut = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8);
+  if (threadIdx.x < 256)
+    lut[threadIdx.x] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   for (; g - lane < n; g += stride) {                              // warp-uniform trip count
     const bool valid = g < n;
@@ -136,7 +140,7 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
     if (obs_out) {
       wboards[lane] = nb;
       __syncwarp();
-      tfe_warp_write_obs<SIDE>(wboards, g - lane, n, obs_out);
+      tfe_warp_write_obs<SIDE>(wboards, lut, g - lane, n, obs_out);
       __syncwarp();
     }
     b = nb_in; total = ntotal; a = na; was_done = ndone;
