@@ -315,6 +315,11 @@ static float reward_table(const OraclePoker* s, int g, int64_t a, int actor) {
   return (float)s->alpha * th;
 }
 
+/* poker_reward_gpu called on its own (PokerGPU.py:305-329): no legality masking, actor given by the caller */
+void oracle_poker_reward(const OraclePoker* s, const int64_t* actions, const int32_t* actor_idx, float* out) {
+  for (int g = 0; g < s->n_games; ++g) out[g] = reward_table(s, g, actions[g], actor_idx[g]);
+}
+
 /* step, PokerGPU.py:527-633.  use_cached_equities != 0 skips step 1 (a caller that replaced
  * calculate_equities has already run its own). */
 void oracle_poker_step(OraclePoker* s, const int64_t* actions, float* obs, float* rewards,

@@ -76,8 +76,8 @@ PULSE_HD void compat_step_one(const PulsePokerState& S, const PokerParams& pr, c
   if (phases & PK_PH_RAW_REWARD) {
     actor = actor_idx ? actor_idx[g] : t.idx;
     prev_inv = S.prev_invested[g];
-  } else if (phases & PK_PH_EXECUTE) {
-    S.prev_invested[g] = prev_inv;
+  } else if ((phases & PK_PH_EXECUTE) && (phases & PK_PH_ADVANCE)) {
+    S.prev_invested[g] = prev_inv;                          // written by step (:539), not by execute_actions
   }
   if ((phases & PK_PH_EQUITY) && t.dirty) {                 // :542-543
     for (int s = 0; s < AP; ++s)
@@ -89,7 +89,7 @@ PULSE_HD void compat_step_one(const PulsePokerState& S, const PokerParams& pr, c
   if (phases & PK_PH_ADVANCE) pk_advance(t, pr, deck);      // :547-616
   const bool newly = (phases & PK_PH_NEWLY_IS_DONE) ? t.done : (t.done && !prev_done);  // :619-620
   if ((phases & PK_PH_FOLDWIN) && newly) pk_fold_winner(t, pr);   // :621
-  if ((phases & PK_PH_SHOWDOWN) && newly) pk_showdown(t, pr, deck, PokerCardRanker());  // :622
+  if ((phases & PK_PH_SHOWDOWN) && newly) pk_showdown(t, pr, deck, PokerFaithfulRanker{S.hand_ranks, (long long)S.n_hand_ranks});  // :622
   if ((phases & PK_PH_CLEAR) && t.done) {                   // :625-628
 #pragma unroll
     for (int s = 0; s < MAXP; ++s) { t.crb[s] = 0; t.inv[s] = 0; }

@@ -68,6 +68,23 @@ PULSE_HD int pk_next_active(uint32_t st, int from, int AP) {
   return PULSE_FFS(above ? above : a) - 1;
 }
 
+// The reference's own chained walk p = HR[p + card] from 53 (:437-444, :477-478), with torch's wrap of
+// negative indices.  Needed only where a seat's cards are NOT distinct valid cards (the reference's
+// white-box tests put -1 boards and colliding cards into the state): there the table's answer is
+// arbitrary but deterministic, and only the walk itself reproduces it.  Valid hands never come here.
+PULSE_HD int32_t pk_hr_at(const int32_t* __restrict__ hr, long long n, long long i) {
+  if (i < 0) i += n;
+  return (i >= 0 && i < n) ? PULSE_LDG(hr + i) : 0;
+}
+PULSE_HD int32_t pk_table_walk(const int32_t* __restrict__ hr, long long n, int h0, int h1,
+                               const int32_t (&board)[5], int n_board) {
+  int32_t p = pk_hr_at(hr, n, 53ll + h0);
+  p = pk_hr_at(hr, n, (long long)p + h1);
+  for (int i = 0; i < n_board; ++i) p = pk_hr_at(hr, n, (long long)p + board[i]);
+  return p;
+}
+PULSE_HD int pk_popc64(uint64_t m) { return PULSE_POPC((uint32_t)m) + PULSE_POPC((uint32_t)(m >> 32)); }
+
 // The reference's hand-strength proxy for one seat (:455-525).  stage 3: 7-card value; stage 2:
 // 6-card value; stage 1: HR[HR[p5]] where HR[p5] is the 5-card value, i.e. one real lookup into the
 // low part of the table (only its first 36,875 entries are ever touched).
@@ -78,11 +95,16 @@ PULSE_HD float pk_equity(int stage, int h0, int h1, const int32_t (&board)[5],
   m = pe_add_card64(board[2], pe_add_card64(board[1], pe_add_card64(board[0], m)));
   if (stage >= 2) m = pe_add_card64(board[3], m);
   if (stage >= 3) m = pe_add_card64(board[4], m);
-  int v = pe_eval_mask64(m);
+  int v;
   float lo = 4109.0f, den = 32765.0f;  // :17-18, :65
-  if (stage == 1) {
-    v = (v >= 0 && v < n_hr) ? PULSE_LDG(hand_ranks + v) : 0;  // :521
-    lo = 74359.0f; den = 749420.0f;                        // :15-16, :66
+  if (stage == 1) { lo = 74359.0f; den = 749420.0f; }      // :15-16, :66
+  if (pk_popc64(m) == stage + 4) {
+    v = pe_eval_mask64(m);
+    if (stage == 1) v = pk_hr_at(hand_ranks, n_hr, v);      // :521 (non-negative here)
+  } else {  // invalid or repeated cards: the literal walk (:477-478, :497-500, :518-521)
+    v = pk_table_walk(hand_ranks, n_hr, h0, h1, board, stage + 2);
+    if (stage <= 2) v = pk_hr_at(hand_ranks, n_hr, v);
+    if (stage == 1) v = pk_hr_at(hand_ranks, n_hr, v);
   }
   float e = PULSE_FDIV(PULSE_FSUB((float)v, lo), den);
   return fminf(fmaxf(e, 0.0f), 1.0f);
@@ -181,6 +203,20 @@ PULSE_HD void pk_fold_winner(PokerTable<MAXP>& t, const PokerParams& pr) {
 
 // resolve_terminated_games + _award_showdown_side_pots (:380-453, :340-378)
 // Ranker::rank(t, s) gives the showdown value of live seat s once the board is complete.
+// Reference-shaped layout: computed evaluator for seven distinct valid cards, the literal table walk otherwise.
+struct PokerFaithfulRanker {
+  const int32_t* hr; long long n;
+  template <int MAXP>
+  PULSE_HD int32_t rank(const PokerTable<MAXP>& t, int s) const {
+    const int h0 = pk_sel(t.hole0, s), h1 = pk_sel(t.hole1, s);
+    uint64_t m = pe_add_card64(h1, pe_add_card64(h0, 0));
+#pragma unroll
+    for (int i = 0; i < 5; ++i) m = pe_add_card64(t.board[i], m);
+    if (pk_popc64(m) == 7) return pe_eval_mask64(m);
+    return pk_table_walk(hr, n, h0, h1, t.board, 5);
+  }
+};
+
 struct PokerCardRanker {  // evaluates the seat's two hole cards + the five board cards
   template <int MAXP>
   PULSE_HD int32_t rank(const PokerTable<MAXP>& t, int s) const {

@@ -117,3 +117,65 @@ def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, 
             np.testing.assert_allclose(to_np(ra), to_np(rb), rtol=REWARD_RTOL, atol=reward_atol(alpha), err_msg=tag + " reward")
             if to_np(da).all():
                 break
+
+
+# ---- replay of the call traces recorded from the reference's own unit tests -------------------------------
+# tests/golden/poker_reftests.npz (made by tests/golden/record_reference_tests.py): every top-level env call
+# the reference's tests/poker/test_poker_gpu_*.py make on the reference env, with full state before/after.
+KAT_N = ("deck_positions", "pots", "stages", "button", "sb", "bb", "idx", "highest", "agg", "acted",
+         "last_raise_size", "prev_invested")
+KAT_NP = ("stacks", "current_round_bet", "total_invested", "status")
+KAT_OTHER = ("decks", "board", "hands", "is_done", "equity_dirty", "equities")
+
+
+class KatRecord:
+    def __init__(self, z, i):
+        self.i, self.test, self.method = i, str(z["tests"][i]), str(z["methods"][i])
+        self.env_id, self.first, self.had_button = int(z["env_ids"][i]), bool(z["first_reset"][i]), bool(z["had_button"][i])
+        pre = f"r{i}/"
+        self.ctor, self.args, self.before, self.after, self.ret = {}, {}, {}, {}, {}
+        for k in z.files:
+            if k.startswith(pre):
+                _, part, name = k.split("/")
+                getattr(self, part)[name] = z[k]
+        self.ctor = {k: (float(v) if k in ("w1", "w2") else int(v)) for k, v in self.ctor.items()}
+
+
+def load_reference_kat():
+    z = np.load(GOLDEN / "poker_reftests.npz")
+    return [KatRecord(z, i) for i in range(int(z["n_records"]))]
+
+
+def replay_reference_kat(make_engine, records=None):
+    """make_engine(ctor_kwargs) -> adapter with set_state(dict, active_players), get_state(name),
+    reset(rec) -> obs, call(rec) -> dict of returned arrays.  Every record is replayed on a fresh engine:
+    set "before", make the call, compare with "after" (ints/obs exact, fp32 reward within tolerance)."""
+    records = records if records is not None else load_reference_kat()
+    checked = 0
+    for r in records:
+        eng = make_engine(r.ctor)
+        tag = f"[{r.i}] {r.test} :: {r.method}"
+        eng.set_state(r.before, int(r.before["active_players"]), r)
+        ret = eng.reset(r) if r.method == "reset" else eng.call(r)
+        assert int(eng.get_state("active_players")) == int(r.after["active_players"]), tag + " active_players"
+        for f in KAT_N + KAT_NP + KAT_OTHER:
+            if f not in r.after:
+                continue
+            want, got = r.after[f], np.asarray(eng.get_state(f))
+            if f == "equities":
+                ap = int(r.after["active_players"])   # columns >= active_players are never read (see set_state)
+                np.testing.assert_array_equal(got.reshape(want.shape[0], -1)[:, :ap], want[:, :ap], err_msg=tag + " equities")
+                continue
+            got = got.astype(want.dtype).reshape(want.shape)
+            if not np.array_equal(got, want):
+                bad = tuple(np.argwhere(got != want)[0])
+                raise AssertionError(f"{tag}: {f} at {bad}: got {got[bad]} want {want[bad]}")
+        alpha = abs(r.ctor["alpha"])
+        for k, want in r.ret.items():
+            got = np.asarray(ret[k])
+            if k == "reward" or (k == "value" and r.method == "poker_reward_gpu"):
+                np.testing.assert_allclose(got, want, rtol=REWARD_RTOL, atol=reward_atol(alpha), err_msg=tag + " " + k)
+            else:
+                np.testing.assert_array_equal(got.astype(want.dtype).reshape(want.shape), want, err_msg=tag + " ret " + k)
+        checked += 1
+    return checked
