@@ -13,6 +13,48 @@ constexpr int kBlock = 128;
 // per store instruction).  MT > 0: max_players is the compile-time constant MT, W % 4 == 0, rows
 // are staged as float4 with an odd row stride (in 16 B units) so both sides are conflict-free.
 // MT == 0: any max_players, scalar staging with row stride W + 1.
+// Ends with a block barrier so the staging buffer can be reused by the next grid-stride iteration.
+template <int MT, int WT>
+__device__ __forceinline__ void stage_obs_rows(const float (&row)[WT], float4* smem4, float* __restrict__ obs_out,
+                                               long long base, long long g, long long n, int W) {
+  const long long rows = (n - base) < kBlock ? (n - base) : kBlock;
+  if (MT > 0) {
+    constexpr int W4 = WT / 4, S4 = W4 | 1;
+    if (g < n) {
+#pragma unroll
+      for (int c = 0; c < W4; ++c)
+        smem4[threadIdx.x * S4 + c] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+    }
+    __syncthreads();
+    float4* dst = reinterpret_cast<float4*>(obs_out + base * WT);
+    const int total = (int)rows * W4;
+#pragma unroll
+    for (int it = 0; it < W4; ++it) {
+      const int q = threadIdx.x + it * kBlock;
+      if (q < total) {
+        const int r = q / W4, c = q - r * W4;
+        dst[q] = smem4[r * S4 + c];
+      }
+    }
+  } else {
+    float* smem = reinterpret_cast<float*>(smem4);
+    float* mine = smem + threadIdx.x * (W + 1);
+    if (g < n)
+      for (int i = 0; i < W; ++i) mine[i] = row[i];
+    __syncthreads();
+    const int total = (int)rows * W;
+    float* dst = obs_out + base * W;
+    const int dq = kBlock / W, dr = kBlock - dq * W;
+    int r = threadIdx.x / W, c = threadIdx.x - r * W;
+    for (int e = threadIdx.x; e < total; e += kBlock) {
+      dst[e] = smem[r * (W + 1) + c];
+      r += dq; c += dr;
+      if (c >= W) { c -= W; ++r; }
+    }
+  }
+  __syncthreads();
+}
+
 template <int MAXP, int MT, int MINB>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
@@ -29,57 +71,32 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
     if (g < n)
       packed_step_one<MAXP>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base, starting_bbs,
                             max_bbs, g, n);
-    const long long rows = (n - base) < kBlock ? (n - base) : kBlock;
-    if (MT > 0) {
-      constexpr int W4 = WT / 4, S4 = W4 | 1;
-      if (g < n) {
-#pragma unroll
-        for (int c = 0; c < W4; ++c)
-          smem4[threadIdx.x * S4 + c] = make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
-      }
-      __syncthreads();
-      float4* dst = reinterpret_cast<float4*>(obs_out + base * WT);
-      const int total = (int)rows * W4;
-#pragma unroll
-      for (int it = 0; it < W4; ++it) {
-        const int q = threadIdx.x + it * kBlock;
-        if (q < total) {
-          const int r = q / W4, c = q - r * W4;
-          dst[q] = smem4[r * S4 + c];
-        }
-      }
-    } else {
-      float* smem = reinterpret_cast<float*>(smem4);
-      float* mine = smem + threadIdx.x * (W + 1);
-      if (g < n)
-        for (int i = 0; i < W; ++i) mine[i] = row[i];
-      __syncthreads();
-      const int total = (int)rows * W;
-      float* dst = obs_out + base * W;
-      const int dq = kBlock / W, dr = kBlock - dq * W;
-      int r = threadIdx.x / W, c = threadIdx.x - r * W;
-      for (int e = threadIdx.x; e < total; e += kBlock) {
-        dst[e] = smem[r * (W + 1) + c];
-        r += dq; c += dr;
-        if (c >= W) { c -= W; ++r; }
-      }
-    }
-    __syncthreads();
+    stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
   }
 }
 
-template <int MAXP>
-__global__ void __launch_bounds__(kBlock)
+// Whole-batch deal.  Shared memory: the shuffle scratch (13 words per thread, word-interleaved, see
+// PackedDeckShared) followed by the observation staging buffer of stage_obs_rows.
+constexpr int kDeckSmemBytes = 13 * kBlock * 4;
+
+template <int MAXP, int MT>
+__global__ void __launch_bounds__(kBlock, MAXP <= 2 ? 8 : MAXP <= 6 ? 5 : 3)
 poker_packed_reset_kernel(PulsePokerPacked S, PokerParams pr, const int32_t* __restrict__ prefixed, uint64_t seed,
                           uint64_t env_base, uint32_t hand, int rotation, int first_reset, int starting_bbs,
                           int max_bbs, float* __restrict__ obs_out, long long n) {
+  extern __shared__ float4 smem4[];
+  if (MT > 0) pr.M = MT;
+  constexpr int WT = MT > 0 ? 13 + 3 * (MT - 1) : 13 + 3 * 15;
   const int W = 13 + 3 * (pr.M - 1);
-  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
-    float row[13 + 3 * 15];
-    packed_reset_one<MAXP>(S, pr, prefixed, seed, env_base, hand, rotation, first_reset, starting_bbs, max_bbs,
-                           obs_out ? row : nullptr, g, n);
-    if (obs_out)
-      for (int i = 0; i < W; ++i) obs_out[g * W + i] = row[i];
+  PackedDeckShared dk{reinterpret_cast<uint8_t*>(smem4) + 4 * threadIdx.x, 4 * kBlock};
+  float4* stage = smem4 + kDeckSmemBytes / 16;
+  for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
+    const long long g = base + threadIdx.x;
+    float row[WT];
+    if (g < n)
+      packed_reset_one<MAXP>(S, pr, prefixed, seed, env_base, hand, rotation, first_reset, starting_bbs, max_bbs,
+                             obs_out ? row : nullptr, g, n, dk);
+    if (obs_out) stage_obs_rows<MT, WT>(row, stage, obs_out, base, g, n, W);  // obs_out is uniform: barriers are safe
   }
 }
 
@@ -125,9 +142,22 @@ int pulse_poker_packed_reset(const PulsePokerPacked* st, const PulsePokerConfig*
   if (cfg->n_games == 0) return PULSE_OK;
   PokerParams pr = make_params(cfg);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
-  PKP_DISPATCH(pr.P, (poker_packed_reset_kernel<MP><<<grid, kBlock, 0, stream>>>(
-                         *st, pr, prefixed, seed, env_base, hand_counter, rotation, first_reset, cfg->starting_bbs,
-                         cfg->max_bbs, obs_out, (long long)cfg->n_games)));
+  const int W = 13 + 3 * (pr.M - 1);
+#define PKP_RESET(MP, MT, STAGE)                                                                                   \
+  poker_packed_reset_kernel<MP, MT><<<grid, kBlock, kDeckSmemBytes + (STAGE), stream>>>(                            \
+      *st, pr, prefixed, seed, env_base, hand_counter, rotation, first_reset, cfg->starting_bbs, cfg->max_bbs,     \
+      obs_out, (long long)cfg->n_games)
+#define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
+  const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
+  if (pr.P <= 2 && pr.M == 2 && aligned) PKP_RESET(2, 2, PKP_SMEM4(2));
+  else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) PKP_RESET(6, 6, PKP_SMEM4(6));
+  else if (pr.P > 6 && pr.M == 10 && aligned) PKP_RESET(10, 10, PKP_SMEM4(10));
+  else {
+    const size_t stage = (size_t)kBlock * (W + 1) * sizeof(float);
+    PKP_DISPATCH(pr.P, PKP_RESET(MP, 0, stage));
+  }
+#undef PKP_RESET
+#undef PKP_SMEM4
   return pulse_check_launch("pulse_poker_packed_reset");
 }
 

@@ -119,31 +119,57 @@ PULSE_HD void packed_store(const PokerTable<MAXP>& t, const PokerTable<MAXP>& o,
     }
 }
 
+// Scratch for the partial Fisher-Yates shuffle: 52 card bytes addressed by a run-time index.  In a
+// thread's local memory such an array costs one L1 sector per lane per access (lanes index different
+// bytes) -- the reset kernel spent 28% of its stall samples on STL/LDL.  PackedDeckShared keeps it in
+// shared memory, word-interleaved across the block's threads (byte i of thread t lives in word
+// (i / 4) * block + t), so any index pattern across a warp is bank-conflict free.
+struct PackedDeckLocal {
+  uint8_t d[52];
+  PULSE_HD int get(int i) const { return d[i]; }
+  PULSE_HD void set(int i, int v) { d[i] = (uint8_t)v; }
+  PULSE_HD void fill_identity() { for (int i = 0; i < 52; ++i) d[i] = (uint8_t)(i + 1); }
+};
+struct PackedDeckShared {
+  uint8_t* base;     // this thread's byte 0 of word 0
+  int word_stride;   // bytes between consecutive words of one thread: 4 * blockDim.x
+  PULSE_HD int get(int i) const { return base[(i >> 2) * word_stride + (i & 3)]; }
+  PULSE_HD void set(int i, int v) { base[(i >> 2) * word_stride + (i & 3)] = (uint8_t)v; }
+  PULSE_HD void fill_identity() {
+#pragma unroll
+    for (int w = 0; w < 13; ++w)  // cards 4w+1 .. 4w+4, little endian
+      *reinterpret_cast<uint32_t*>(base + w * word_stride) = 0x04030201u + 0x04040404u * (uint32_t)w;
+  }
+};
+
 // Deals a new hand to one table (PokerGPU.py:73-157 for a single row).  Cards come from
 // `prefixed` (int32 [N,52]) or from the chance tape; only the first 2AP+8 deck positions matter.
 // keep_stacks == 0 fills every stack with starting_bbs; otherwise busted / oversized stacks are
 // refilled and rolled by `rotation`.
-template <int MAXP>
+template <int MAXP, class DeckBuf>
 PULSE_HD void packed_deal(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPacked& S, const PokerParams& pr,
                           const int32_t* __restrict__ prefixed, uint64_t seed, uint64_t env_id, uint32_t hand,
                           int rotation, int keep_stacks, int button, int starting_bbs, int max_bbs, long long g,
-                          long long n) {
+                          long long n, DeckBuf& dk) {
   const int P = pr.P, AP = pr.AP;
   const int need = 2 * AP + 8;
-  uint8_t d[52];
   if (prefixed) {
-    for (int i = 0; i < need; ++i) d[i] = (uint8_t)prefixed[g * 52 + i];
+    for (int i = 0; i < need; ++i) dk.set(i, prefixed[g * 52 + i]);
   } else {
-    for (int i = 0; i < 52; ++i) d[i] = (uint8_t)(i + 1);
+    dk.fill_identity();
     PulseU4 blk;
     blk.x = blk.y = blk.z = blk.w = 0;
     for (int i = 0; i < need; ++i) {  // forward Fisher-Yates fixes position i at iteration i
       if ((i & 3) == 0) blk = pulse_tape(seed, env_id, PULSE_STREAM_POKER_DECK, hand * 16u + (uint32_t)(i >> 2));
       uint32_t u = (i & 3) == 0 ? blk.x : (i & 3) == 1 ? blk.y : (i & 3) == 2 ? blk.z : blk.w;
       int j = i + (int)pulse_mulhi32(u, (uint32_t)(52 - i));
-      uint8_t tmp = d[i]; d[i] = d[j]; d[j] = tmp;
+      const int ci = dk.get(i), cj = dk.get(j);
+      dk.set(j, ci); dk.set(i, cj);
     }
   }
+  // the cards this deal uses: two per dealt seat, then burn/flop/burn/turn/burn/river
+  const int b0 = 2 * AP;
+  const int f0 = dk.get(b0 + 1), f1 = dk.get(b0 + 2), f2 = dk.get(b0 + 3), tn = dk.get(b0 + 5), rv = dk.get(b0 + 7);
   int32_t old[MAXP];
 #pragma unroll
   for (int s = 0; s < MAXP; ++s) {
@@ -161,8 +187,8 @@ PULSE_HD void packed_deal(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
     t.stack[s] = s < P ? pk_sel(old, keep_stacks ? src : s) : 0;
     t.crb[s] = 0; t.inv[s] = 0;
     const bool dealt = s < AP;
-    t.hole0[s] = dealt ? d[2 * s] : -1;
-    t.hole1[s] = dealt ? d[2 * s + 1] : -1;
+    t.hole0[s] = dealt ? dk.get(2 * s) : -1;
+    t.hole1[s] = dealt ? dk.get(2 * s + 1) : -1;
     if (s < P) st = pk_set_status(st, s, dealt ? PK_ACTIVE : PK_SITOUT);
   }
   t.st = st;
@@ -175,34 +201,53 @@ PULSE_HD void packed_deal(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
   for (int i = 0; i < 5; ++i) t.board[i] = -1;
   t.stage = 0; t.idx = AP == 2 ? button : (bb + 1) % AP;           // :130-133
   t.agg = bb; t.acted = 0; t.button = button; t.deck_pos = 2 * AP; t.done = false; t.dirty = false;
-  const int b0 = 2 * AP;
-  fb = (uint32_t)d[b0 + 1] | ((uint32_t)d[b0 + 2] << 6) | ((uint32_t)d[b0 + 3] << 12) |
-       ((uint32_t)d[b0 + 5] << 18) | ((uint32_t)d[b0 + 7] << 24);
+  fb = (uint32_t)f0 | ((uint32_t)f1 << 6) | ((uint32_t)f2 << 12) | ((uint32_t)tn << 18) | ((uint32_t)rv << 24);
   // hand values of every dealt seat on the flop, turn and river boards of this deal
-  const uint64_t flop = pe_add_card64(d[b0 + 3], pe_add_card64(d[b0 + 2], pe_add_card64(d[b0 + 1], 0)));
-  const uint64_t turn = pe_add_card64(d[b0 + 5], flop), river = pe_add_card64(d[b0 + 7], turn);
-  for (int s = 0; s < AP; ++s) {
-    const uint64_t h = pe_add_card64(d[2 * s + 1], pe_add_card64(d[2 * s], 0));
+  const uint64_t flop = pe_add_card64(f2, pe_add_card64(f1, pe_add_card64(f0, 0)));
+  const uint64_t turn = pe_add_card64(tn, flop), river = pe_add_card64(rv, turn);
+  for (int s = 0; s < AP; ++s) {  // rolled: one copy of the evaluator, hole cards re-read from the scratch
+    const uint64_t h = pe_add_card64(dk.get(2 * s + 1), pe_add_card64(dk.get(2 * s), 0));
     const int v5 = pe_eval_mask64(h | flop), v6 = pe_eval_mask64(h | turn), v7 = pe_eval_mask64(h | river);
     const int f = (v5 >= 0 && v5 < S.n_hand_ranks) ? PULSE_LDG(S.hand_ranks + v5) : 0;  // HR[HR[p5]] (:521)
     S.ev[(long long)s * n + g] = (uint64_t)(uint32_t)v7 | ((uint64_t)(uint32_t)v6 << 16) | ((uint64_t)(uint32_t)f << 32);
   }
 }
 
-// equity of seat `s` at `stage` from the stored hand values (PokerGPU.py:455-525)
-PULSE_HD float pkp_equity(const PulsePokerPacked& S, int stage, int s, long long g, long long n) {
+// equity of a seat at `stage` from its stored hand-value word (PokerGPU.py:455-525)
+PULSE_HD float pkp_equity_from(uint64_t ev, int stage) {
   if (stage < 1 || stage > 3) return 0.5f;  // :461
-  const uint64_t ev = S.ev[(long long)s * n + g];
   const int v = stage == 3 ? (int)(ev & 0xFFFFu) : stage == 2 ? (int)((ev >> 16) & 0xFFFFu) : (int)(ev >> 32);
   const float lo = stage == 1 ? 74359.0f : 4109.0f, den = stage == 1 ? 749420.0f : 32765.0f;  // :15-18, :65-66
   const float e = PULSE_FDIV(PULSE_FSUB((float)v, lo), den);
   return fminf(fmaxf(e, 0.0f), 1.0f);
 }
 
-struct PackedEvRanker {  // showdown rank = the stored seven-card value
+// Hand-value words of one table.  PRE == true (heads-up): both seats' words are requested together
+// with the rest of the table, so neither the actor's equity nor the showdown waits for a second,
+// dependent trip to DRAM (+8 B read per table-step).  PRE == false: one word is fetched when it is
+// needed (the actor's, or each live seat's at showdown) -- with six or ten seats prefetching all of
+// them would cost more bandwidth than the latency is worth.
+template <int MAXP, bool PRE>
+struct PackedEv {
   const uint64_t* ev; long long g, n;
-  template <int MAXP>
-  PULSE_HD int32_t rank(const PokerTable<MAXP>&, int s) const { return (int32_t)(ev[(long long)s * n + g] & 0xFFFFu); }
+  uint64_t w[PRE ? MAXP : 1];
+  PULSE_HD void prefetch(int AP) {
+    if (PRE) {
+#pragma unroll
+      for (int s = 0; s < MAXP; ++s) w[s] = s < AP ? ev[(long long)s * n + g] : 0;
+    }
+  }
+  PULSE_HD uint64_t word(int s) const {
+    if (PRE) {
+      uint64_t v = w[0];
+#pragma unroll
+      for (int k = 1; k < (PRE ? MAXP : 1); ++k) if (s == k) v = w[k];
+      return v;
+    }
+    return ev[(long long)s * n + g];
+  }
+  template <int MP>
+  PULSE_HD int32_t rank(const PokerTable<MP>&, int s) const { return (int32_t)(word(s) & 0xFFFFu); }  // showdown rank = seven-card value
 };
 
 // unconditional store of a freshly dealt table
@@ -232,12 +277,15 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   const int P = pr.P, AP = pr.AP;
   PokerTable<MAXP> t;
   uint32_t fb;
+  PackedEv<MAXP, (MAXP <= 2)> evw{S.ev, g, n};
+  evw.prefetch(AP);
   packed_load(t, fb, S, g, n, AP);
   if (auto_reset && t.done) {
     uint32_t hand = S.hand_ctr[g] + 1u;
     S.hand_ctr[g] = hand;
+    PackedDeckLocal dk;
     packed_deal(t, fb, S, pr, nullptr, seed, env_base + (uint64_t)g, hand, 0, 1, t.button + 1 < AP ? t.button + 1 : (t.button + 1) % AP,
-                starting_bbs, max_bbs, g, n);
+                starting_bbs, max_bbs, g, n, dk);
     packed_store_all(t, fb, S, g, n, P);
     reward_out[g] = 0.0f;
     done_out[g] = 0;
@@ -253,12 +301,12 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   const int prev_inv = pk_sel(t.crb, actor);                         // :539
   float e = 0.5f;
   if (legal)  // the reward is zeroed otherwise (:632), so the equity is only needed for legal actors
-    e = pkp_equity(S, t.stage, actor, g, n);
+    e = (t.stage >= 1 && t.stage <= 3) ? pkp_equity_from(evw.word(actor), t.stage) : 0.5f;
   pk_execute(t, a);                                                  // :546
   pk_advance(t, pr, deck);                                           // :547-616
   if (t.done && !prev_done) {                                        // :619-622
     pk_fold_winner(t, pr);
-    pk_showdown(t, pr, deck, PackedEvRanker{S.ev, g, n});
+    pk_showdown(t, pr, deck, evw);
   }
   if (t.done) {                                                      // :625-628
 #pragma unroll
@@ -271,19 +319,29 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   pk_obs(t, pr, obs_row);                                            // :633
 }
 
-template <int MAXP>
+template <int MAXP, class DeckBuf>
 PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr, const int32_t* __restrict__ prefixed,
                                uint64_t seed, uint64_t env_base, uint32_t hand, int rotation, int first_reset,
-                               int starting_bbs, int max_bbs, float* __restrict__ obs_row, long long g, long long n) {
+                               int starting_bbs, int max_bbs, float* __restrict__ obs_row, long long g, long long n,
+                               DeckBuf& dk) {
   PokerTable<MAXP> t;
   uint32_t fb;
   int button = 0;
   if (!(first_reset & 2)) button = (int)(((S.tbl[4 * g] >> 11) & 15u) + 1u) % pr.AP;  // :121
   packed_deal(t, fb, S, pr, prefixed, seed, env_base + (uint64_t)g, hand, rotation, !(first_reset & 1), button,
-              starting_bbs, max_bbs, g, n);
+              starting_bbs, max_bbs, g, n, dk);
   packed_store_all(t, fb, S, g, n, pr.P);
   if (S.hand_ctr) S.hand_ctr[g] = hand;
   if (obs_row) pk_obs(t, pr, obs_row);
+}
+
+template <int MAXP>
+PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr, const int32_t* __restrict__ prefixed,
+                               uint64_t seed, uint64_t env_base, uint32_t hand, int rotation, int first_reset,
+                               int starting_bbs, int max_bbs, float* __restrict__ obs_row, long long g, long long n) {
+  PackedDeckLocal dk;
+  packed_reset_one<MAXP>(S, pr, prefixed, seed, env_base, hand, rotation, first_reset, starting_bbs, max_bbs, obs_row,
+                         g, n, dk);
 }
 
 // packed -> reference-shaped tensors (for inspection and parity checks); decks, sb/bb, equities and
