@@ -23,6 +23,14 @@ SPECS = {
                         "the chance tape, auto-reset on lock-out, rows tensor is the observation"),
     "particle2d": dict(n=1 << 24, algo_bytes=70, kernel="particle2d_step_kernel", graph=0, actions=4,
                        desc="Particle2D fp32, {n} envs/GPU, dt=0.1, max_steps=200, uniform actions in [-1,1]^2"),
+    # build_actions + step as ONE launch (scripted seats evaluated inside the step kernel),
+    # per-table auto-reset.  Bytes: the step's 201 B with the 8 B action read replaced by the 8 B write of
+    # the action that was played.
+    "poker_hu_scripted": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_step_kernel<2, 2, 10, true>", graph=0,
+                              actions=1,
+                              desc="PokerGPU heads-up, {n} tables/GPU, seats played by the scripted TightAggressive and "
+                                   "SmallBall rules inside the step kernel (no action tensor), draws from the chance "
+                                   "tape, per-table auto-reset"),
     "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_step_kernel", graph=0, actions=8,
                       desc="Blackjack, {n} envs/GPU (the reference's CPU-sized config), uniform hit/stand, whole-batch "
                            "reset every 8 steps inside the timed region; working set is L2-resident by construction"),
@@ -64,6 +72,18 @@ def _make(name, dev, n, rank, e2e=False):
         def step(e, a):
             o, r, t, _, _ = e.step(a)
             return o, r, t
+    elif name == "poker_hu_scripted":
+        from pulselib_b200 import policy
+        from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+        env = PokerGPUPacked(dev, n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3,
+                             K=100, alpha=50, seed=SEED, env_base=rank * n, auto_reset=True)
+        acts = torch.zeros((L, 1), dtype=torch.int64, device=dev)
+        kinds = bytes([policy.TIGHT_AGGRESSIVE, policy.SMALL_BALL])
+
+        def step(e, a):
+            o, r, d, _, info = e.step_policy(kinds)
+            return o, r, d, info["actions"]
     elif name == "blackjack":
         from pulselib_b200.envs.blackjack import BlackJack
 
@@ -253,6 +273,26 @@ def cpu_baseline(name, min_seconds=10.0):
             spent += time.perf_counter() - t0
             steps += n; k += 1
         sample = f"{n} envs x {k} steps, oracle/oracle_core.c::oracle_particle2d_step"
+    elif name == "poker_hu_scripted":
+        from pulselib_b200 import handranks
+
+        n = 1 << 20
+        kw = dict(n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3, K=100, alpha=50)
+        orc = pyoracle.OraclePoker(handranks.load_table(), **kw)
+        kinds = np.array([3, 5], np.uint8)
+        ch = [rng.integers(0, 2**32, (n, 2), dtype=np.uint64).astype(np.uint32) for _ in range(4)]
+        acts = np.zeros(n, np.int64)
+        k = hands = 0
+        while spent < min_seconds:
+            orc.tape_decks(SEED, 0, hands)
+            t0 = time.perf_counter()
+            orc.reset(None)
+            for i in range(16):   # whole-batch hands: the oracle has no per-table auto-reset
+                pyoracle.poker_policy(orc.obs, orc.idx, kinds, ch[i % 4], acts)
+                orc.step(acts)
+            spent += time.perf_counter() - t0
+            steps += 16 * n; k += 16; hands += 1
+        sample = f"{n} tables x {hands} hands x 16 steps (oracle policy + reset + step, obs built), oracle/oracle_poker.c"
     elif name == "blackjack":
         n = 4096
         orc = pyoracle.OracleBlackjack(n)

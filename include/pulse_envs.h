@@ -222,6 +222,36 @@ int pulse_poker_packed_reset(const PulsePokerPacked* st, const PulsePokerConfig*
 int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int64_t* actions,
                             float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset, uint64_t seed,
                             uint64_t env_base, pulse_stream_t stream);
+/* ---- scripted opponents + build_actions ---------------------------------------
+ * Replaces /root/reference/environments/Poker/utils.py:108-123 (build_actions) and the four scripted GPU
+ * agents of /root/reference/environments/Poker/Player.py:79-176 with one rule per table.
+ * seat_kinds: HOST array of n_seats bytes, one PULSE_AGENT_* per seat (the caller's rotated agent_types).
+ * Chance: two 32-bit words per table (raise size = lo + mulhi32(w0, hi - lo), LoosePassive's uniform =
+ * (w1 >> 8) * 2^-24), injected as chance2 uint32 [N,2] or taken from the tape at (seed, env_base + i,
+ * stream 2, counter).  Tables whose acting seat is PULSE_AGENT_EXTERNAL keep the caller's action. */
+enum {
+  PULSE_AGENT_EXTERNAL = 0,         /* qlearning / host-side agent: action supplied by the caller */
+  PULSE_AGENT_RANDOM = 1,           /* utils.py:119-120 */
+  PULSE_AGENT_HEURISTIC_HANDS = 2,  /* Player.py:79-103 */
+  PULSE_AGENT_TIGHT_AGGRESSIVE = 3, /* Player.py:105-126 */
+  PULSE_AGENT_LOOSE_PASSIVE = 4,    /* Player.py:128-150 */
+  PULSE_AGENT_SMALL_BALL = 5        /* Player.py:152-176 */
+};
+/* on the reference-shaped observation: obs float32 [N, obs_width], seat_idx int32 [N] (info["seat_idx"]),
+ * actions_inout int64 [N] */
+int pulse_poker_policy(const float* obs, int obs_width, const int32_t* seat_idx, const uint8_t* seat_kinds,
+                       int n_seats, const uint32_t* chance2_or_null, uint64_t seed, uint64_t env_base,
+                       uint32_t counter, int64_t* actions_inout, long long n_games, pulse_stream_t stream);
+/* fused into the packed step: the acting seat's rule is evaluated on the registers the step already holds
+ * (hole cards, pot), so a scripted seat costs no extra HBM traffic and no extra launch.  actions_or_null is
+ * read only for PULSE_AGENT_EXTERNAL seats (may be NULL when every seat is scripted); chosen_out_or_null
+ * int64 [N] receives the action that was played (what build_actions leaves in `actions`). */
+int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
+                                   const int64_t* actions_or_null, const uint8_t* seat_kinds,
+                                   const uint32_t* chance2_or_null, uint32_t counter, int64_t* chosen_out_or_null,
+                                   float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
+                                   uint64_t seed, uint64_t env_base, pulse_stream_t stream);
+
 /* packed -> reference-shaped tensors (decks, sb/bb, equities, prev_invested are not represented) */
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
                        pulse_stream_t stream);

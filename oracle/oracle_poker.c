@@ -7,6 +7,7 @@
 #include <limits.h>
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 
 enum { ACTIVE = 0, FOLDED = 1, ALLIN = 2, SITOUT = 3 }; /* PokerGPU.py:11 */
 
@@ -406,5 +407,79 @@ void oracle_tape_actions(uint64_t seed, uint64_t env_base, uint32_t step, int n_
     uint32_t blk[4];
     oracle_tape(seed, env_base + (uint64_t)g, ORACLE_STREAM_ACTION, step, blk);
     out[g] = (int64_t)oracle_mulhi32(blk[0], (uint32_t)n_actions);
+  }
+}
+
+/* ---- scripted opponents + build_actions -------------------------------------------
+ * Restates /root/reference/environments/Poker/Player.py:79-176 (the four scripted GPU agents) and the
+ * router /root/reference/environments/Poker/utils.py:108-123, one table at a time, in the reference's
+ * own order of mask assignments (default action, fold mask, call mask, raise mask -- later masks
+ * overwrite earlier ones exactly as the tensor assignments do).
+ * kinds: 0 external (action untouched), 1 random, 2 heuristic_hands, 3 tight_aggressive,
+ * 4 loose_passive, 5 small_ball.  chance2 [N,2]: word 0 -> torch.randint(lo, hi) = lo + mulhi32(w0, hi-lo),
+ * word 1 -> torch.rand = (w1 >> 8) * 2^-24. */
+static int py_mod13(int v) { int r = v % 13; return r < 0 ? r + 13 : r; }
+static int tape_randint(uint32_t w, int lo, int hi) { return lo + (int)(((uint64_t)w * (uint64_t)(hi - lo)) >> 32); }
+
+void oracle_poker_policy(const float* obs, int W, const int32_t* seat_idx, const uint8_t* seat_kinds, int n_seats,
+                         const uint32_t* chance2, int64_t* actions, int n) {
+  static const int raise_distribution[9] = {2, 3, 4, 5, 6, 7, 8, 9, 10};  /* torch.arange(2, 11) */
+  for (int g = 0; g < n; ++g) {
+    int seat = seat_idx[g];
+    int kind = (seat >= 0 && seat < n_seats) ? seat_kinds[seat] : 0;
+    if (kind == 0) continue;                                   /* utils.py:117-118: the Q agent's own call */
+    uint32_t w0 = chance2[2 * g], w1 = chance2[2 * g + 1];
+    if (kind == 1) { actions[g] = tape_randint(w0, 0, 13); continue; }   /* utils.py:119-120 */
+    const float* st = obs + (size_t)g * W;
+    int rank1 = py_mod13((int)st[5]), rank2 = py_mod13((int)st[6]);    /* hands = states[:, 5:7]; ranks = hands % 13 */
+    int diff = abs(rank1 - rank2);
+    int64_t act;
+    if (kind == 2) {                                           /* HeuristicHandsPlayerGPU.action :86-101 */
+      act = 0;
+      int fold_mask = rank1 < 8 && rank2 < 8;
+      if (fold_mask) act = 0;
+      int pair_mask = rank1 == rank2;
+      int high_card_mask = rank1 >= 10 || rank2 >= 10;
+      int raise_mask = (pair_mask || high_card_mask) && !fold_mask;
+      if (raise_mask) act = raise_distribution[tape_randint(w0, 0, 9)];
+    } else if (kind == 3) {                                    /* TightAggressivePlayerGPU.action :111-124 */
+      act = 1;
+      int fold_mask = rank1 < 7 && rank2 < 7 && diff > 5;
+      if (fold_mask) act = 0;
+      int pair_mask = rank1 == rank2;
+      int high_card_mask = (rank1 >= 10 && rank2 > 5) || (rank2 >= 10 && rank1 > 5);
+      int raise_mask = (pair_mask || high_card_mask) && !fold_mask;
+      if (raise_mask) act = raise_distribution[tape_randint(w0, 5, 9)];
+    } else if (kind == 4) {                                    /* LoosePassivePlayerGPU.action :134-148 */
+      act = 0;
+      float probs = (float)(w1 >> 8) * (1.0f / 16777216.0f);
+      int fold_mask = rank1 <= 4 && rank2 <= 4 && diff > 9;
+      if (fold_mask) act = 0;
+      int pair_mask = rank1 == rank2 && rank1 > 8;
+      int high_card_mask = (rank1 >= 11 && rank2 > 9) || (rank2 >= 11 && rank1 > 9);
+      int call_mask = (pair_mask || high_card_mask) && !fold_mask;
+      int raise_mask = probs > 0.9f && call_mask;
+      if (call_mask) act = 1;
+      if (raise_mask) act = raise_distribution[tape_randint(w0, 0, 4)];
+    } else {                                                   /* SmallBallPlayerGPU.action :158-174 */
+      act = 0;
+      float pot_size = st[9];
+      int fold_mask = (rank1 < 6 && rank2 < 6 && pot_size > 30.0f) || (rank1 < 9 && rank2 < 9 && pot_size > 80.0f);
+      if (fold_mask) act = 0;
+      int pair_mask = rank1 == rank2;
+      int high_card_mask = (rank1 >= 10 && rank2 > 5) || (rank2 >= 10 && rank1 > 5);
+      int raise_mask = (pair_mask || high_card_mask) && !fold_mask;
+      if (raise_mask) act = raise_distribution[tape_randint(w0, 0, 3)];
+    }
+    actions[g] = act;
+  }
+}
+
+/* the tape's chance pair for the policy (stream 2, counter = step): words x, y of the Philox block */
+void oracle_policy_tape(uint64_t seed, uint64_t env_base, uint32_t counter, uint32_t* chance2, int n) {
+  for (int g = 0; g < n; ++g) {
+    uint32_t b[4];
+    oracle_tape(seed, env_base + (uint64_t)g, 2u, counter, b);
+    chance2[2 * g] = b[0]; chance2[2 * g + 1] = b[1];
   }
 }

@@ -123,6 +123,24 @@ class OraclePoker:
         getattr(self.L, "oracle_poker_" + name)(C.byref(self.s), *args)
 
 
+def poker_policy(obs, seat_idx, kinds, chance2, actions):
+    """oracle_poker_policy: the reference's scripted agents + build_actions, in place on `actions`."""
+    obs = np.ascontiguousarray(obs, dtype=np.float32)
+    seat = np.ascontiguousarray(seat_idx, dtype=np.int32)
+    k = np.ascontiguousarray(kinds, dtype=np.uint8)
+    c = np.ascontiguousarray(chance2, dtype=np.uint32)
+    assert actions.dtype == np.int64 and actions.flags.c_contiguous
+    lib().oracle_poker_policy(p(obs), C.c_int(obs.shape[1]), p(seat), p(k), C.c_int(len(k)), p(c), p(actions),
+                              C.c_int(obs.shape[0]))
+    return actions
+
+
+def policy_tape(seed, env_base, counter, n):
+    out = np.zeros((n, 2), np.uint32)
+    lib().oracle_policy_tape(C.c_uint64(seed), C.c_uint64(env_base), C.c_uint32(counter), p(out), C.c_int(n))
+    return out
+
+
 # ---- Blackjack -----------------------------------------------------------------------------------
 BJ_FIELDS = ("decks", "deck_positions", "terminated", "players_cards", "players_card_idx", "player_card_sums",
              "has_ace", "dealer_cards", "dealer_card_idx", "dealer_upcard", "dealer_card_sums", "dealer_has_ace",

@@ -55,12 +55,12 @@ __device__ __forceinline__ void stage_obs_rows(const float (&row)[WT], float4* s
   __syncthreads();
 }
 
-template <int MAXP, int MT, int MINB>
+template <int MAXP, int MT, int MINB, bool POLICY = false>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
                          float* __restrict__ obs_out, float* __restrict__ reward_out,
                          uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
-                         int starting_bbs, int max_bbs, long long n) {
+                         int starting_bbs, int max_bbs, long long n, PackedPolicy pol = PackedPolicy()) {
   extern __shared__ float4 smem4[];
   if (MT > 0) pr.M = MT;
   constexpr int WT = MT > 0 ? 13 + 3 * (MT - 1) : 13 + 3 * 15;  // row buffer size
@@ -69,8 +69,8 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
     const long long g = base + threadIdx.x;
     float row[WT];
     if (g < n)
-      packed_step_one<MAXP>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base, starting_bbs,
-                            max_bbs, g, n);
+      packed_step_one<MAXP, POLICY>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base,
+                                    starting_bbs, max_bbs, g, n, &pol);
     stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
   }
 }
@@ -202,6 +202,49 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #undef PKP_STEP_B
 #undef PKP_SMEM4
   return pulse_check_launch("pulse_poker_packed_step");
+}
+
+int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
+                                   const int64_t* actions_or_null, const uint8_t* seat_kinds,
+                                   const uint32_t* chance2_or_null, uint32_t counter, int64_t* chosen_out_or_null,
+                                   float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
+                                   uint64_t seed, uint64_t env_base, cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  PULSE_REQUIRE(seat_kinds != nullptr, "seat_kinds is null");
+  PackedPolicy pol;
+  bool any_external = false;
+  for (int s = 0; s < 16; ++s) {
+    pol.kinds.kind[s] = s < cfg->n_players ? seat_kinds[s] : (uint8_t)PULSE_AGENT_EXTERNAL;
+    if (s < cfg->n_players) {
+      PULSE_REQUIRE(pol.kinds.kind[s] <= PULSE_AGENT_SMALL_BALL, "unknown agent kind");
+      any_external |= pol.kinds.kind[s] == PULSE_AGENT_EXTERNAL;
+    }
+  }
+  PULSE_REQUIRE(!any_external || actions_or_null, "actions are required when a seat is PULSE_AGENT_EXTERNAL");
+  if (cfg->n_games == 0) return PULSE_OK;
+  PULSE_REQUIRE(obs_out && reward_out && done_out, "null buffer");
+  PULSE_REQUIRE(!auto_reset || st->hand_ctr, "auto_reset needs hand_ctr");
+  pol.chance2 = chance2_or_null; pol.chosen = chosen_out_or_null; pol.counter = counter;
+  PokerParams pr = make_params(cfg);
+  const int W = 13 + 3 * (pr.M - 1);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+#define PKP_POL(MP, MT, MINB, SMEM)                                                                        \
+  poker_packed_step_kernel<MP, MT, MINB, true><<<grid, kBlock, SMEM, stream>>>(                             \
+      *st, pr, actions_or_null, obs_out, reward_out, done_out, auto_reset, seed, env_base, cfg->starting_bbs, \
+      cfg->max_bbs, (long long)cfg->n_games, pol)
+#define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
+  const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
+  if (pr.P <= 2 && pr.M == 2 && aligned) PKP_POL(2, 2, 10, PKP_SMEM4(2));
+  else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) PKP_POL(6, 6, 8, PKP_SMEM4(6));
+  else if (pr.P > 6 && pr.M == 10 && aligned) PKP_POL(10, 10, 8, PKP_SMEM4(10));
+  else {
+    const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
+    PKP_DISPATCH(pr.P, PKP_POL(MP, 0, 8, smem));
+  }
+#undef PKP_POL
+#undef PKP_SMEM4
+  return pulse_check_launch("pulse_poker_packed_step_policy");
 }
 
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,

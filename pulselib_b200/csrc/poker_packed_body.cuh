@@ -25,6 +25,7 @@
 // takes the evaluator (the most divergent code) out of the per-step kernel.
 #pragma once
 #include "poker_core.cuh"
+#include "poker_policy.cuh"
 
 struct PackedDeck {
   uint32_t fb;   // five board cards, 6 bits each
@@ -266,20 +267,45 @@ PULSE_HD void packed_store_all(const PokerTable<MAXP>& t, uint32_t fb, const Pul
     }
 }
 
+// Scripted seats evaluated inside the step (rules in poker_policy.cuh): the acting seat's
+// kind picks the rule, its hole cards and the pot are already in registers.
+struct PackedPolicy {
+  PulseSeatKinds kinds;
+  const uint32_t* chance2;   // uint32 [N,2] injected draws, or NULL: tape (seed, env, PULSE_STREAM_ACTION, counter)
+  int64_t* chosen;           // int64 [N] action played, or NULL
+  uint32_t counter;
+};
+
 // One step of one table in the packed layout (PokerGPU.py:527-633).  auto_reset: a table that was
 // already done when the step began is dealt a new hand instead (engine extension):
 // the action is ignored, reward 0, done 0 and the observation is the new hand's first one.
-template <int MAXP>
+template <int MAXP, bool POLICY = false>
 PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, const int64_t* __restrict__ actions,
                               float* __restrict__ obs_row, float* __restrict__ reward_out,
                               uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
-                              int starting_bbs, int max_bbs, long long g, long long n) {
+                              int starting_bbs, int max_bbs, long long g, long long n,
+                              const PackedPolicy* pol = nullptr) {
   const int P = pr.P, AP = pr.AP;
   PokerTable<MAXP> t;
   uint32_t fb;
   PackedEv<MAXP, (MAXP <= 2)> evw{S.ev, g, n};
   evw.prefetch(AP);
   packed_load(t, fb, S, g, n, AP);
+  long long a;
+  if (POLICY) {  // build_actions: computed from the pre-step state for every table, done or not (utils.py:108-123)
+    const int kind = pol->kinds.kind[t.idx & 15];
+    if (kind == PULSE_AGENT_EXTERNAL) {
+      a = actions[g];
+    } else {
+      uint32_t w0, w1;
+      if (pol->chance2) { w0 = pol->chance2[2 * g]; w1 = pol->chance2[2 * g + 1]; }
+      else { PulseU4 b = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_ACTION, pol->counter); w0 = b.x; w1 = b.y; }
+      a = pulse_policy_action(kind, pk_sel(t.hole0, t.idx), pk_sel(t.hole1, t.idx), (float)t.pot, w0, w1);
+    }
+    if (pol->chosen) pol->chosen[g] = a;
+  } else {
+    a = actions[g];
+  }
   if (auto_reset && t.done) {
     uint32_t hand = S.hand_ctr[g] + 1u;
     S.hand_ctr[g] = hand;
@@ -294,7 +320,6 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   }
   const PokerTable<MAXP> t0 = t;
   const PackedDeck deck{fb, 2 * AP};
-  const long long a = actions[g];
   const bool prev_done = t.done;
   const int actor = t.idx;                                           // :531
   const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537

@@ -126,6 +126,44 @@ class PokerGPUPacked(gym.Env):
         self._done = done
         return self.obs, rewards, done, self.is_truncated, self.get_info()
 
+    def step_policy(self, seat_kinds, actions=None, chance2=None, counter=None, return_actions=True):
+        """step() with the scripted seats' rules evaluated inside the step kernel: one
+        launch does build_actions + step.  seat_kinds: one PULSE_AGENT_* per seat (pulselib_b200.policy);
+        `actions` int64 [N] is read only for EXTERNAL seats.  Returns step()'s tuple with the played
+        actions added to info["actions"]."""
+        kb = bytes(seat_kinds)
+        if len(kb) != self.n_players:
+            raise ValueError(f"seat_kinds must have {self.n_players} entries")
+        N, dev = self.n_games, self.device
+        if actions is not None:
+            actions = torch.as_tensor(actions, device=dev)
+            if actions.dtype != torch.int64 or not actions.is_contiguous():
+                actions = actions.to(torch.int64).contiguous()
+            if tuple(actions.shape) != (N,):
+                raise ValueError(f"actions must have shape {(N,)}, got {tuple(actions.shape)}")
+        elif any(k == 0 for k in kb):
+            raise ValueError("actions are required when a seat is EXTERNAL")
+        if chance2 is not None:
+            chance2 = torch.as_tensor(chance2, device=dev)
+            if tuple(chance2.shape) != (N, 2):
+                raise ValueError(f"chance2 must have shape {(N, 2)}")
+            chance2 = chance2.to(torch.int64).to(torch.int32).contiguous()
+        if counter is None:
+            counter = self._policy_counter = getattr(self, "_policy_counter", -1) + 1
+        rewards = torch.empty(N, dtype=torch.float32, device=dev)
+        done = torch.empty(N, dtype=torch.bool, device=dev)
+        chosen = torch.empty(N, dtype=torch.int64, device=dev) if return_actions else None
+        cfg = self._config()
+        with _lib.device_guard(dev):
+            _lib.check(self._lib.pulse_poker_packed_step_policy(
+                C.byref(self._packed), C.byref(cfg), ptr(actions), C.c_char_p(kb), ptr(chance2), c_u32(counter),
+                ptr(chosen), ptr(self.obs), ptr(rewards), ptr(done), c_i(1 if self.auto_reset else 0),
+                c_u64(self.seed_value), c_u64(self.env_base), _lib.cuda_stream(dev)), "pulse_poker_packed_step_policy")
+        self._done = done
+        info = self.get_info()
+        info["actions"] = chosen
+        return self.obs, rewards, done, self.is_truncated, info
+
     def get_info(self):
         # seat_idx / stacks are what build_actions and the trainers read (environments/Poker/utils.py:108-123)
         return {"active_players": self.active_players, "stacks": _Lazy(self, "stacks"), "seat_idx": _Lazy(self, "idx")}

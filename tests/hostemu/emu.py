@@ -149,6 +149,32 @@ class EmuPokerPacked(EmuPoker):
         return self.obs, self.rewards, self.is_done.astype(bool)
 
 
+    def step_policy(self, kinds, chance2=None, counter=0, actions=None):
+        """packed step with the scripted seats evaluated inside; returns the played actions too"""
+        k = np.ascontiguousarray(kinds, dtype=np.uint8)
+        a = None if actions is None else np.ascontiguousarray(actions, dtype=np.int64)
+        c = None if chance2 is None else np.ascontiguousarray(chance2, dtype=np.uint32)
+        chosen = np.zeros(self.n_games, np.int64)
+        s = self._packed()
+        lib().emu_poker_packed_step_policy(C.byref(s), C.byref(self.cfg), p(a), p(k), p(c), C.c_uint32(counter),
+                                           p(chosen), p(self.obs), p(self.rewards), p(self.is_done),
+                                           C.c_int(self.auto_reset), C.c_uint64(self.seed), C.c_uint64(self.env_base))
+        self._unpack()
+        return self.obs, self.rewards, self.is_done.astype(bool), chosen
+
+
+def emu_policy(obs, seat_idx, kinds, actions, chance2=None, seed=0, env_base=0, counter=0):
+    """pulse_policy_action over observation rows (the body of pulse_poker_policy), in place on `actions`."""
+    obs = np.ascontiguousarray(obs, dtype=np.float32)
+    seat = np.ascontiguousarray(seat_idx, dtype=np.int32)
+    k = np.ascontiguousarray(kinds, dtype=np.uint8)
+    c = None if chance2 is None else np.ascontiguousarray(chance2, dtype=np.uint32)
+    assert actions.dtype == np.int64 and actions.flags.c_contiguous
+    lib().emu_poker_policy(p(obs), C.c_int(obs.shape[1]), p(seat), p(k), C.c_int(len(k)), p(c), C.c_uint64(seed),
+                           C.c_uint64(env_base), C.c_uint32(counter), p(actions), C.c_longlong(obs.shape[0]))
+    return actions
+
+
 # ---- Blackjack / TFE / Tetris bodies -----------------------------------------------------------------
 BJ_COMPAT = (("decks", np.int64, 52), ("deck_positions", np.int32, 0), ("players_cards", np.int32, 20),
              ("players_card_idx", np.int32, 0), ("player_card_sums", np.int32, 0), ("has_ace", np.uint8, 0),

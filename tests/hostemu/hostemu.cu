@@ -63,6 +63,37 @@ int emu_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* cf
                                             env_base, cfg->starting_bbs, cfg->max_bbs, g, (long long)cfg->n_games)));
   return 0;
 }
+// scripted opponents: the per-table rule on observation rows, and fused into the packed step
+int emu_poker_policy(const float* obs, int W, const int32_t* seat_idx, const uint8_t* kinds, int n_seats,
+                     const uint32_t* chance2, uint64_t seed, uint64_t env_base, uint32_t counter, int64_t* actions,
+                     long long n) {
+  for (long long g = 0; g < n; ++g) {
+    const int seat = seat_idx[g];
+    const int kind = (seat >= 0 && seat < n_seats) ? kinds[seat] : PULSE_AGENT_EXTERNAL;
+    if (kind == PULSE_AGENT_EXTERNAL) continue;
+    uint32_t w0, w1;
+    if (chance2) { w0 = chance2[2 * g]; w1 = chance2[2 * g + 1]; }
+    else { PulseU4 b = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_ACTION, counter); w0 = b.x; w1 = b.y; }
+    const float* row = obs + g * W;
+    actions[g] = pulse_policy_action(kind, (int)row[5], (int)row[6], row[9], w0, w1);
+  }
+  return 0;
+}
+int emu_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const int64_t* actions,
+                                 const uint8_t* kinds, const uint32_t* chance2, uint32_t counter, int64_t* chosen,
+                                 float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset, uint64_t seed,
+                                 uint64_t env_base) {
+  PokerParams pr = mk(cfg);
+  const int W = 13 + 3 * (pr.M - 1);
+  PackedPolicy pol;
+  for (int s = 0; s < 16; ++s) pol.kinds.kind[s] = s < cfg->n_players ? kinds[s] : (uint8_t)PULSE_AGENT_EXTERNAL;
+  pol.chance2 = chance2; pol.chosen = chosen; pol.counter = counter;
+  for (long long g = 0; g < cfg->n_games; ++g)
+    EMU_DISPATCH(pr.P, (packed_step_one<MP, true>(*st, pr, actions, obs_out + g * W, reward_out, done_out, auto_reset,
+                                                  seed, env_base, cfg->starting_bbs, cfg->max_bbs, g,
+                                                  (long long)cfg->n_games, &pol)));
+  return 0;
+}
 int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg) {
   PokerParams pr = mk(cfg);
   for (long long g = 0; g < cfg->n_games; ++g)
