@@ -100,6 +100,29 @@ poker_packed_reset_kernel(PulsePokerPacked S, PokerParams pr, const int32_t* __r
   }
 }
 
+// Redeal pass of auto_reset: one thread per table, most of them return after reading 4 B (hand_ctr); a marked
+// table is dealt its next hand exactly as the whole-batch reset would (same shuffle scratch in shared
+// memory) and its observation row is rewritten.
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock, MAXP <= 2 ? 8 : MAXP <= 6 ? 5 : 3)
+poker_packed_redeal_kernel(PulsePokerPacked S, PokerParams pr, uint64_t seed, uint64_t env_base, int starting_bbs,
+                           int max_bbs, float* __restrict__ obs_out, long long n) {
+  extern __shared__ float4 smem4[];
+  const int W = 13 + 3 * (pr.M - 1);
+  PackedDeckShared dk{reinterpret_cast<uint8_t*>(smem4) + 4 * threadIdx.x, 4 * kBlock};
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
+    float row[13 + 3 * 15];
+    if (!packed_redeal_one<MAXP>(S, pr, seed, env_base, starting_bbs, max_bbs, row, g, n, dk)) continue;
+    float* dst = obs_out + g * W;
+    if ((W & 3) == 0 && (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0) {
+      for (int c = 0; c < W; c += 4)
+        *reinterpret_cast<float4*>(dst + c) = make_float4(row[c], row[c + 1], row[c + 2], row[c + 3]);
+    } else {
+      for (int c = 0; c < W; ++c) dst[c] = row[c];
+    }
+  }
+}
+
 template <int MAXP>
 __global__ void __launch_bounds__(kBlock)
 poker_packed_unpack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr, long long n) {
@@ -124,6 +147,9 @@ PokerParams make_params(const PulsePokerConfig* c) {
 
 }  // namespace
 
+static int launch_redeal(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const PokerParams& pr, uint64_t seed,
+                         uint64_t env_base, float* obs_out, cudaStream_t stream);
+
 #define PKP_DISPATCH(P, CALL)                            \
   do {                                                   \
     if ((P) <= 2) { constexpr int MP = 2; CALL; }        \
@@ -131,6 +157,14 @@ PokerParams make_params(const PulsePokerConfig* c) {
     else if ((P) <= 6) { constexpr int MP = 6; CALL; }   \
     else { constexpr int MP = 10; CALL; }                \
   } while (0)
+
+static int launch_redeal(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const PokerParams& pr, uint64_t seed,
+                         uint64_t env_base, float* obs_out, cudaStream_t stream) {
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_redeal_kernel<MP><<<grid, kBlock, kDeckSmemBytes, stream>>>(
+                         *st, pr, seed, env_base, cfg->starting_bbs, cfg->max_bbs, obs_out, (long long)cfg->n_games)));
+  return pulse_check_launch("pulse_poker_packed_step (redeal pass)");
+}
 
 extern "C" {
 
@@ -174,7 +208,8 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
 #define PKP_STEP_B(MP, MT, MINB, SMEM)                                                                            \
   poker_packed_step_kernel<MP, MT, MINB><<<grid, kBlock, SMEM, stream>>>(*st, pr, actions, obs_out, reward_out, \
-                                                                         done_out, auto_reset, seed, env_base,    \
+                                                                         done_out, auto_reset ? 2 : 0, seed,      \
+                                                                         env_base,                                \
                                                                          cfg->starting_bbs, cfg->max_bbs,         \
                                                                          (long long)cfg->n_games)
   // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 8 (64) otherwise --
@@ -201,7 +236,9 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #undef PKP_STEP
 #undef PKP_STEP_B
 #undef PKP_SMEM4
-  return pulse_check_launch("pulse_poker_packed_step");
+  rc = pulse_check_launch("pulse_poker_packed_step");
+  if (rc || !auto_reset) return rc;
+  return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
 }
 
 int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
@@ -231,7 +268,8 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
 #define PKP_POL(MP, MT, MINB, SMEM)                                                                        \
   poker_packed_step_kernel<MP, MT, MINB, true><<<grid, kBlock, SMEM, stream>>>(                             \
-      *st, pr, actions_or_null, obs_out, reward_out, done_out, auto_reset, seed, env_base, cfg->starting_bbs, \
+      *st, pr, actions_or_null, obs_out, reward_out, done_out, auto_reset ? 2 : 0, seed, env_base,            \
+      cfg->starting_bbs,                                                                                       \
       cfg->max_bbs, (long long)cfg->n_games, pol)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
@@ -244,7 +282,9 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   }
 #undef PKP_POL
 #undef PKP_SMEM4
-  return pulse_check_launch("pulse_poker_packed_step_policy");
+  rc = pulse_check_launch("pulse_poker_packed_step_policy");
+  if (rc || !auto_reset) return rc;
+  return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
 }
 
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,

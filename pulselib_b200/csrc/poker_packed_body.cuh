@@ -27,6 +27,8 @@
 #include "poker_core.cuh"
 #include "poker_policy.cuh"
 
+#define PKP_REDEAL_MARK 0x80000000u  // top bit of hand_ctr: table waits for the redeal pass
+
 struct PackedDeck {
   uint32_t fb;   // five board cards, 6 bits each
   int base;      // 2 * active_players: first deck position after the hole cards
@@ -306,6 +308,17 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   } else {
     a = actions[g];
   }
+  if (auto_reset == 2 && t.done) {
+    // device path: the deal is left to the redeal pass that follows the step kernel on the same stream
+    // (poker_packed.cu).  Dealing here would put the shuffle and 3 x AP hand evaluations into the step
+    // kernel's register budget and make every warp with one finished table wait for it (measured: 1.7 ms per
+    // 4M-table step when half the tables redeal, against 0.16 + 0.2 ms for step + redeal pass).
+    S.hand_ctr[g] |= PKP_REDEAL_MARK;
+    reward_out[g] = 0.0f;
+    done_out[g] = 0;
+    pk_obs(t, pr, obs_row);   // placeholder row of the finished hand; the redeal pass overwrites it
+    return;
+  }
   if (auto_reset && t.done) {
     uint32_t hand = S.hand_ctr[g] + 1u;
     S.hand_ctr[g] = hand;
@@ -358,6 +371,18 @@ PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr,
   packed_store_all(t, fb, S, g, n, pr.P);
   if (S.hand_ctr) S.hand_ctr[g] = hand;
   if (obs_row) pk_obs(t, pr, obs_row);
+}
+
+// The redeal pass of auto_reset: deals the next hand to a table the step kernel marked.  Returns whether it did.
+template <int MAXP, class DeckBuf>
+PULSE_HD bool packed_redeal_one(const PulsePokerPacked& S, const PokerParams& pr, uint64_t seed, uint64_t env_base,
+                                int starting_bbs, int max_bbs, float* __restrict__ obs_row, long long g, long long n,
+                                DeckBuf& dk) {
+  const uint32_t ctr = S.hand_ctr[g];
+  if (!(ctr & PKP_REDEAL_MARK)) return false;
+  packed_reset_one<MAXP>(S, pr, nullptr, seed, env_base, (ctr & ~PKP_REDEAL_MARK) + 1u, 0, 0, starting_bbs, max_bbs,
+                         obs_row, g, n, dk);   // stores hand_ctr = new counter: the mark is cleared
+  return true;
 }
 
 template <int MAXP>

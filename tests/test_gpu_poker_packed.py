@@ -125,3 +125,34 @@ def test_auto_reset_deals_next_hand(cuda_device, hr_table):
     orc = pyoracle.OraclePoker(hr_table, **kw)
     orc.tape_decks(11, 5, 1)                     # hand counter 1 of each table's tape
     np.testing.assert_array_equal(snap["hands"].cpu().numpy()[:, :, :], orc.decks[:, :4].reshape(N, 2, 2))
+
+
+@pytest.mark.parametrize("P,N", [(2, 30_011), (6, 8_009)])
+def test_auto_reset_rollout_matches_inline_semantics(P, N, cuda_device, hr_table):
+    """auto_reset on the device is two launches (the step marks finished tables, the redeal pass deals them);
+    the kernel body compiled for the host deals inline.  Both must give the same trajectories: state, obs,
+    reward, done, step after step, with tables finishing and redealing at different times."""
+    import torch
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+    from tests.hostemu.emu import EmuPokerPacked
+
+    kw = dict(n_players=P, max_players=P, n_games=N, starting_bbs=40, max_bbs=150, w1=.5, w2=.3, K=100, alpha=50)
+    env = PokerGPUPacked(cuda_device, seed=3, env_base=17, auto_reset=True, **kw)
+    emu = EmuPokerPacked(hr_table, auto_reset=True, seed=3, env_base=17, **kw)
+    rng = np.random.default_rng(P)
+    np.testing.assert_array_equal(env.reset()[0].cpu().numpy(), emu.reset(None, hand=0))
+    redeals = 0
+    for t in range(60):
+        a = rng.integers(0, 13, N).astype(np.int64)
+        was_done = emu.is_done.astype(bool).copy()
+        o1, r1, d1, _, _ = env.step(torch.from_numpy(a).to(cuda_device))
+        o2, r2, d2 = emu.step(a)
+        redeals += int(was_done.sum())
+        np.testing.assert_array_equal(o1.cpu().numpy(), o2, err_msg=f"step {t} obs")
+        np.testing.assert_array_equal(d1.cpu().numpy(), d2, err_msg=f"step {t} done")
+        np.testing.assert_allclose(r1.cpu().numpy(), r2, rtol=pu.REWARD_RTOL, atol=pu.reward_atol(50))
+        if t % 10 == 9:
+            snap = env.unpack()
+            for f in FIELDS:
+                assert np.array_equal(snap[f].cpu().numpy(), getattr(emu, f)), f"step {t} field {f}"
+    assert redeals > N  # every table was redealt more than once on average
