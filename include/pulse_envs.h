@@ -265,19 +265,19 @@ int pulse_stats_accumulate(const void* reward, int reward_is_float, const uint8_
 /* ---- hand-level statistics ----------------------------------------------------
  * One pass per step over the hands that finished on this step (done && !terminated), replacing the
  * host-side mask gathers of /root/reference/scripts/Poker/trainGPU_performance.py:186-206 and the reductions
- * of /root/reference/utils/performance.py:55-59, :104-174.  stats46 double [46] on the device, accumulated:
+ * of /root/reference/utils/performance.py:55-59, :104-253.  stats67 double [67] on the device, accumulated:
  *   [0] hands  [1] sum d  [2] sum d^2  [3] #(d > 0)        d = stacks[q_seat] - initial_q_stacks
- *   [4..8] hands per terminal-stage bucket (stage >= 4 -> 4)  [9..13] sum d per bucket
- *   [14..29] hands per position (q_seat - button) mod active_players  [30..45] sum d per position
+ *   per terminal-stage bucket b (stage >= 4 -> 4): [4+b] hands  [9+b] sum d  [14+b] wins
+ *   per position p = (q_seat - button) mod active_players: [19+p] hands  [35+p] sum d  [51+p] wins
  * terminated_inout uint8 [N] |= done (the caller's `terminated`).  The vector is what gets all-reduced. */
-#define PULSE_HAND_STATS_LEN 46
+#define PULSE_HAND_STATS_LEN 67
 int pulse_poker_hand_stats(const int32_t* stacks /*[N,P]*/, int n_players, const int32_t* stages /*[N]*/,
                            const int32_t* button /*[N]*/, const uint8_t* done, uint8_t* terminated_inout,
-                           const int32_t* initial_q_stacks /*[N]*/, int q_seat, int active_players, double* stats46,
+                           const int32_t* initial_q_stacks /*[N]*/, int q_seat, int active_players, double* stats67,
                            long long n_games, pulse_stream_t stream);
 int pulse_poker_packed_hand_stats(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const uint8_t* done,
                                   uint8_t* terminated_inout, const int32_t* initial_q_stacks, int q_seat,
-                                  double* stats46, pulse_stream_t stream);
+                                  double* stats67, pulse_stream_t stream);
 
 #ifdef __cplusplus
 }

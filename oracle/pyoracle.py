@@ -141,6 +141,27 @@ def policy_tape(seed, env_base, counter, n):
     return out
 
 
+def hand_stats_update(vec, q_stacks, initial, stages, button, done, terminated, q_seat, active_players):
+    """Numpy restatement of one step of the reference's hand bookkeeping
+    (/root/reference/scripts/Poker/trainGPU_performance.py:186-206 + utils/performance.py:55-59, :170-174) folded into
+    the 67-double layout of include/pulse_envs.h.  `terminated` (bool array) is updated in place."""
+    done = np.asarray(done).astype(bool)
+    newly = done & ~terminated                                   # dones & ~terminated_before
+    terminated |= done
+    d = (np.asarray(q_stacks)[newly].astype(np.float64) - np.asarray(initial)[newly].astype(np.float64))
+    bucket = np.where(np.asarray(stages)[newly] >= 4, 4, np.clip(np.asarray(stages)[newly], 0, 3))
+    pos = np.remainder(q_seat - np.asarray(button)[newly].astype(np.int64), active_players)
+    win = d > 0
+    vec[0] += d.size; vec[1] += d.sum(); vec[2] += (d * d).sum(); vec[3] += win.sum()
+    for b in range(5):
+        m = bucket == b
+        vec[4 + b] += m.sum(); vec[9 + b] += d[m].sum(); vec[14 + b] += (win & m).sum()
+    for p_ in range(16):
+        m = pos == p_
+        vec[19 + p_] += m.sum(); vec[35 + p_] += d[m].sum(); vec[51 + p_] += (win & m).sum()
+    return vec
+
+
 # ---- Blackjack -----------------------------------------------------------------------------------
 BJ_FIELDS = ("decks", "deck_positions", "terminated", "players_cards", "players_card_idx", "player_card_sums",
              "has_ace", "dealer_cards", "dealer_card_idx", "dealer_upcard", "dealer_card_sums", "dealer_has_ace",

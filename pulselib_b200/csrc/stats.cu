@@ -57,15 +57,16 @@ extern "C" int pulse_stats_accumulate(const void* reward, int reward_is_float, c
 // What the reference's performance loop gathers on the host every step with boolean-mask indexing
 // (/root/reference/scripts/Poker/trainGPU_performance.py:188-206: newly_done = dones & ~terminated_before,
 // final - initial stack of the Q seat, terminal stage, button-relative position) and reduces afterwards
-// (/root/reference/utils/performance.py:104-167: mean delta, win rate, hands, BB/100, LCB95; :170-174 stage
-// buckets; :55-59 positions).  Here one pass per step folds the newly finished hands into a 46-double
-// vector on the device -- the vector that is summed over ranks by NCCL:
+// (/root/reference/utils/performance.py:104-167: mean delta, win rate, hands, BB/100, LCB95; :170-196 stage
+// buckets and street win percentages; :55-59, :199-253 positions, position win rates, seat-balanced BB/100).
+// Here one pass per step folds the newly finished hands into a 67-double vector on the device -- the vector
+// that is summed over ranks by NCCL:
 //   [0] hands  [1] sum d  [2] sum d^2  [3] #(d > 0)
-//   [4..8] hands per terminal-stage bucket (0 preflop .. 3 river, 4 = stage >= 4)   [9..13] sum d per bucket
-//   [14..29] hands per position (q_seat - button) mod active_players                [30..45] sum d per position
+//   per terminal-stage bucket b (0 preflop .. 3 river, 4 = stage >= 4): [4+b] hands  [9+b] sum d  [14+b] wins
+//   per position p = (q_seat - button) mod active_players:              [19+p] hands [35+p] sum d [51+p] wins
 // Deltas are integers (chips), so every sum is exact in double and independent of the order of the atomics.
 namespace {
-constexpr int kHandStats = 46;
+constexpr int kHandStats = 67;
 
 struct CompatHandView {   // reference-shaped tensors
   const int32_t* stacks; int P; const int32_t* stages; const int32_t* button;
@@ -97,9 +98,9 @@ hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict_
       int pos = (q_seat - v.btn(g)) % active_players;                        // calculate_q_seat_positions
       if (pos < 0) pos += active_players;
       atomicAdd(&sh[0], 1.0); atomicAdd(&sh[1], delta); atomicAdd(&sh[2], delta * delta);
-      if (delta > 0.0) atomicAdd(&sh[3], 1.0);
       atomicAdd(&sh[4 + bucket], 1.0); atomicAdd(&sh[9 + bucket], delta);
-      atomicAdd(&sh[14 + (pos & 15)], 1.0); atomicAdd(&sh[30 + (pos & 15)], delta);
+      atomicAdd(&sh[19 + (pos & 15)], 1.0); atomicAdd(&sh[35 + (pos & 15)], delta);
+      if (delta > 0.0) { atomicAdd(&sh[3], 1.0); atomicAdd(&sh[14 + bucket], 1.0); atomicAdd(&sh[51 + (pos & 15)], 1.0); }
     }
     if (d && !before) terminated[g] = 1;                    // terminated |= dones (:187)
   }
@@ -121,26 +122,26 @@ int launch_hand_stats(View v, const uint8_t* done, uint8_t* terminated, const in
 extern "C" int pulse_poker_hand_stats(const int32_t* stacks, int n_players, const int32_t* stages,
                                       const int32_t* button, const uint8_t* done, uint8_t* terminated_inout,
                                       const int32_t* initial_q_stacks, int q_seat, int active_players,
-                                      double* stats46, long long n_games, cudaStream_t stream) {
+                                      double* stats67, long long n_games, cudaStream_t stream) {
   PULSE_REQUIRE(n_games >= 0, "n_games < 0");
   PULSE_REQUIRE(n_players >= 2 && n_players <= 16 && active_players >= 1 && active_players <= n_players, "bad table size");
   PULSE_REQUIRE(q_seat >= 0 && q_seat < n_players, "q_seat out of range");
   if (n_games == 0) return PULSE_OK;
-  PULSE_REQUIRE(stacks && stages && button && done && terminated_inout && initial_q_stacks && stats46, "null buffer");
+  PULSE_REQUIRE(stacks && stages && button && done && terminated_inout && initial_q_stacks && stats67, "null buffer");
   return launch_hand_stats(CompatHandView{stacks, n_players, stages, button}, done, terminated_inout, initial_q_stacks,
-                           q_seat, active_players, stats46, n_games, stream, "pulse_poker_hand_stats");
+                           q_seat, active_players, stats67, n_games, stream, "pulse_poker_hand_stats");
 }
 
 extern "C" int pulse_poker_packed_hand_stats(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
                                              const uint8_t* done, uint8_t* terminated_inout,
-                                             const int32_t* initial_q_stacks, int q_seat, double* stats46,
+                                             const int32_t* initial_q_stacks, int q_seat, double* stats67,
                                              cudaStream_t stream) {
   PULSE_REQUIRE(st && cfg, "null state/config");
   PULSE_REQUIRE(q_seat >= 0 && q_seat < cfg->n_players, "q_seat out of range");
   PULSE_REQUIRE(cfg->active_players >= 1 && cfg->active_players <= cfg->n_players, "bad active_players");
   if (cfg->n_games == 0) return PULSE_OK;
-  PULSE_REQUIRE(done && terminated_inout && initial_q_stacks && stats46, "null buffer");
+  PULSE_REQUIRE(done && terminated_inout && initial_q_stacks && stats67, "null buffer");
   return launch_hand_stats(PackedHandView{st->stack, (long long)cfg->n_games, st->tbl}, done, terminated_inout,
-                           initial_q_stacks, q_seat, cfg->active_players, stats46, cfg->n_games, stream,
+                           initial_q_stacks, q_seat, cfg->active_players, stats67, cfg->n_games, stream,
                            "pulse_poker_packed_hand_stats");
 }
