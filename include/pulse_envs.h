@@ -279,6 +279,25 @@ int pulse_poker_packed_hand_stats(const PulsePokerPacked* st, const PulsePokerCo
                                   uint8_t* terminated_inout, const int32_t* initial_q_stacks, int q_seat,
                                   double* stats67, pulse_stream_t stream);
 
+/* ---- transition hand-off to the learner ------------------------------------------
+ * Appends this step's transitions of the learning seat -- tables with seat_idx_before == q_seat that were not
+ * terminated before the step -- to a device ring buffer, in table order: the masked gathers of
+ * /root/reference/scripts/Poker/trainGPU.py:79-94 plus ReplayBufferTorch.add
+ * (/root/reference/utils/ReplayBuffer.py:47-60: slots arange(position, position + batch) % capacity).
+ * state / next_state float32 [N, obs_width] (the observation before and after the step), actions int64 [N],
+ * rewards float32 [N], dones uint8 [N], seat_idx_before int32 [N], terminated_before uint8 [N] or NULL.
+ * Ring: state_buf / next_state_buf float32 [capacity, obs_width], action_buf int64, reward_buf float32,
+ * done_buf uint8 [capacity].  total_inout uint64 [1] on the device = transitions appended so far
+ * (position = total % capacity, size = min(total, capacity)); appended_out uint64 [1] = rows added by this call.
+ * scratch: pulse_replay_scratch_bytes(n_games) bytes of device memory.  Requires n_games <= capacity. */
+size_t pulse_replay_scratch_bytes(long long n_games);
+int pulse_replay_append(const float* state, const float* next_state, int obs_width, const int64_t* actions,
+                        const float* rewards, const uint8_t* dones, const int32_t* seat_idx_before,
+                        const uint8_t* terminated_before_or_null, int q_seat, float* state_buf, float* next_state_buf,
+                        int64_t* action_buf, float* reward_buf, uint8_t* done_buf, long long capacity,
+                        uint64_t* total_inout, uint64_t* appended_out, void* scratch, long long n_games,
+                        pulse_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -162,6 +162,35 @@ def hand_stats_update(vec, q_stacks, initial, stages, button, done, terminated, 
     return vec
 
 
+class OracleRing:
+    """Numpy restatement of the reference's transition hand-off: the masked gathers of
+    /root/reference/scripts/Poker/trainGPU.py:79-94 followed by ReplayBufferTorch.add
+    (/root/reference/utils/ReplayBuffer.py:47-60), with float32 state/reward buffers."""
+
+    def __init__(self, capacity, obs_width):
+        self.capacity = capacity
+        self.state_buffer = np.zeros((capacity, obs_width), np.float32)
+        self.next_state_buffer = np.zeros((capacity, obs_width), np.float32)
+        self.action_buffer = np.zeros(capacity, np.int64)
+        self.reward_buffer = np.zeros(capacity, np.float32)
+        self.terminated_buffer = np.zeros(capacity, bool)
+        self.position = self.size = self.total = 0
+
+    def append(self, state, actions, rewards, next_state, dones, seat, term_before, q_seat):
+        active = (np.asarray(seat) == q_seat)
+        if term_before is not None:
+            active &= ~np.asarray(term_before).astype(bool)
+        k = int(active.sum())
+        idx = np.arange(self.position, self.position + k) % self.capacity
+        self.state_buffer[idx] = state[active]; self.next_state_buffer[idx] = next_state[active]
+        self.action_buffer[idx] = actions[active]; self.reward_buffer[idx] = rewards[active]
+        self.terminated_buffer[idx] = np.asarray(dones)[active].astype(bool)
+        self.position = (self.position + k) % self.capacity
+        self.size = min(self.size + k, self.capacity)
+        self.total += k
+        return k
+
+
 # ---- Blackjack -----------------------------------------------------------------------------------
 BJ_FIELDS = ("decks", "deck_positions", "terminated", "players_cards", "players_card_idx", "player_card_sums",
              "has_ace", "dealer_cards", "dealer_card_idx", "dealer_upcard", "dealer_card_sums", "dealer_has_ace",
