@@ -403,7 +403,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=32)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="poker_hu",
-                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tetris", "particle2d", "blackjack", "poker_hu_scripted"])
+                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tetris", "particle2d", "blackjack", "poker_hu_scripted", "poker_hu_train_loop"])
     ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` block of the poker line")
     ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")
     ap.add_argument("--e2e-chunks", type=int, default=4)

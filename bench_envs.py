@@ -31,6 +31,16 @@ SPECS = {
                               desc="PokerGPU heads-up, {n} tables/GPU, seats played by the scripted TightAggressive and "
                                    "SmallBall rules inside the step kernel (no action tensor), draws from the chance "
                                    "tape, per-table auto-reset"),
+    # SURVEY 8(f) N1+N2+N3 together: what one iteration of the reference's training loop does around the step
+    # (scripts/Poker/trainGPU_performance.py:176-206) with everything on the device: scripted opponent inside the
+    # step, learning seat's actions supplied, hand statistics folded, learning-seat transitions appended to the
+    # ring; state/next_state ping-pong instead of state.clone().  Bytes: step 201 + stats 2 + ring select 5 +
+    # ~half the tables' transitions (2 rows read + written, 141 B each way).
+    "poker_hu_train_loop": dict(n=1 << 22, algo_bytes=201 + 2 + 5 + 141, kernel="step<2,2,10,true> + redeal + hand_stats + replay x3",
+                                graph=0, actions=16,
+                                desc="PokerGPU heads-up, {n} tables/GPU, seat 0 = learner (uniform random actions supplied), "
+                                     "seat 1 = TightAggressive rule inside the step kernel, per-table auto-reset, hand "
+                                     "statistics and the learner's transitions (ring of 8M) gathered on the device every step"),
     "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_step_kernel", graph=0, actions=8,
                       desc="Blackjack, {n} envs/GPU (the reference's CPU-sized config), uniform hit/stand, whole-batch "
                            "reset every 8 steps inside the timed region; working set is L2-resident by construction"),
@@ -84,6 +94,28 @@ def _make(name, dev, n, rank, e2e=False):
         def step(e, a):
             o, r, d, _, info = e.step_policy(kinds)
             return o, r, d, info["actions"]
+    elif name == "poker_hu_train_loop":
+        from pulselib_b200 import policy
+        from pulselib_b200.envs.poker_packed import PokerGPUPacked
+        from pulselib_b200.hand_stats import HandStats
+        from pulselib_b200.replay import TransitionRing
+
+        env = PokerGPUPacked(dev, n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3,
+                             K=100, alpha=50, seed=SEED, env_base=rank * n, auto_reset=True)
+        acts = torch.randint(0, 13, (L, n), dtype=torch.int64, device=dev, generator=gen)
+        kinds = bytes([policy.EXTERNAL, policy.TIGHT_AGGRESSIVE])
+        env._hs = HandStats(env, q_seat=0)
+        env._ring = TransitionRing(dev, 2 * n, env.obs_size)
+        env._pp = [torch.zeros_like(env.obs), torch.zeros_like(env.obs)]
+        env._k = 0
+
+        def step(e, a):
+            cur, nxt = e._pp[e._k & 1], e._pp[(e._k + 1) & 1]
+            o, r, d, _, info = e.step_policy(kinds, actions=a, obs_out=nxt, return_seat=True)
+            e._hs.update(d)                      # auto-reset: every done flag is one finished hand (rearm mode)
+            e._ring.append(cur, info["actions"], r, nxt, d, info["seat_idx_before"], None, 0)
+            e._k += 1
+            return o, r, d
     elif name == "blackjack":
         from pulselib_b200.envs.blackjack import BlackJack
 
@@ -99,7 +131,10 @@ def _make(name, dev, n, rank, e2e=False):
             return o, r, t
     else:
         raise KeyError(name)
-    env.reset()
+    first_obs = env.reset()
+    if name == "poker_hu_train_loop":
+        env._pp[0].copy_(first_obs[0])
+        env._hs.begin_hand()
     return env, acts, step
 
 
@@ -293,6 +328,35 @@ def cpu_baseline(name, min_seconds=10.0):
             spent += time.perf_counter() - t0
             steps += 16 * n; k += 16; hands += 1
         sample = f"{n} tables x {hands} hands x 16 steps (oracle policy + reset + step, obs built), oracle/oracle_poker.c"
+    elif name == "poker_hu_train_loop":
+        from pulselib_b200 import handranks
+
+        n = 1 << 20
+        kw = dict(n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3, K=100, alpha=50)
+        orc = pyoracle.OraclePoker(handranks.load_table(), **kw)
+        ring = pyoracle.OracleRing(2 * n, orc.obs_size)
+        kinds = np.array([0, 3], np.uint8)
+        ch = [rng.integers(0, 2**32, (n, 2), dtype=np.uint64).astype(np.uint32) for _ in range(4)]
+        ext = rng.integers(0, 13, (4, n)).astype(np.int64)
+        vec = np.zeros(67)
+        k = hands = 0
+        while spent < min_seconds:
+            orc.tape_decks(SEED, 0, hands)
+            t0 = time.perf_counter()
+            state = orc.reset(None).copy()
+            initial, term = orc.stacks[:, 0].copy(), np.zeros(n, bool)
+            for i in range(16):
+                acts = pyoracle.poker_policy(state, orc.idx, kinds, ch[i % 4], ext[i % 4].copy())
+                seat = orc.idx.copy()
+                nxt, rew, done = orc.step(acts)
+                pyoracle.hand_stats_update(vec, orc.stacks[:, 0], initial, orc.stages, orc.button, done, term.copy(), 0, 2)
+                ring.append(state, acts, rew, nxt, done, seat, term, 0)
+                term |= done
+                state = nxt.copy()
+            spent += time.perf_counter() - t0
+            steps += 16 * n; k += 16; hands += 1
+        sample = (f"{n} tables x {hands} hands x 16 steps: oracle policy + step (OpenMP) + numpy hand statistics and ring "
+                  f"append (the reference does these with torch masks), whole-batch hands")
     elif name == "blackjack":
         n = 4096
         orc = pyoracle.OracleBlackjack(n)

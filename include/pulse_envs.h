@@ -245,11 +245,12 @@ int pulse_poker_policy(const float* obs, int obs_width, const int32_t* seat_idx,
 /* fused into the packed step: the acting seat's rule is evaluated on the registers the step already holds
  * (hole cards, pot), so a scripted seat costs no extra HBM traffic and no extra launch.  actions_or_null is
  * read only for PULSE_AGENT_EXTERNAL seats (may be NULL when every seat is scripted); chosen_out_or_null
- * int64 [N] receives the action that was played (what build_actions leaves in `actions`). */
+ * int64 [N] receives the action that was played (what build_actions leaves in `actions`);
+ * seat_idx_out_or_null int32 [N] the seat that acted (info["seat_idx"] as it was before the step). */
 int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
                                    const int64_t* actions_or_null, const uint8_t* seat_kinds,
                                    const uint32_t* chance2_or_null, uint32_t counter, int64_t* chosen_out_or_null,
-                                   float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
+                                   int32_t* seat_idx_out_or_null, float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
                                    uint64_t seed, uint64_t env_base, pulse_stream_t stream);
 
 /* packed -> reference-shaped tensors (decks, sb/bb, equities, prev_invested are not represented) */
@@ -269,14 +270,17 @@ int pulse_stats_accumulate(const void* reward, int reward_is_float, const uint8_
  *   [0] hands  [1] sum d  [2] sum d^2  [3] #(d > 0)        d = stacks[q_seat] - initial_q_stacks
  *   per terminal-stage bucket b (stage >= 4 -> 4): [4+b] hands  [9+b] sum d  [14+b] wins
  *   per position p = (q_seat - button) mod active_players: [19+p] hands  [35+p] sum d  [51+p] wins
- * terminated_inout uint8 [N] |= done (the caller's `terminated`).  The vector is what gets all-reduced. */
+ * terminated_inout uint8 [N] |= done (the caller's `terminated`).  The vector is what gets all-reduced.
+ * rearm != 0 (packed engine with auto_reset): every raised done flag is a finished hand, `terminated` is not
+ * used, and initial_q_stacks[g] is set to the stack the next deal will start from (refilled like
+ * PokerGPU.py:105-108), so consecutive hands of a table are each measured from their own start. */
 #define PULSE_HAND_STATS_LEN 67
 int pulse_poker_hand_stats(const int32_t* stacks /*[N,P]*/, int n_players, const int32_t* stages /*[N]*/,
                            const int32_t* button /*[N]*/, const uint8_t* done, uint8_t* terminated_inout,
-                           const int32_t* initial_q_stacks /*[N]*/, int q_seat, int active_players, double* stats67,
+                           int32_t* initial_q_stacks /*[N]*/, int q_seat, int active_players, double* stats67,
                            long long n_games, pulse_stream_t stream);
 int pulse_poker_packed_hand_stats(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const uint8_t* done,
-                                  uint8_t* terminated_inout, const int32_t* initial_q_stacks, int q_seat,
+                                  uint8_t* terminated_inout, int32_t* initial_q_stacks, int q_seat, int rearm,
                                   double* stats67, pulse_stream_t stream);
 
 /* ---- transition hand-off to the learner ------------------------------------------

@@ -16,7 +16,7 @@ echo "smoke exit $?" >> $OUT/${TAG}_smoke.log
 
 : > $OUT/${TAG}_bench_lines.jsonl
 timeout 600 python bench.py >> $OUT/${TAG}_bench_lines.jsonl 2> $OUT/${TAG}_bench_default.err
-for w in poker_6max tfe_4x4 tetris particle2d blackjack; do
+for w in poker_6max tfe_4x4 tetris particle2d blackjack poker_hu_scripted poker_hu_train_loop; do
   timeout 400 python bench.py --workload $w --steps 512 --warmup 16 >> $OUT/${TAG}_bench_lines.jsonl 2> $OUT/${TAG}_bench_$w.err
 done
 timeout 400 python bench.py --impl reference --steps 8 --warmup 3 >> $OUT/${TAG}_bench_lines.jsonl 2> $OUT/${TAG}_bench_ref.err
@@ -38,5 +38,13 @@ cap poker_hu_reset poker_packed_reset 1 --steps 16 --warmup 3
 cap poker_6max_step poker_packed_step_kernel 20 --workload poker_6max --steps 16 --warmup 3
 cap tfe_step tfe_step_kernel 40 --workload tfe_4x4 --steps 64 --warmup 8
 cap tetris_step tetris_step_kernel 40 --workload tetris --steps 64 --warmup 8
+# the callers either side of the step (N1-N3): fused policy step, redeal pass, hand statistics, ring append
+cap loop_policy_step poker_packed_step_kernel 12 --workload poker_hu_train_loop --steps 16 --warmup 3
+cap loop_redeal poker_packed_redeal_kernel 12 --workload poker_hu_train_loop --steps 16 --warmup 3
+cap loop_hand_stats hand_stats_kernel 12 --workload poker_hu_train_loop --steps 16 --warmup 3
+cap loop_replay_write replay_write_kernel 12 --workload poker_hu_train_loop --steps 16 --warmup 3
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv \
+  --log-file $OUT/${TAG}_launches_train_loop_steps16.csv \
+  python bench.py --workload poker_hu_train_loop --steps 16 --warmup 3 --cpu-seconds 0 > $OUT/${TAG}_ncu_launches_loop.log 2>&1
 ls -la $OUT > $OUT/${TAG}_ls.txt
 exit 0

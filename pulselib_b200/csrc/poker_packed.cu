@@ -244,7 +244,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
                                    const int64_t* actions_or_null, const uint8_t* seat_kinds,
                                    const uint32_t* chance2_or_null, uint32_t counter, int64_t* chosen_out_or_null,
-                                   float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
+                                   int32_t* seat_idx_out_or_null, float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
                                    uint64_t seed, uint64_t env_base, cudaStream_t stream) {
   int rc = check_cfg(st, cfg);
   if (rc) return rc;
@@ -262,7 +262,8 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   if (cfg->n_games == 0) return PULSE_OK;
   PULSE_REQUIRE(obs_out && reward_out && done_out, "null buffer");
   PULSE_REQUIRE(!auto_reset || st->hand_ctr, "auto_reset needs hand_ctr");
-  pol.chance2 = chance2_or_null; pol.chosen = chosen_out_or_null; pol.counter = counter;
+  pol.chance2 = chance2_or_null; pol.chosen = chosen_out_or_null; pol.seat_before = seat_idx_out_or_null;
+  pol.counter = counter;
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);

@@ -275,6 +275,7 @@ struct PackedPolicy {
   PulseSeatKinds kinds;
   const uint32_t* chance2;   // uint32 [N,2] injected draws, or NULL: tape (seed, env, PULSE_STREAM_ACTION, counter)
   int64_t* chosen;           // int64 [N] action played, or NULL
+  int32_t* seat_before;      // int32 [N] seat that acted (info["seat_idx"] before the step), or NULL
   uint32_t counter;
 };
 
@@ -305,6 +306,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
       a = pulse_policy_action(kind, pk_sel(t.hole0, t.idx), pk_sel(t.hole1, t.idx), (float)t.pot, w0, w1);
     }
     if (pol->chosen) pol->chosen[g] = a;
+    if (pol->seat_before) pol->seat_before[g] = t.idx;
   } else {
     a = actions[g];
   }

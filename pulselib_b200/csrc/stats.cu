@@ -84,13 +84,14 @@ struct PackedHandView {   // packed layout: seat-major stacks, stage/button in t
 template <class View>
 __global__ void __launch_bounds__(kBlock)
 hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict__ terminated,
-                  const int32_t* __restrict__ initial_q, int q_seat, int active_players, double* __restrict__ stats,
-                  long long n) {
+                  int32_t* __restrict__ initial_q, int q_seat, int active_players, int rearm_starting, int rearm_max,
+                  double* __restrict__ stats, long long n) {
   __shared__ double sh[kHandStats];
   for (int i = threadIdx.x; i < kHandStats; i += kBlock) sh[i] = 0.0;
   __syncthreads();
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
-    const bool d = done[g] != 0, before = terminated[g] != 0;
+    // rearm (per-table auto-reset): done is raised for one step only, the next deal starts the next hand
+    const bool d = done[g] != 0, before = rearm_starting > 0 ? false : terminated[g] != 0;
     if (d && !before) {                                     // newly_done (:190)
       const double delta = (double)(v.q_stack(g, q_seat) - initial_q[g]);   // :193-194
       int bucket = v.stage(g);
@@ -102,7 +103,14 @@ hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict_
       atomicAdd(&sh[19 + (pos & 15)], 1.0); atomicAdd(&sh[35 + (pos & 15)], delta);
       if (delta > 0.0) { atomicAdd(&sh[3], 1.0); atomicAdd(&sh[14 + bucket], 1.0); atomicAdd(&sh[51 + (pos & 15)], 1.0); }
     }
-    if (d && !before) terminated[g] = 1;                    // terminated |= dones (:187)
+    if (d && !before) {
+      if (rearm_starting > 0) {   // the next hand's starting stack: what the deal will leave in the seat (PokerGPU.py:105-108)
+        const int fin = v.q_stack(g, q_seat);
+        initial_q[g] = (fin == 0 || fin > rearm_max) ? rearm_starting : fin;
+      } else {
+        terminated[g] = 1;                                  // terminated |= dones (:187)
+      }
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kHandStats; i += kBlock)
@@ -110,18 +118,20 @@ hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict_
 }
 
 template <class View>
-int launch_hand_stats(View v, const uint8_t* done, uint8_t* terminated, const int32_t* initial_q, int q_seat,
-                      int active_players, double* stats, long long n, cudaStream_t stream, const char* what) {
+int launch_hand_stats(View v, const uint8_t* done, uint8_t* terminated, int32_t* initial_q, int q_seat,
+                      int active_players, int rearm_starting, int rearm_max, double* stats, long long n,
+                      cudaStream_t stream, const char* what) {
   long long need = (n + kBlock - 1) / kBlock;
   const int grid = (int)(need < 148 * 8 ? need : 148 * 8);
-  hand_stats_kernel<View><<<grid, kBlock, 0, stream>>>(v, done, terminated, initial_q, q_seat, active_players, stats, n);
+  hand_stats_kernel<View><<<grid, kBlock, 0, stream>>>(v, done, terminated, initial_q, q_seat, active_players,
+                                                       rearm_starting, rearm_max, stats, n);
   return pulse_check_launch(what);
 }
 }  // namespace
 
 extern "C" int pulse_poker_hand_stats(const int32_t* stacks, int n_players, const int32_t* stages,
                                       const int32_t* button, const uint8_t* done, uint8_t* terminated_inout,
-                                      const int32_t* initial_q_stacks, int q_seat, int active_players,
+                                      int32_t* initial_q_stacks, int q_seat, int active_players,
                                       double* stats67, long long n_games, cudaStream_t stream) {
   PULSE_REQUIRE(n_games >= 0, "n_games < 0");
   PULSE_REQUIRE(n_players >= 2 && n_players <= 16 && active_players >= 1 && active_players <= n_players, "bad table size");
@@ -129,12 +139,12 @@ extern "C" int pulse_poker_hand_stats(const int32_t* stacks, int n_players, cons
   if (n_games == 0) return PULSE_OK;
   PULSE_REQUIRE(stacks && stages && button && done && terminated_inout && initial_q_stacks && stats67, "null buffer");
   return launch_hand_stats(CompatHandView{stacks, n_players, stages, button}, done, terminated_inout, initial_q_stacks,
-                           q_seat, active_players, stats67, n_games, stream, "pulse_poker_hand_stats");
+                           q_seat, active_players, 0, 0, stats67, n_games, stream, "pulse_poker_hand_stats");
 }
 
 extern "C" int pulse_poker_packed_hand_stats(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
                                              const uint8_t* done, uint8_t* terminated_inout,
-                                             const int32_t* initial_q_stacks, int q_seat, double* stats67,
+                                             int32_t* initial_q_stacks, int q_seat, int rearm, double* stats67,
                                              cudaStream_t stream) {
   PULSE_REQUIRE(st && cfg, "null state/config");
   PULSE_REQUIRE(q_seat >= 0 && q_seat < cfg->n_players, "q_seat out of range");
@@ -142,6 +152,6 @@ extern "C" int pulse_poker_packed_hand_stats(const PulsePokerPacked* st, const P
   if (cfg->n_games == 0) return PULSE_OK;
   PULSE_REQUIRE(done && terminated_inout && initial_q_stacks && stats67, "null buffer");
   return launch_hand_stats(PackedHandView{st->stack, (long long)cfg->n_games, st->tbl}, done, terminated_inout,
-                           initial_q_stacks, q_seat, cfg->active_players, stats67, cfg->n_games, stream,
-                           "pulse_poker_packed_hand_stats");
+                           initial_q_stacks, q_seat, cfg->active_players, rearm ? cfg->starting_bbs : 0, cfg->max_bbs,
+                           stats67, cfg->n_games, stream, "pulse_poker_packed_hand_stats");
 }

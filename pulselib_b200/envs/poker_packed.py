@@ -126,11 +126,14 @@ class PokerGPUPacked(gym.Env):
         self._done = done
         return self.obs, rewards, done, self.is_truncated, self.get_info()
 
-    def step_policy(self, seat_kinds, actions=None, chance2=None, counter=None, return_actions=True):
+    def step_policy(self, seat_kinds, actions=None, chance2=None, counter=None, return_actions=True, obs_out=None,
+                    return_seat=False):
         """step() with the scripted seats' rules evaluated inside the step kernel: one
         launch does build_actions + step.  seat_kinds: one PULSE_AGENT_* per seat (pulselib_b200.policy);
         `actions` int64 [N] is read only for EXTERNAL seats.  Returns step()'s tuple with the played
-        actions added to info["actions"]."""
+        actions added to info["actions"] (and, with return_seat, the seat that acted in info["seat_idx_before"]).
+        obs_out: write the observation there instead of self.obs (lets a loop ping-pong state / next_state
+        without the reference's state.clone())."""
         kb = bytes(seat_kinds)
         if len(kb) != self.n_players:
             raise ValueError(f"seat_kinds must have {self.n_players} entries")
@@ -153,16 +156,20 @@ class PokerGPUPacked(gym.Env):
         rewards = torch.empty(N, dtype=torch.float32, device=dev)
         done = torch.empty(N, dtype=torch.bool, device=dev)
         chosen = torch.empty(N, dtype=torch.int64, device=dev) if return_actions else None
+        seat = torch.empty(N, dtype=torch.int32, device=dev) if return_seat else None
+        obs = self.obs if obs_out is None else obs_out
         cfg = self._config()
         with _lib.device_guard(dev):
             _lib.check(self._lib.pulse_poker_packed_step_policy(
                 C.byref(self._packed), C.byref(cfg), ptr(actions), C.c_char_p(kb), ptr(chance2), c_u32(counter),
-                ptr(chosen), ptr(self.obs), ptr(rewards), ptr(done), c_i(1 if self.auto_reset else 0),
+                ptr(chosen), ptr(seat), ptr(obs), ptr(rewards), ptr(done), c_i(1 if self.auto_reset else 0),
                 c_u64(self.seed_value), c_u64(self.env_base), _lib.cuda_stream(dev)), "pulse_poker_packed_step_policy")
         self._done = done
         info = self.get_info()
         info["actions"] = chosen
-        return self.obs, rewards, done, self.is_truncated, info
+        if return_seat:
+            info["seat_idx_before"] = seat
+        return obs, rewards, done, self.is_truncated, info
 
     def get_info(self):
         # seat_idx / stacks are what build_actions and the trainers read (environments/Poker/utils.py:108-123)

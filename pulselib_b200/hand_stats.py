@@ -76,8 +76,12 @@ class HandStats:
         self.initial.copy_(self._q_stacks())
         self.terminated.zero_()
 
-    def update(self, done):
-        """Fold the hands that finished on this step (done & ~terminated) into the vector; terminated |= done."""
+    def update(self, done, rearm=None):
+        """Fold the hands that finished on this step (done & ~terminated) into the vector; terminated |= done.
+        rearm (default: the env's auto_reset): every done flag is a finished hand and the table's starting stack is
+        re-armed for the hand the engine deals next."""
+        if rearm is None:
+            rearm = bool(getattr(self.env, "auto_reset", False))
         env, dev = self.env, self.device
         done = done if done.dtype == torch.bool and done.is_contiguous() else done.to(torch.bool).contiguous()
         with _lib.device_guard(dev):
@@ -85,7 +89,7 @@ class HandStats:
                 cfg = env._config()
                 rc = self._lib.pulse_poker_packed_hand_stats(C.byref(env._packed), C.byref(cfg), ptr(done),
                                                              ptr(self.terminated), ptr(self.initial), c_i(self.q_seat),
-                                                             ptr(self.vec), _lib.cuda_stream(dev))
+                                                             c_i(1 if rearm else 0), ptr(self.vec), _lib.cuda_stream(dev))
             else:
                 stacks = env._tensor("stacks", torch.int32)
                 stages = env._tensor("stages", torch.int32)

@@ -87,7 +87,7 @@ int emu_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerCon
   const int W = 13 + 3 * (pr.M - 1);
   PackedPolicy pol;
   for (int s = 0; s < 16; ++s) pol.kinds.kind[s] = s < cfg->n_players ? kinds[s] : (uint8_t)PULSE_AGENT_EXTERNAL;
-  pol.chance2 = chance2; pol.chosen = chosen; pol.counter = counter;
+  pol.chance2 = chance2; pol.chosen = chosen; pol.seat_before = nullptr; pol.counter = counter;
   for (long long g = 0; g < cfg->n_games; ++g)
     EMU_DISPATCH(pr.P, (packed_step_one<MP, true>(*st, pr, actions, obs_out + g * W, reward_out, done_out, auto_reset,
                                                   seed, env_base, cfg->starting_bbs, cfg->max_bbs, g,

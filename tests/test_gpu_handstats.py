@@ -68,3 +68,36 @@ def test_hand_stats_on_packed_rollout(P, q_seat, cuda_device):
     assert s["hands_completed"] == int(want[0]) > 2 * N
     assert sum(m["hands"] for m in s["by_position"].values()) == s["hands_completed"]
     assert sum(m["hands"] for m in s["by_stage"].values()) == s["hands_completed"]
+
+
+def test_hand_stats_rearm_with_auto_reset(cuda_device):
+    """Per-table auto-reset: every done flag is one finished hand, measured from that hand's own starting stack
+    (the stack the deal left in the seat, refilled when busted or above max_bbs)."""
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+    from pulselib_b200.hand_stats import HandStats
+
+    N, P, q = 60_001, 2, 0
+    env = PokerGPUPacked(cuda_device, n_players=P, max_players=P, n_games=N, starting_bbs=30, max_bbs=45, seed=2,
+                         env_base=8, auto_reset=True)
+    hs = HandStats(env, q_seat=q)
+    env.reset()
+    hs.begin_hand()
+    initial = env.unpack()["stacks"][:, q].cpu().numpy().astype(np.int64)
+    want = np.zeros(67)
+    gen = torch.Generator(device=cuda_device)
+    gen.manual_seed(5)
+    refills = 0
+    for t in range(40):
+        a = torch.randint(0, 13, (N,), dtype=torch.int64, device=cuda_device, generator=gen)
+        _, _, done, _, _ = env.step(a)
+        hs.update(done)
+        snap = env.unpack()
+        d = done.cpu().numpy()
+        fin = snap["stacks"][:, q].cpu().numpy().astype(np.int64)
+        pyoracle.hand_stats_update(want, fin, initial, snap["stages"].cpu().numpy(), snap["button"].cpu().numpy(), d,
+                                   np.zeros(N, bool), q, P)
+        refill = (fin == 0) | (fin > 45)
+        refills += int((d & refill).sum())
+        initial = np.where(d, np.where(refill, 30, fin), initial)
+    np.testing.assert_array_equal(hs.vec.cpu().numpy(), want)
+    assert want[0] > 3 * N and refills > 0

@@ -79,10 +79,12 @@ def test_fused_packed_step_equals_oracle_policy_then_step(P, kinds, N, cuda_devi
             chance = rng.integers(0, 2 ** 32, (N, 2), dtype=np.uint64).astype(np.uint32) if inject else \
                 pyoracle.policy_tape(5, 1000, step, N)
             want = pyoracle.poker_policy(orc.obs, orc.idx, np.frombuffer(kb, np.uint8), chance, ext.copy())
+            seat_before = orc.idx.copy()
             o2, r2, d2 = orc.step(want)
             o1, r1, d1, _, info = env.step_policy(kb, actions=torch.from_numpy(ext).to(cuda_device),
                                                   chance2=torch.from_numpy(chance.astype(np.int64)) if inject else None,
-                                                  counter=step)
+                                                  counter=step, return_seat=True)
+            np.testing.assert_array_equal(info["seat_idx_before"].cpu().numpy(), seat_before)
             tag = f"P{P} hand {hand} step {t}"
             np.testing.assert_array_equal(info["actions"].cpu().numpy(), want, err_msg=tag + " played actions")
             np.testing.assert_array_equal(o1.cpu().numpy(), o2, err_msg=tag + " obs")
