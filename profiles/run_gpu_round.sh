@@ -32,6 +32,9 @@ cap() {  # name, kernel regex, skip, bench args...
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:$regex -s $skip -c 1 \
     -o $OUT/${TAG}_${name} -f python bench.py "$@" --cpu-seconds 0 --no-extras > $OUT/${TAG}_ncu_${name}.log 2>&1
   ncu -i $OUT/${TAG}_${name}.ncu-rep --page raw --csv > $OUT/${TAG}_${name}_raw.csv 2>/dev/null
+  ncu -i $OUT/${TAG}_${name}.ncu-rep --page source --csv --print-source cuda,sass > $OUT/${TAG}_${name}_source.csv 2>/dev/null
+  gzip -f $OUT/${TAG}_${name}_source.csv
+  rm -f $OUT/${TAG}_${name}.ncu-rep   # gpurun_out/ is capped at 64 MiB: keep the CSV pages, not the report
 }
 cap poker_hu_step poker_packed_step_kernel 20 --steps 16 --warmup 3
 cap poker_hu_reset poker_packed_reset 1 --steps 16 --warmup 3

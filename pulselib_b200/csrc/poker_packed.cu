@@ -55,7 +55,7 @@ __device__ __forceinline__ void stage_obs_rows(const float (&row)[WT], float4* s
   __syncthreads();
 }
 
-template <int MAXP, int MT, int MINB, bool POLICY = false>
+template <int MAXP, int MT, int MINB, bool POLICY = false, int AUTO = 0>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
                          float* __restrict__ obs_out, float* __restrict__ reward_out,
@@ -69,8 +69,8 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
     const long long g = base + threadIdx.x;
     float row[WT];
     if (g < n)
-      packed_step_one<MAXP, POLICY>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base,
-                                    starting_bbs, max_bbs, g, n, &pol);
+      packed_step_one<MAXP, POLICY, AUTO>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base,
+                                          starting_bbs, max_bbs, g, n, &pol);
     stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
   }
 }
@@ -100,26 +100,47 @@ poker_packed_reset_kernel(PulsePokerPacked S, PokerParams pr, const int32_t* __r
   }
 }
 
-// Redeal pass of auto_reset: one thread per table, most of them return after reading 4 B (hand_ctr); a marked
-// table is dealt its next hand exactly as the whole-batch reset would (same shuffle scratch in shared
-// memory) and its observation row is rewritten.
+// Redeal pass of auto_reset.  Marked tables are usually a small, scattered fraction of the batch, and a deal is
+// ~1,500 instructions: one thread per table would leave most lanes of every warp idle through the whole deal
+// (measured: 3 of 32 lanes active with 10% of the tables marked).  So each block first compacts the marked
+// tables of its tile (kRedealTile tables, 4 B coalesced read of hand_ctr each) into a list in shared memory, then
+// its threads deal list entries densely.  Dealt tables get their observation row rewritten.
+constexpr int kRedealTile = 8 * kBlock;
+
 template <int MAXP>
 __global__ void __launch_bounds__(kBlock, MAXP <= 2 ? 8 : MAXP <= 6 ? 5 : 3)
 poker_packed_redeal_kernel(PulsePokerPacked S, PokerParams pr, uint64_t seed, uint64_t env_base, int starting_bbs,
                            int max_bbs, float* __restrict__ obs_out, long long n) {
   extern __shared__ float4 smem4[];
+  __shared__ int list[kRedealTile];
+  __shared__ int count;
   const int W = 13 + 3 * (pr.M - 1);
+  const bool vec = (W & 3) == 0 && (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
   PackedDeckShared dk{reinterpret_cast<uint8_t*>(smem4) + 4 * threadIdx.x, 4 * kBlock};
-  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
-    float row[13 + 3 * 15];
-    if (!packed_redeal_one<MAXP>(S, pr, seed, env_base, starting_bbs, max_bbs, row, g, n, dk)) continue;
-    float* dst = obs_out + g * W;
-    if ((W & 3) == 0 && (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0) {
-      for (int c = 0; c < W; c += 4)
-        *reinterpret_cast<float4*>(dst + c) = make_float4(row[c], row[c + 1], row[c + 2], row[c + 3]);
-    } else {
-      for (int c = 0; c < W; ++c) dst[c] = row[c];
+  for (long long base = (long long)blockIdx.x * kRedealTile; base < n; base += (long long)gridDim.x * kRedealTile) {
+    if (threadIdx.x == 0) count = 0;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kRedealTile / kBlock; ++k) {
+      const int local = k * kBlock + threadIdx.x;
+      const long long g = base + local;
+      if (g < n && (S.hand_ctr[g] & PKP_REDEAL_MARK)) list[atomicAdd(&count, 1)] = local;
     }
+    __syncthreads();
+    const int cnt = count;
+    for (int i = threadIdx.x; i < cnt; i += kBlock) {
+      const long long g = base + list[i];
+      float row[13 + 3 * 15];
+      packed_redeal_one<MAXP>(S, pr, seed, env_base, starting_bbs, max_bbs, row, g, n, dk);
+      float* dst = obs_out + g * W;
+      if (vec) {
+        for (int c = 0; c < W; c += 4)
+          *reinterpret_cast<float4*>(dst + c) = make_float4(row[c], row[c + 1], row[c + 2], row[c + 3]);
+      } else {
+        for (int c = 0; c < W; ++c) dst[c] = row[c];
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -160,7 +181,7 @@ static int launch_redeal(const PulsePokerPacked* st, const PulsePokerConfig* cfg
 
 static int launch_redeal(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const PokerParams& pr, uint64_t seed,
                          uint64_t env_base, float* obs_out, cudaStream_t stream) {
-  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  const int grid = pulse_grid_for(((long long)cfg->n_games + 7) / 8, kBlock);   // one block per kRedealTile tables
   PKP_DISPATCH(pr.P, (poker_packed_redeal_kernel<MP><<<grid, kBlock, kDeckSmemBytes, stream>>>(
                          *st, pr, seed, env_base, cfg->starting_bbs, cfg->max_bbs, obs_out, (long long)cfg->n_games)));
   return pulse_check_launch("pulse_poker_packed_step (redeal pass)");
@@ -206,23 +227,24 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
-#define PKP_STEP_B(MP, MT, MINB, SMEM)                                                                            \
-  poker_packed_step_kernel<MP, MT, MINB><<<grid, kBlock, SMEM, stream>>>(*st, pr, actions, obs_out, reward_out, \
-                                                                         done_out, auto_reset ? 2 : 0, seed,      \
-                                                                         env_base,                                \
-                                                                         cfg->starting_bbs, cfg->max_bbs,         \
-                                                                         (long long)cfg->n_games)
+#define PKP_STEP_A(MP, MT, MINB, AUTO, SMEM)                                                              \
+  poker_packed_step_kernel<MP, MT, MINB, false, AUTO><<<grid, kBlock, SMEM, stream>>>(                     \
+      *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
+      (long long)cfg->n_games)
+#define PKP_STEP_B(MP, MT, MINB, SMEM)                       \
+  do {                                                       \
+    if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);       \
+    else PKP_STEP_A(MP, MT, MINB, 0, SMEM);                  \
+  } while (0)
   // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 8 (64) otherwise --
   // measured on B200 (profiles/r1c_poker_launch_bounds.md); PULSE_POKER_MINB overrides for experiments
   static const int minb_env = getenv("PULSE_POKER_MINB") ? atoi(getenv("PULSE_POKER_MINB")) : 0;
 #define PKP_STEP(MP, MT, SMEM)                                    \
   do {                                                            \
     const int minb = minb_env > 0 ? minb_env : ((MP) <= 2 ? 10 : 8); \
-    if (minb >= 16) PKP_STEP_B(MP, MT, 16, SMEM);                 \
-    else if (minb >= 12) PKP_STEP_B(MP, MT, 12, SMEM);            \
+    if (minb >= 12) PKP_STEP_B(MP, MT, 12, SMEM);                 \
     else if (minb >= 10) PKP_STEP_B(MP, MT, 10, SMEM);            \
-    else if (minb >= 8) PKP_STEP_B(MP, MT, 8, SMEM);              \
-    else PKP_STEP_B(MP, MT, 6, SMEM);                             \
+    else PKP_STEP_B(MP, MT, 8, SMEM);                             \
   } while (0)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
@@ -235,6 +257,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   }
 #undef PKP_STEP
 #undef PKP_STEP_B
+#undef PKP_STEP_A
 #undef PKP_SMEM4
   rc = pulse_check_launch("pulse_poker_packed_step");
   if (rc || !auto_reset) return rc;
@@ -267,11 +290,15 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
-#define PKP_POL(MP, MT, MINB, SMEM)                                                                        \
-  poker_packed_step_kernel<MP, MT, MINB, true><<<grid, kBlock, SMEM, stream>>>(                             \
-      *st, pr, actions_or_null, obs_out, reward_out, done_out, auto_reset ? 2 : 0, seed, env_base,            \
-      cfg->starting_bbs,                                                                                       \
+#define PKP_POL_A(MP, MT, MINB, AUTO, SMEM)                                                                \
+  poker_packed_step_kernel<MP, MT, MINB, true, AUTO><<<grid, kBlock, SMEM, stream>>>(                       \
+      *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,      \
       cfg->max_bbs, (long long)cfg->n_games, pol)
+#define PKP_POL(MP, MT, MINB, SMEM)                          \
+  do {                                                       \
+    if (auto_reset) PKP_POL_A(MP, MT, MINB, 2, SMEM);        \
+    else PKP_POL_A(MP, MT, MINB, 0, SMEM);                   \
+  } while (0)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
   if (pr.P <= 2 && pr.M == 2 && aligned) PKP_POL(2, 2, 10, PKP_SMEM4(2));
@@ -282,6 +309,7 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
     PKP_DISPATCH(pr.P, PKP_POL(MP, 0, 8, smem));
   }
 #undef PKP_POL
+#undef PKP_POL_A
 #undef PKP_SMEM4
   rc = pulse_check_launch("pulse_poker_packed_step_policy");
   if (rc || !auto_reset) return rc;

@@ -282,7 +282,10 @@ struct PackedPolicy {
 // One step of one table in the packed layout (PokerGPU.py:527-633).  auto_reset: a table that was
 // already done when the step began is dealt a new hand instead (engine extension):
 // the action is ignored, reward 0, done 0 and the observation is the new hand's first one.
-template <int MAXP, bool POLICY = false>
+// AUTO: what a table that was already done when the step began does -- 0 nothing (stays done), 1 deal inline
+// (host emulation of the semantics), 2 mark for the redeal pass (device).  A compile-time choice so the plain
+// step kernel carries no shuffle / evaluator code at all.
+template <int MAXP, bool POLICY = false, int AUTO = 1>
 PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, const int64_t* __restrict__ actions,
                               float* __restrict__ obs_row, float* __restrict__ reward_out,
                               uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
@@ -310,7 +313,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   } else {
     a = actions[g];
   }
-  if (auto_reset == 2 && t.done) {
+  if (AUTO == 2 && auto_reset && t.done) {
     // device path: the deal is left to the redeal pass that follows the step kernel on the same stream
     // (poker_packed.cu).  Dealing here would put the shuffle and 3 x AP hand evaluations into the step
     // kernel's register budget and make every warp with one finished table wait for it (measured: 1.7 ms per
@@ -321,7 +324,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
     pk_obs(t, pr, obs_row);   // placeholder row of the finished hand; the redeal pass overwrites it
     return;
   }
-  if (auto_reset && t.done) {
+  if (AUTO == 1 && auto_reset && t.done) {
     uint32_t hand = S.hand_ctr[g] + 1u;
     S.hand_ctr[g] = hand;
     PackedDeckLocal dk;

@@ -71,6 +71,11 @@ replay_scan_kernel(int32_t* __restrict__ counts, int nb, unsigned long long* __r
   }
 }
 
+// Row mover.  VEC: obs_width % 4 == 0 and 16 B aligned buffers -> a row is L4 = W/4 float4 chunks and a warp moves
+// 32 / L4 selected tables per pass (W = 16: eight tables per pass, every lane busy); otherwise one table per pass,
+// 4 B per lane.  Slots advance by one per selected table, so the ring position is reduced modulo the capacity once
+// per warp and then kept in range with a compare-and-subtract (no 64-bit division per row).
+template <bool VEC>
 __global__ void __launch_bounds__(kBlock)
 replay_write_kernel(const float* __restrict__ state, const float* __restrict__ next_state, int W,
                     const int64_t* __restrict__ actions, const float* __restrict__ rewards,
@@ -80,32 +85,52 @@ replay_write_kernel(const float* __restrict__ state, const float* __restrict__ n
                     float* __restrict__ next_buf, int64_t* __restrict__ action_buf, float* __restrict__ reward_buf,
                     uint8_t* __restrict__ done_buf, long long capacity, long long n) {
   __shared__ int warp_cnt[kBlock / 32];
+  __shared__ int src_list[kBlock / 32][32];
   const long long g = (long long)blockIdx.x * kBlock + threadIdx.x;
   const bool sel = rp_selected(seat, term_before, q_seat, g, n);
   const unsigned bal = __ballot_sync(0xFFFFFFFFu, sel);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) warp_cnt[warp] = __popc(bal);
+  const int cnt = __popc(bal);
+  if (lane == 0) warp_cnt[warp] = cnt;
+  if (sel) src_list[warp][__popc(bal & ((1u << lane) - 1u))] = threadIdx.x;   // rank among the warp's selected
   __syncthreads();
+  if (cnt == 0) return;
   int woff = 0;
   for (int w = 0; w < warp; ++w) woff += warp_cnt[w];
-  const unsigned long long first = *base + (unsigned long long)(offsets[blockIdx.x] + woff);
-  unsigned m = bal;
-  int k = 0;
-  while (m) {                                   // all lanes move the k-th selected table of this warp
-    const int src_lane = __ffs(m) - 1;
-    m &= m - 1;
-    const long long src = (long long)blockIdx.x * kBlock + warp * 32 + src_lane;
-    const long long slot = (long long)((first + (unsigned long long)k) % (unsigned long long)capacity);
-    for (int c = lane; c < W; c += 32) {
-      state_buf[slot * W + c] = state[src * W + c];
-      next_buf[slot * W + c] = next_state[src * W + c];
+  const long long first = (long long)((*base + (unsigned long long)(offsets[blockIdx.x] + woff)) %
+                                      (unsigned long long)capacity);
+  const long long blk = (long long)blockIdx.x * kBlock;
+  if (lane < cnt) {                                    // scalars: lane k moves the k-th selected table's
+    const long long src = blk + src_list[warp][lane];
+    long long slot = first + lane;
+    while (slot >= capacity) slot -= capacity;
+    action_buf[slot] = actions[src];
+    reward_buf[slot] = rewards[src];
+    done_buf[slot] = dones[src];
+  }
+  if (VEC) {
+    const int L4 = W >> 2, per_pass = 32 / L4;         // W <= 128 is checked by the launcher
+    const int r = lane / L4, c = lane - r * L4;
+    for (int k0 = 0; k0 < cnt; k0 += per_pass) {
+      const int k = k0 + r;
+      if (r < per_pass && k < cnt) {
+        const long long src = blk + src_list[warp][k];
+        long long slot = first + k;
+        while (slot >= capacity) slot -= capacity;
+        reinterpret_cast<float4*>(state_buf + slot * W)[c] = reinterpret_cast<const float4*>(state + src * W)[c];
+        reinterpret_cast<float4*>(next_buf + slot * W)[c] = reinterpret_cast<const float4*>(next_state + src * W)[c];
+      }
     }
-    if (lane == 0) {
-      action_buf[slot] = actions[src];
-      reward_buf[slot] = rewards[src];
-      done_buf[slot] = dones[src];
+  } else {
+    for (int k = 0; k < cnt; ++k) {
+      const long long src = blk + src_list[warp][k];
+      long long slot = first + k;
+      while (slot >= capacity) slot -= capacity;
+      for (int c = lane; c < W; c += 32) {
+        state_buf[slot * W + c] = state[src * W + c];
+        next_buf[slot * W + c] = next_state[src * W + c];
+      }
     }
-    ++k;
   }
 }
 }  // namespace
@@ -133,9 +158,15 @@ extern "C" int pulse_replay_append(const float* state, const float* next_state, 
   replay_count_kernel<<<(int)nb, kBlock, 0, stream>>>(seat_idx_before, terminated_before_or_null, q_seat, counts, n_games);
   replay_scan_kernel<<<1, 1024, 0, stream>>>(counts, (int)nb, reinterpret_cast<unsigned long long*>(total_inout), base,
                                              reinterpret_cast<unsigned long long*>(appended_out));
-  replay_write_kernel<<<(int)nb, kBlock, 0, stream>>>(state, next_state, obs_width, actions, rewards, dones,
-                                                      seat_idx_before, terminated_before_or_null, q_seat, counts, base,
-                                                      state_buf, next_state_buf, action_buf, reward_buf, done_buf,
-                                                      capacity, n_games);
+  const bool vec = (obs_width & 3) == 0 && obs_width <= 128 &&
+                   ((reinterpret_cast<uintptr_t>(state) | reinterpret_cast<uintptr_t>(next_state) |
+                     reinterpret_cast<uintptr_t>(state_buf) | reinterpret_cast<uintptr_t>(next_state_buf)) & 15u) == 0;
+#define RP_WRITE(V)                                                                                              \
+  replay_write_kernel<V><<<(int)nb, kBlock, 0, stream>>>(state, next_state, obs_width, actions, rewards, dones,   \
+                                                         seat_idx_before, terminated_before_or_null, q_seat, counts, \
+                                                         base, state_buf, next_state_buf, action_buf, reward_buf,  \
+                                                         done_buf, capacity, n_games)
+  if (vec) RP_WRITE(true); else RP_WRITE(false);
+#undef RP_WRITE
   return pulse_check_launch("pulse_replay_append");
 }

@@ -81,31 +81,34 @@ struct PackedHandView {   // packed layout: seat-major stacks, stage/button in t
   __device__ int btn(long long g) const { return (int)((tbl[4 * g] >> 11) & 15u); }
 };
 
+// Accumulation is in 64-bit integers in shared memory (native atomics; a double atomicAdd in shared memory is a
+// compare-and-swap loop and every finishing table of a block hits the same few slots), converted to double for
+// the one global atomic per non-zero slot per block.  d^2 summed over a 4M-table batch stays far below 2^63.
 template <class View>
 __global__ void __launch_bounds__(kBlock)
 hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict__ terminated,
                   int32_t* __restrict__ initial_q, int q_seat, int active_players, int rearm_starting, int rearm_max,
                   double* __restrict__ stats, long long n) {
-  __shared__ double sh[kHandStats];
-  for (int i = threadIdx.x; i < kHandStats; i += kBlock) sh[i] = 0.0;
+  __shared__ unsigned long long sh[kHandStats];
+  for (int i = threadIdx.x; i < kHandStats; i += kBlock) sh[i] = 0ull;
   __syncthreads();
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
     // rearm (per-table auto-reset): done is raised for one step only, the next deal starts the next hand
     const bool d = done[g] != 0, before = rearm_starting > 0 ? false : terminated[g] != 0;
     if (d && !before) {                                     // newly_done (:190)
-      const double delta = (double)(v.q_stack(g, q_seat) - initial_q[g]);   // :193-194
+      const int fin = v.q_stack(g, q_seat);
+      const long long delta = (long long)fin - (long long)initial_q[g];     // :193-194
       int bucket = v.stage(g);
       bucket = bucket >= 4 ? 4 : (bucket < 0 ? 0 : bucket);                 // bucketize_terminal_stages
       int pos = (q_seat - v.btn(g)) % active_players;                        // calculate_q_seat_positions
       if (pos < 0) pos += active_players;
-      atomicAdd(&sh[0], 1.0); atomicAdd(&sh[1], delta); atomicAdd(&sh[2], delta * delta);
-      atomicAdd(&sh[4 + bucket], 1.0); atomicAdd(&sh[9 + bucket], delta);
-      atomicAdd(&sh[19 + (pos & 15)], 1.0); atomicAdd(&sh[35 + (pos & 15)], delta);
-      if (delta > 0.0) { atomicAdd(&sh[3], 1.0); atomicAdd(&sh[14 + bucket], 1.0); atomicAdd(&sh[51 + (pos & 15)], 1.0); }
-    }
-    if (d && !before) {
+      pos &= 15;
+      const unsigned long long ud = (unsigned long long)delta;               // two's complement: sums wrap back
+      atomicAdd(&sh[0], 1ull); atomicAdd(&sh[1], ud); atomicAdd(&sh[2], (unsigned long long)(delta * delta));
+      atomicAdd(&sh[4 + bucket], 1ull); atomicAdd(&sh[9 + bucket], ud);
+      atomicAdd(&sh[19 + pos], 1ull); atomicAdd(&sh[35 + pos], ud);
+      if (delta > 0) { atomicAdd(&sh[3], 1ull); atomicAdd(&sh[14 + bucket], 1ull); atomicAdd(&sh[51 + pos], 1ull); }
       if (rearm_starting > 0) {   // the next hand's starting stack: what the deal will leave in the seat (PokerGPU.py:105-108)
-        const int fin = v.q_stack(g, q_seat);
         initial_q[g] = (fin == 0 || fin > rearm_max) ? rearm_starting : fin;
       } else {
         terminated[g] = 1;                                  // terminated |= dones (:187)
@@ -114,7 +117,7 @@ hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict_
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kHandStats; i += kBlock)
-    if (sh[i] != 0.0) atomicAdd(stats + i, sh[i]);
+    if (sh[i] != 0ull) atomicAdd(stats + i, (double)(long long)sh[i]);
 }
 
 template <class View>
