@@ -301,7 +301,11 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   } while (0)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
-  if (pr.P <= 2 && pr.M == 2 && aligned) PKP_POL(2, 2, 10, PKP_SMEM4(2));
+  static const int pol_minb = getenv("PULSE_POKER_POLICY_MINB") ? atoi(getenv("PULSE_POKER_POLICY_MINB")) : 10;
+  if (pr.P <= 2 && pr.M == 2 && aligned) {
+    if (pol_minb >= 10) PKP_POL(2, 2, 10, PKP_SMEM4(2));
+    else PKP_POL(2, 2, 8, PKP_SMEM4(2));
+  }
   else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) PKP_POL(6, 6, 8, PKP_SMEM4(6));
   else if (pr.P > 6 && pr.M == 10 && aligned) PKP_POL(10, 10, 8, PKP_SMEM4(10));
   else {

@@ -231,26 +231,31 @@ PULSE_HD float pkp_equity_from(uint64_t ev, int stage) {
 // needed (the actor's, or each live seat's at showdown) -- with six or ten seats prefetching all of
 // them would cost more bandwidth than the latency is worth.
 template <int MAXP, bool PRE>
-struct PackedEv {
+struct PackedEv;
+template <int MAXP>
+struct PackedEv<MAXP, true> {
   const uint64_t* ev; long long g, n;
-  uint64_t w[PRE ? MAXP : 1];
+  uint64_t w[MAXP];
   PULSE_HD void prefetch(int AP) {
-    if (PRE) {
 #pragma unroll
-      for (int s = 0; s < MAXP; ++s) w[s] = s < AP ? ev[(long long)s * n + g] : 0;
-    }
+    for (int s = 0; s < MAXP; ++s) w[s] = s < AP ? ev[(long long)s * n + g] : 0;
   }
   PULSE_HD uint64_t word(int s) const {
-    if (PRE) {
-      uint64_t v = w[0];
+    uint64_t v = w[0];
 #pragma unroll
-      for (int k = 1; k < (PRE ? MAXP : 1); ++k) if (s == k) v = w[k];
-      return v;
-    }
-    return ev[(long long)s * n + g];
+    for (int k = 1; k < MAXP; ++k) if (s == k) v = w[k];
+    return v;
   }
   template <int MP>
   PULSE_HD int32_t rank(const PokerTable<MP>&, int s) const { return (int32_t)(word(s) & 0xFFFFu); }  // showdown rank = seven-card value
+};
+template <int MAXP>
+struct PackedEv<MAXP, false> {
+  const uint64_t* ev; long long g, n;
+  PULSE_HD void prefetch(int) {}
+  PULSE_HD uint64_t word(int s) const { return ev[(long long)s * n + g]; }
+  template <int MP>
+  PULSE_HD int32_t rank(const PokerTable<MP>&, int s) const { return (int32_t)(word(s) & 0xFFFFu); }
 };
 
 // unconditional store of a freshly dealt table
@@ -310,8 +315,6 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
     }
     if (pol->chosen) pol->chosen[g] = a;
     if (pol->seat_before) pol->seat_before[g] = t.idx;
-  } else {
-    a = actions[g];
   }
   if (AUTO == 2 && auto_reset && t.done) {
     // device path: the deal is left to the redeal pass that follows the step kernel on the same stream
@@ -338,6 +341,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   }
   const PokerTable<MAXP> t0 = t;
   const PackedDeck deck{fb, 2 * AP};
+  if (!POLICY) a = actions[g];
   const bool prev_done = t.done;
   const int actor = t.idx;                                           // :531
   const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537

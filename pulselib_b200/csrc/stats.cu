@@ -89,9 +89,14 @@ __global__ void __launch_bounds__(kBlock)
 hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict__ terminated,
                   int32_t* __restrict__ initial_q, int q_seat, int active_players, int rearm_starting, int rearm_max,
                   double* __restrict__ stats, long long n) {
-  __shared__ unsigned long long sh[kHandStats];
-  for (int i = threadIdx.x; i < kHandStats; i += kBlock) sh[i] = 0ull;
+  // totals live in registers and are reduced by shuffles; the per-bucket / per-position slots are private to each
+  // warp, so an atomic only ever meets lanes of its own warp instruction
+  __shared__ unsigned long long sh[kBlock / 32][kHandStats];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < (kBlock / 32) * kHandStats; i += kBlock) (&sh[0][0])[i] = 0ull;
   __syncthreads();
+  unsigned long long t_n = 0, t_s = 0, t_s2 = 0, t_w = 0;
+  unsigned long long* mine = sh[warp];
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
     // rearm (per-table auto-reset): done is raised for one step only, the next deal starts the next hand
     const bool d = done[g] != 0, before = rearm_starting > 0 ? false : terminated[g] != 0;
@@ -104,10 +109,10 @@ hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict_
       if (pos < 0) pos += active_players;
       pos &= 15;
       const unsigned long long ud = (unsigned long long)delta;               // two's complement: sums wrap back
-      atomicAdd(&sh[0], 1ull); atomicAdd(&sh[1], ud); atomicAdd(&sh[2], (unsigned long long)(delta * delta));
-      atomicAdd(&sh[4 + bucket], 1ull); atomicAdd(&sh[9 + bucket], ud);
-      atomicAdd(&sh[19 + pos], 1ull); atomicAdd(&sh[35 + pos], ud);
-      if (delta > 0) { atomicAdd(&sh[3], 1ull); atomicAdd(&sh[14 + bucket], 1ull); atomicAdd(&sh[51 + pos], 1ull); }
+      t_n += 1ull; t_s += ud; t_s2 += (unsigned long long)(delta * delta);
+      atomicAdd(&mine[4 + bucket], 1ull); atomicAdd(&mine[9 + bucket], ud);
+      atomicAdd(&mine[19 + pos], 1ull); atomicAdd(&mine[35 + pos], ud);
+      if (delta > 0) { t_w += 1ull; atomicAdd(&mine[14 + bucket], 1ull); atomicAdd(&mine[51 + pos], 1ull); }
       if (rearm_starting > 0) {   // the next hand's starting stack: what the deal will leave in the seat (PokerGPU.py:105-108)
         initial_q[g] = (fin == 0 || fin > rearm_max) ? rearm_starting : fin;
       } else {
@@ -115,9 +120,19 @@ hand_stats_kernel(View v, const uint8_t* __restrict__ done, uint8_t* __restrict_
       }
     }
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    t_n += __shfl_down_sync(0xFFFFFFFFu, t_n, o); t_s += __shfl_down_sync(0xFFFFFFFFu, t_s, o);
+    t_s2 += __shfl_down_sync(0xFFFFFFFFu, t_s2, o); t_w += __shfl_down_sync(0xFFFFFFFFu, t_w, o);
+  }
+  if (lane == 0) { mine[0] = t_n; mine[1] = t_s; mine[2] = t_s2; mine[3] = t_w; }
   __syncthreads();
-  for (int i = threadIdx.x; i < kHandStats; i += kBlock)
-    if (sh[i] != 0ull) atomicAdd(stats + i, (double)(long long)sh[i]);
+  for (int i = threadIdx.x; i < kHandStats; i += kBlock) {
+    unsigned long long acc = 0ull;
+#pragma unroll
+    for (int w = 0; w < kBlock / 32; ++w) acc += sh[w][i];
+    if (acc != 0ull) atomicAdd(stats + i, (double)(long long)acc);
+  }
 }
 
 template <class View>
