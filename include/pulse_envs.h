@@ -253,6 +253,13 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
                                    int32_t* seat_idx_out_or_null, float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
                                    uint64_t seed, uint64_t env_base, pulse_stream_t stream);
 
+/* Enumerated hand strength (no reference behaviour -- the reference's notes call its table-walk
+ * proxy a known weakness, rl/depth_notes.txt:302-333).  strength_out float32 [N, active_players]: the expectation over
+ * the board cards still to come of the river strength clamp((v7 - 4109) / 32765, 0, 1) (PokerGPU.py:477-481) from each
+ * seat's own point of view; river = the reference's value, turn = 46 cards, flop = 1081 pairs, preflop / finished
+ * hands = 0.5.  An optional input for a caller's reward; the step's own reward keeps the reference's proxy. */
+int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,
+                                           pulse_stream_t stream);
 /* packed -> reference-shaped tensors (decks, sb/bb, equities, prev_invested are not represented) */
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
                        pulse_stream_t stream);

@@ -190,3 +190,51 @@ int oracle_set_threads(int n) { if (n > 0) omp_set_num_threads(n); return omp_ge
 #else
 int oracle_set_threads(int n) { (void)n; return 1; }
 #endif
+
+/* Enumerated hand strength -- no reference code computes it; this restates the DEFINITION the
+ * engine's header gives (include/pulse_envs.h, pulse_poker_packed_enumerated_strength), built on the reference's river
+ * quantity clamp((v7 - 4109) / 32765, 0, 1) (/root/reference/environments/Poker/PokerGPU.py:477-481): the mean of
+ * that quantity over every completion of the board from the cards the seat cannot see.  Brute force with the
+ * five-of-seven evaluator above; board = five cards (1..52), the first 3/4/5 visible at stage 1/2/3. */
+float oracle_enumerated_strength(int stage, int h0, int h1, const int32_t* board) {
+  if (stage < 1 || stage > 3) return 0.5f;
+  int vis = stage + 2;
+  int32_t c[7];
+  char used[53] = {0};
+  c[0] = h0; c[1] = h1; used[h0] = used[h1] = 1;
+  for (int i = 0; i < vis; ++i) { c[2 + i] = board[i]; used[board[i]] = 1; }
+  long long sum = 0, count = 0;
+  if (stage == 3) {
+    int v = oracle_eval_bruteforce(c, 7) - 4109;
+    sum = v < 0 ? 0 : (v > 32765 ? 32765 : v); count = 1;
+  } else if (stage == 2) {
+    for (int x = 1; x <= 52; ++x) {
+      if (used[x]) continue;
+      c[6] = x;
+      int v = oracle_eval_bruteforce(c, 7) - 4109;
+      sum += v < 0 ? 0 : (v > 32765 ? 32765 : v); ++count;
+    }
+  } else {
+    for (int x = 1; x <= 52; ++x) {
+      if (used[x]) continue;
+      for (int y = x + 1; y <= 52; ++y) {
+        if (used[y]) continue;
+        c[5] = x; c[6] = y;
+        int v = oracle_eval_bruteforce(c, 7) - 4109;
+        sum += v < 0 ? 0 : (v > 32765 ? 32765 : v); ++count;
+      }
+    }
+  }
+  return (float)sum / ((float)count * 32765.0f);
+}
+
+/* out [n, ap] from the reference-shaped arrays: stages [n], hands [n, P, 2], board [n, 5] (int32) */
+void oracle_enumerated_strength_batch(const int32_t* stages, const int32_t* hands, const int32_t* board, int P, int ap,
+                                      long long n, float* out) {
+  init_keys();
+#pragma omp parallel for schedule(dynamic, 16)
+  for (long long g = 0; g < n; ++g)
+    for (int s = 0; s < ap; ++s)
+      out[g * ap + s] = oracle_enumerated_strength(stages[g], hands[(g * P + s) * 2], hands[(g * P + s) * 2 + 1],
+                                                   board + g * 5);
+}

@@ -141,6 +141,17 @@ def policy_tape(seed, env_base, counter, n):
     return out
 
 
+def enumerated_strength(stages, hands, board, active_players):
+    """oracle_enumerated_strength_batch: brute-force mean river strength over the unseen board cards, [n, ap]."""
+    st = np.ascontiguousarray(stages, dtype=np.int32)
+    h = np.ascontiguousarray(hands, dtype=np.int32)
+    b = np.ascontiguousarray(board, dtype=np.int32)
+    out = np.zeros((len(st), int(active_players)), np.float32)
+    lib().oracle_enumerated_strength_batch(p(st), p(h), p(b), C.c_int(h.shape[1]), C.c_int(int(active_players)),
+                                           C.c_longlong(len(st)), p(out))
+    return out
+
+
 def hand_stats_update(vec, q_stacks, initial, stages, button, done, terminated, q_seat, active_players):
     """Numpy restatement of one step of the reference's hand bookkeeping
     (/root/reference/scripts/Poker/trainGPU_performance.py:186-206 + utils/performance.py:55-59, :170-174) folded into

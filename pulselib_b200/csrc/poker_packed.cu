@@ -151,6 +151,20 @@ poker_packed_unpack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr
     packed_unpack_one<MAXP>(S, C, pr, g, n);
 }
 
+// one thread per (table, seat): seat-major so a warp reads 32 consecutive tables' hole cards and table words
+__global__ void __launch_bounds__(kBlock)
+poker_packed_strength_kernel(PulsePokerPacked S, int AP, float* __restrict__ out, long long n) {
+  const long long total = n * AP;
+  for (long long i = (long long)blockIdx.x * kBlock + threadIdx.x; i < total; i += (long long)gridDim.x * kBlock) {
+    const int s = (int)(i / n);
+    const long long g = i - (long long)s * n;
+    const int stage = (int)(S.tbl[4 * g] & 7u);
+    const uint32_t fb = S.tbl2[2 * g + 1];
+    const uint32_t h = S.hole[(long long)s * n + g];
+    out[g * AP + s] = packed_enumerated_strength(stage, (int)(h & 63u), (int)((h >> 6) & 63u), fb);
+  }
+}
+
 int check_cfg(const void* st, const PulsePokerConfig* cfg) {
   if (!st || !cfg) { pulse_set_error("null state/config"); return PULSE_EINVAL; }
   if (cfg->n_players < 2 || cfg->n_players > 10) { pulse_set_error("n_players must be in 2..10"); return PULSE_EINVAL; }
@@ -318,6 +332,18 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   rc = pulse_check_launch("pulse_poker_packed_step_policy");
   if (rc || !auto_reset) return rc;
   return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
+}
+
+int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,
+                                           cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  if (cfg->n_games == 0) return PULSE_OK;
+  PULSE_REQUIRE(strength_out != nullptr, "strength_out is null");
+  const long long total = (long long)cfg->n_games * cfg->active_players;
+  poker_packed_strength_kernel<<<pulse_grid_for(total, kBlock), kBlock, 0, stream>>>(*st, cfg->active_players,
+                                                                                    strength_out, (long long)cfg->n_games);
+  return pulse_check_launch("pulse_poker_packed_enumerated_strength");
 }
 
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,

@@ -403,6 +403,41 @@ PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr,
                          g, n, dk);
 }
 
+// ---- enumerated hand strength ---------------------------------------------------------
+// The reference's equity is a table-walk proxy that its own notes call a known weakness
+// (/root/reference/rl/depth_notes.txt:302-333): on the turn and flop it feeds 6- and 5-card table values through
+// constants fitted to other quantities (PokerGPU.py:497-523).  This is the enumerated form of the same river
+// quantity: the expectation, over the board cards still to come, of the river strength
+// clamp((v7 - 4109) / 32765, 0, 1) (:477-481), from the seat's own point of view (unseen = 52 minus its two hole
+// cards and the visible board).  River: the reference's value itself.  Turn: 46 river cards.  Flop: C(47,2) = 1081
+// turn/river pairs.  Preflop: 0.5, as the reference (:461).  The numerators are summed as integers, so the result
+// does not depend on the enumeration order: strength = float(sum) / (float(count) * 32765).
+PULSE_HD int64_t pkp_strength_num(uint64_t m7) {
+  int v = pe_eval_mask64(m7) - 4109;
+  return v < 0 ? 0 : (v > 32765 ? 32765 : v);
+}
+PULSE_HD float packed_enumerated_strength(int stage, int h0, int h1, uint32_t fb) {
+  if (stage < 1 || stage > 3) return 0.5f;
+  uint64_t known = pe_add_card64(h1, pe_add_card64(h0, 0));
+  const int vis = stage == 1 ? 3 : stage == 2 ? 4 : 5;
+  for (int i = 0; i < vis; ++i) known = pe_add_card64((int)((fb >> (6 * i)) & 63u), known);
+  int64_t sum = 0, count = 0;
+  if (stage == 3) { sum = pkp_strength_num(known); count = 1; }
+  else {
+    for (int c1 = 1; c1 <= 52; ++c1) {
+      const uint64_t m1 = pe_add_card64(c1, 0);
+      if (m1 & known) continue;
+      if (stage == 2) { sum += pkp_strength_num(known | m1); ++count; continue; }
+      for (int c2 = c1 + 1; c2 <= 52; ++c2) {
+        const uint64_t m2 = pe_add_card64(c2, 0);
+        if (m2 & known) continue;
+        sum += pkp_strength_num(known | m1 | m2); ++count;
+      }
+    }
+  }
+  return PULSE_FDIV((float)sum, PULSE_FMUL((float)count, 32765.0f));
+}
+
 // packed -> reference-shaped tensors (for inspection and parity checks); decks, sb/bb, equities and
 // prev_invested are not represented in the packed layout and are left untouched.
 template <int MAXP>

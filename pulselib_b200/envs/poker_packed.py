@@ -171,6 +171,17 @@ class PokerGPUPacked(gym.Env):
             info["seat_idx_before"] = seat
         return obs, rewards, done, self.is_truncated, info
 
+    def enumerated_strength(self):
+        """float32 [N, active_players]: river hand strength averaged over the board cards still to come, per seat
+        (see include/pulse_envs.h).  An optional reward input; step() keeps the reference's proxy."""
+        out = torch.empty((self.n_games, int(self.active_players)), dtype=torch.float32, device=self.device)
+        cfg = self._config()
+        with _lib.device_guard(self.device):
+            _lib.check(self._lib.pulse_poker_packed_enumerated_strength(C.byref(self._packed), C.byref(cfg), ptr(out),
+                                                                       _lib.cuda_stream(self.device)),
+                       "pulse_poker_packed_enumerated_strength")
+        return out
+
     def get_info(self):
         # seat_idx / stacks are what build_actions and the trainers read (environments/Poker/utils.py:108-123)
         return {"active_players": self.active_players, "stacks": _Lazy(self, "stacks"), "seat_idx": _Lazy(self, "idx")}

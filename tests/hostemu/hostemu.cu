@@ -94,6 +94,7 @@ int emu_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerCon
                                                   (long long)cfg->n_games, &pol)));
   return 0;
 }
+float emu_enumerated_strength(int stage, int h0, int h1, uint32_t fb) { return packed_enumerated_strength(stage, h0, h1, fb); }
 int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg) {
   PokerParams pr = mk(cfg);
   for (long long g = 0; g < cfg->n_games; ++g)
