@@ -49,5 +49,6 @@ cap loop_replay_write replay_write_kernel 12 --workload poker_hu_train_loop --st
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv \
   --log-file $OUT/${TAG}_launches_train_loop_steps16.csv \
   python bench.py --workload poker_hu_train_loop --steps 16 --warmup 3 --cpu-seconds 0 > $OUT/${TAG}_ncu_launches_loop.log 2>&1
+timeout 300 python profiles/time_strength.py > $OUT/${TAG}_time_strength.json 2> $OUT/${TAG}_time_strength.err
 ls -la $OUT > $OUT/${TAG}_ls.txt
 exit 0
