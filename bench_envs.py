@@ -26,7 +26,7 @@ SPECS = {
     # build_actions + step as ONE launch (scripted seats evaluated inside the step kernel),
     # per-table auto-reset.  Bytes: the step's 201 B with the 8 B action read replaced by the 8 B write of
     # the action that was played.
-    "poker_hu_scripted": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_step_kernel<2, 2, 10, true>", graph=0,
+    "poker_hu_scripted": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_step_kernel<2, 2, 8, true, 2>", graph=0,
                               actions=1,
                               desc="PokerGPU heads-up, {n} tables/GPU, seats played by the scripted TightAggressive and "
                                    "SmallBall rules inside the step kernel (no action tensor), draws from the chance "
@@ -36,7 +36,7 @@ SPECS = {
     # step, learning seat's actions supplied, hand statistics folded, learning-seat transitions appended to the
     # ring; state/next_state ping-pong instead of state.clone().  Bytes: step 201 + stats 2 + ring select 5 +
     # ~half the tables' transitions (2 rows read + written, 141 B each way).
-    "poker_hu_train_loop": dict(n=1 << 22, algo_bytes=201 + 2 + 5 + 141, kernel="step<2,2,10,true> + redeal + hand_stats + replay x3",
+    "poker_hu_train_loop": dict(n=1 << 22, algo_bytes=201 + 2 + 5 + 141, kernel="step<2,2,8,true,2> + redeal + hand_stats + replay x3",
                                 graph=0, actions=16,
                                 desc="PokerGPU heads-up, {n} tables/GPU, seat 0 = learner (uniform random actions supplied), "
                                      "seat 1 = TightAggressive rule inside the step kernel, per-table auto-reset, hand "

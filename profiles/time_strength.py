@@ -1,10 +1,14 @@
 """Times pulse_poker_packed_enumerated_strength (8(f) N4) on 1M heads-up tables per street (CUDA events)."""
 import json
 
+import sys
+from pathlib import Path
+
 import numpy as np
 import torch
 
-from pulselib_b200.envs.poker_packed import PokerGPUPacked
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from pulselib_b200.envs.poker_packed import PokerGPUPacked  # noqa: E402
 
 dev = torch.device("cuda:0")
 N = 1 << 20
