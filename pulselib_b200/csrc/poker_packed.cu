@@ -55,13 +55,46 @@ __device__ __forceinline__ void stage_obs_rows(const float (&row)[WT], float4* s
   __syncthreads();
 }
 
+// L2 prefetch one wave ahead.  The step is one short-lived CTA per 128-table tile and every first-level load
+// of a tile goes to DRAM (ncu: long-scoreboard is the top stall, DRAM at 56% with six seats), so the kernel is
+// bound by how many loads a resident thread set can keep in flight.  Each CTA therefore asks L2 (prefetch.global.L2:
+// no register, no scoreboard) for the state lines of the tile `ahead` CTAs further on -- about one resident
+// wave, i.e. the tile that takes this CTA's slot when it retires -- so that tile's loads meet L2 latency instead
+// of DRAM latency.  DRAM traffic is unchanged (every line is still fetched once); one instruction per thread.
+template <int MAXP>
+__device__ __forceinline__ void packed_prefetch_tile(const PulsePokerPacked& S, const int64_t* actions, int AP,
+                                                     long long base, long long n) {
+  if (base >= n) return;
+  const long long cnt = (n - base) < kBlock ? (n - base) : kBlock;
+  // line slots: 16 tbl, 8 tbl2, 8 actions, then per seat 4 stack + 4 crb + 4 inv + 2 hole
+  const int total = 32 + 14 * AP;
+  for (int i = threadIdx.x; i < total; i += kBlock) {
+    const char* p; long long bytes; int k;
+    if (i < 16) { p = reinterpret_cast<const char*>(S.tbl + 4 * base); bytes = cnt * 16; k = i; }
+    else if (i < 24) { p = reinterpret_cast<const char*>(S.tbl2 + 2 * base); bytes = cnt * 8; k = i - 16; }
+    else if (i < 32) { p = reinterpret_cast<const char*>(actions + base); bytes = actions ? cnt * 8 : 0; k = i - 24; }
+    else {
+      const int s = (i - 32) / 14, j = (i - 32) - 14 * s;
+      const long long o = (long long)s * n + base;
+      if (j < 4) { p = reinterpret_cast<const char*>(S.stack + o); bytes = cnt * 4; k = j; }
+      else if (j < 8) { p = reinterpret_cast<const char*>(S.crb + o); bytes = cnt * 4; k = j - 4; }
+      else if (j < 12) { p = reinterpret_cast<const char*>(S.inv + o); bytes = cnt * 4; k = j - 8; }
+      else { p = reinterpret_cast<const char*>(S.hole + o); bytes = cnt * 2; k = j - 12; }
+    }
+    if ((long long)k * 128 < bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + k * 128));
+  }
+}
+
 template <int MAXP, int MT, int MINB, bool POLICY = false, int AUTO = 0>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
                          float* __restrict__ obs_out, float* __restrict__ reward_out,
                          uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
-                         int starting_bbs, int max_bbs, long long n, PackedPolicy pol = PackedPolicy()) {
+                         int starting_bbs, int max_bbs, long long n, int l2_ahead,
+                         PackedPolicy pol = PackedPolicy()) {
   extern __shared__ float4 smem4[];
+  if (l2_ahead > 0)
+    packed_prefetch_tile<MAXP>(S, actions, pr.AP, ((long long)blockIdx.x + l2_ahead) * kBlock, n);
   if (MT > 0) pr.M = MT;
   constexpr int WT = MT > 0 ? 13 + 3 * (MT - 1) : 13 + 3 * 15;  // row buffer size
   const int W = 13 + 3 * (pr.M - 1);
@@ -182,6 +215,13 @@ PokerParams make_params(const PulsePokerConfig* c) {
 
 }  // namespace
 
+// how many CTAs ahead the step kernel prefetches into L2: one resident wave (148 SMs x resident CTAs per SM);
+// PULSE_POKER_L2_AHEAD overrides (0 turns the prefetch off) for experiments
+static int l2_ahead_for(int minb) {
+  static const int env = getenv("PULSE_POKER_L2_AHEAD") ? atoi(getenv("PULSE_POKER_L2_AHEAD")) : -1;
+  return env >= 0 ? env : 148 * minb;
+}
+
 static int launch_redeal(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const PokerParams& pr, uint64_t seed,
                          uint64_t env_base, float* obs_out, cudaStream_t stream);
 
@@ -244,7 +284,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #define PKP_STEP_A(MP, MT, MINB, AUTO, SMEM)                                                              \
   poker_packed_step_kernel<MP, MT, MINB, false, AUTO><<<grid, kBlock, SMEM, stream>>>(                     \
       *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
-      (long long)cfg->n_games)
+      (long long)cfg->n_games, l2_ahead_for(MINB))
 #define PKP_STEP_B(MP, MT, MINB, SMEM)                       \
   do {                                                       \
     if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);       \
@@ -307,7 +347,7 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
 #define PKP_POL_A(MP, MT, MINB, AUTO, SMEM)                                                                \
   poker_packed_step_kernel<MP, MT, MINB, true, AUTO><<<grid, kBlock, SMEM, stream>>>(                       \
       *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,      \
-      cfg->max_bbs, (long long)cfg->n_games, pol)
+      cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB), pol)
 #define PKP_POL(MP, MT, MINB, SMEM)                          \
   do {                                                       \
     if (auto_reset) PKP_POL_A(MP, MT, MINB, 2, SMEM);        \

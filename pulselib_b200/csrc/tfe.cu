@@ -43,6 +43,18 @@ constexpr int kTableBytes = 65536 * 2 + 65536;                    // result u16 
 constexpr int kLutBytes = 256 * 8;                                // byte (two cells) -> two int32 tile values
 constexpr int kStepSmem = kTableBytes + kStepBlock * 8 + kLutBytes;  // + one packed board per thread + the LUT
 
+// The byte LUT's 8-byte entries sit in 16 bank pairs chosen by the low nibble of the index, i.e. by the
+// first cell's exponent alone; with small exponents most of a half-warp lands on 3-4 pairs.  Folding the
+// second cell's low two bits into bits 2-3 (a bijection on bytes) spreads them over all 16 (7.0 -> 4.1
+// wavefronts per read on boards from random play).  The staged board is swizzled once per board instead.
+__device__ __forceinline__ uint32_t tfe_lut_slot(uint32_t byte) { return byte ^ ((byte >> 2) & 0x0Cu); }
+__device__ __forceinline__ uint64_t tfe_lut_swizzle_board(uint64_t b) {
+  uint32_t lo = (uint32_t)b, hi = (uint32_t)(b >> 32);
+  lo ^= (lo >> 2) & 0x0C0C0C0Cu;
+  hi ^= (hi >> 2) & 0x0C0C0C0Cu;
+  return ((uint64_t)hi << 32) | lo;
+}
+
 template <int SIDE>
 __device__ __forceinline__ void tfe_warp_write_obs(const uint64_t* __restrict__ wboards, const uint2* __restrict__ lut,
                                                    const long long wb, const long long n, int32_t* __restrict__ obs_out) {
@@ -109,7 +121,7 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   uint64_t* wboards = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes) + (threadIdx.x & ~31);
   uint2* lut = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8);
   if (threadIdx.x < 256)
-    lut[threadIdx.x] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
+    lut[tfe_lut_slot(threadIdx.x)] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
   __syncthreads();
   const int lane = threadIdx.x & 31;
   for (; g - lane < n; g += stride) {                              // warp-uniform trip count
@@ -119,26 +131,28 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
     if (gn < n) { nb_in = boards[gn]; ntotal = score[gn]; na = (int)actions[gn]; ndone = auto_reset && done_out[gn]; }
     uint64_t nb = 0;
     if (valid) {
-      PulseU4 sp, rc;
-      sp.x = sp.y = sp.z = sp.w = 0; rc = sp;
-      if (was_done) {
-        if (reset_chance) { const uint4 c = reset_chance[g]; rc.x = c.x; rc.y = c.y; rc.z = c.z; rc.w = c.w; }
-        else rc = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TFE_RESET, counter);
+      // one chance block per board-step: the reset stream for a board being re-dealt, the spawn stream
+      // otherwise -- a single Philox call either way (no second instruction stream for finished boards)
+      PulseU4 c;
+      c.x = c.y = c.z = c.w = 0;
+      const bool injected = was_done ? reset_chance != nullptr : chance != nullptr;
+      if (injected) {
+        if (was_done) { const uint4 v = reset_chance[g]; c.x = v.x; c.y = v.y; c.z = v.z; c.w = v.w; }
+        else { const uint2 v = chance[g]; c.x = v.x; c.y = v.y; }
       } else {
-        if (chance) { const uint2 c = chance[g]; sp.x = c.x; sp.y = c.y; }
-        else sp = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_TFE_SPAWN, counter);
+        c = pulse_tape(seed, env_base + (uint64_t)g, was_done ? PULSE_STREAM_TFE_RESET : PULSE_STREAM_TFE_SPAWN, counter);
       }
       int32_t reward; bool done;
       const int64_t total0 = total;
       if (!table_ready) { pulse_mbar_wait(&table_bar, 0); table_ready = true; }  // first board only
-      nb = tfe_step_one<SIDE>(b, a, was_done, auto_reset, sp, rc, total, reward, done, rows);
+      nb = tfe_step_fused<SIDE>(b, a, was_done, c, total, reward, done, rows);
       if (nb != b) boards[g] = nb;
       if (total != total0) score[g] = total;
       reward_out[g] = reward;
       done_out[g] = done;
     }
     if (obs_out) {
-      wboards[lane] = nb;
+      wboards[lane] = SIDE == 4 ? tfe_lut_swizzle_board(nb) : nb;
       __syncwarp();
       tfe_warp_write_obs<SIDE>(wboards, lut, g - lane, n, obs_out);
       __syncwarp();
@@ -153,8 +167,8 @@ __global__ void tfe_build_table_kernel(uint16_t* __restrict__ result, uint8_t* _
   const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r < 65536u) {
     uint32_t sc = 0;
-    result[r] = (uint16_t)tfe_squash_row(r, sc);
-    code[r] = (uint8_t)tfe_score_code(r);
+    result[tfe_row_slot(r)] = (uint16_t)tfe_squash_row(r, sc);
+    code[tfe_row_slot(r)] = (uint8_t)tfe_score_code(r);
   }
 }
 

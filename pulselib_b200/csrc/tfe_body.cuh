@@ -115,10 +115,30 @@ PULSE_HD bool tfe_game_over(uint64_t b) {
   return true;
 }
 
+// Where a row lives in the staged table.  Tile exponents are small (most cells hold 0..3), so the raw row
+// value puts nearly every lookup of a warp into the same ~8 shared-memory banks with different addresses
+// (6.9 wavefronts per lookup measured, profiles/r1q_tfe_step_raw.csv).  Folding bits 6.. and 11.. into the
+// low bits (a bijection on 16 bits: bit i of the slot = row[i] ^ row[i+6] ^ row[i+11]) spreads the same
+// lookups over all 32 banks (3.1-3.4 wavefronts on boards from random play).
+PULSE_HD uint32_t tfe_row_slot(uint32_t row) { return (row ^ (row >> 6) ^ (row >> 11)) & 0xFFFFu; }
+// tfe_row_slot on the four 16-bit rows of a board at once
+PULSE_HD uint64_t tfe_board_slots(uint64_t b) {
+#ifdef __CUDA_ARCH__
+  uint32_t lo = (uint32_t)b, hi = (uint32_t)(b >> 32);
+  lo = lo ^ ((lo >> 6) & 0x03FF03FFu) ^ ((lo >> 11) & 0x001F001Fu);
+  hi = hi ^ ((hi >> 6) & 0x03FF03FFu) ^ ((hi >> 11) & 0x001F001Fu);
+  return ((uint64_t)hi << 32) | lo;
+#else
+  return b ^ ((b >> 6) & 0x03FF03FF03FF03FFULL) ^ ((b >> 11) & 0x001F001F001F001FULL);
+#endif
+}
+
 // How a 16-bit row is squashed: computed (host and device), or looked up in the 65,536-entry row-move
 // table the step kernel stages in shared memory (tfe.cu).  Both give squash_row_optimized's result; the
-// table is built from tfe_squash_row.
+// table is built from tfe_squash_row.  slots() maps a board's rows to what at() is indexed by.
 struct TfeComputedRows {
+  PULSE_HD uint64_t slots(uint64_t b) const { return b; }
+  PULSE_HD uint32_t at(uint32_t row, uint32_t& score) const { return tfe_squash_row(row, score); }
   PULSE_HD uint32_t operator()(uint32_t row, uint32_t& score) const { return tfe_squash_row(row, score); }
 };
 // score code of a row: the exponents of its (at most two) merged tiles, 4 bits each, 0 = none
@@ -134,13 +154,15 @@ PULSE_HD uint32_t tfe_score_code(uint32_t row) {
   return code;
 }
 struct TfeTableRows {
-  const uint16_t* result;  // [65536] squashed row
-  const uint8_t* code;     // [65536] tfe_score_code
-  PULSE_HD uint32_t operator()(uint32_t row, uint32_t& score) const {
-    const uint32_t c = code[row];
+  const uint16_t* result;  // [65536] squashed row, at tfe_row_slot(row)
+  const uint8_t* code;     // [65536] tfe_score_code, at tfe_row_slot(row)
+  PULSE_HD uint64_t slots(uint64_t b) const { return tfe_board_slots(b); }
+  PULSE_HD uint32_t at(uint32_t slot, uint32_t& score) const {
+    const uint32_t c = code[slot];
     score += ((1u << (c & 15u)) & ~1u) + ((1u << (c >> 4)) & ~1u);  // exponent 0 means "no merge": 1 & ~1 = 0
-    return result[row];
+    return result[slot];
   }
+  PULSE_HD uint32_t operator()(uint32_t row, uint32_t& score) const { return at(tfe_row_slot(row), score); }
 };
 
 // the move of TFE.step (:154-178); returns the new board, adds the step's score
@@ -149,10 +171,11 @@ PULSE_HD uint64_t tfe_move(uint64_t b, int action, uint32_t& score, const Rows& 
   const bool vertical = action & 1, toward_end = (action & 2) != 0;     // 1 up, 3 down; 2 right, 3 down
   if (vertical) b = tfe_transpose(b);
   if (toward_end) b = tfe_reverse_rows<SIDE>(b);
+  const uint64_t slots = rows.slots(b);
   uint64_t out = 0;
 #pragma unroll
   for (int r = 0; r < SIDE; ++r)
-    out |= (uint64_t)rows((uint32_t)(b >> (16 * r)) & 0xFFFFu, score) << (16 * r);
+    out |= (uint64_t)rows.at((uint32_t)(slots >> (16 * r)) & 0xFFFFu, score) << (16 * r);
   if (toward_end) out = tfe_reverse_rows<SIDE>(out);
   if (vertical) out = tfe_transpose(out);
   return out;
@@ -164,18 +187,19 @@ PULSE_HD uint64_t tfe_reset_board(PulseU4 c) {
   return tfe_add_tile<SIDE>(tfe_add_tile<SIDE>(0, c.x, c.y), c.z, c.w);
 }
 
-// One step of one board (:152-189).  auto_reset (batched-engine extension): a board that was game-over
-// when the step began is reset instead; that step returns reward 0, done 0.
+// One step of one board (:152-189) with the batched-engine reset folded in.  reset_now (auto_reset and the
+// board was game-over when the step began): the board is cleared first, so the move is a no-op scoring 0,
+// the spawn every step makes (c.x, c.y) is TFE.reset's first tile and a second spawn (c.z, c.w) is its
+// second (:143-149); that step returns reward 0, done 0.  One code path for both cases, so a warp holding
+// a finished board does not run a second instruction stream.
 template <int SIDE, class Rows>
-PULSE_HD uint64_t tfe_step_one(uint64_t b, int action, bool was_done, int auto_reset, PulseU4 spawn /*x,y*/,
-                               PulseU4 reset_c, int64_t& score_total, int32_t& reward, bool& done, const Rows& rows) {
-  if (auto_reset && was_done) {
-    score_total = 0; reward = 0; done = false;
-    return tfe_reset_board<SIDE>(reset_c);
-  }
+PULSE_HD uint64_t tfe_step_fused(uint64_t b, int action, bool reset_now, PulseU4 c, int64_t& score_total,
+                                 int32_t& reward, bool& done, const Rows& rows) {
+  if (reset_now) { b = 0; score_total = 0; }
   uint32_t score = 0;
   b = tfe_move<SIDE>(b, action & 3, score, rows);
-  b = tfe_add_tile<SIDE>(b, spawn.x, spawn.y);                          // :182 always
+  b = tfe_add_tile<SIDE>(b, c.x, c.y);                                  // :182 always
+  if (reset_now) b = tfe_add_tile<SIDE>(b, c.z, c.w);
   score_total += score;                                                 // :168
 #ifdef __CUDA_ARCH__
   reward = score ? 31 - __clz((int)score) : 0;                          // int(step_score).bit_length() - 1 (:185-187)
@@ -184,6 +208,14 @@ PULSE_HD uint64_t tfe_step_one(uint64_t b, int action, bool was_done, int auto_r
 #endif
   done = tfe_game_over<SIDE>(b);                                        // :189
   return b;
+}
+
+// the same with the two chance blocks handed in separately (spawn: x, y; reset: x, y, z, w)
+template <int SIDE, class Rows>
+PULSE_HD uint64_t tfe_step_one(uint64_t b, int action, bool was_done, int auto_reset, PulseU4 spawn /*x,y*/,
+                               PulseU4 reset_c, int64_t& score_total, int32_t& reward, bool& done, const Rows& rows) {
+  const bool reset_now = auto_reset && was_done;
+  return tfe_step_fused<SIDE>(b, action, reset_now, reset_now ? reset_c : spawn, score_total, reward, done, rows);
 }
 
 // packed exponents -> the reference's int32 tile values, row-major side x side

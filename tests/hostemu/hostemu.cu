@@ -170,7 +170,7 @@ int emu_tfe_reset(uint64_t* boards, int64_t* score, uint8_t* done, const uint32_
 int emu_tfe_table_check(void) {
   static uint16_t res[65536];
   static uint8_t code[65536];
-  for (uint32_t r = 0; r < 65536; ++r) { uint32_t sc = 0; res[r] = (uint16_t)tfe_squash_row(r, sc); code[r] = (uint8_t)tfe_score_code(r); }
+  for (uint32_t r = 0; r < 65536; ++r) { uint32_t sc = 0; res[tfe_row_slot(r)] = (uint16_t)tfe_squash_row(r, sc); code[tfe_row_slot(r)] = (uint8_t)tfe_score_code(r); }
   TfeTableRows t{res, code};
   int bad = 0;
   for (uint32_t r = 0; r < 65536; ++r) {
