@@ -63,23 +63,25 @@ __device__ __forceinline__ void stage_obs_rows(const float (&row)[WT], float4* s
 // of DRAM latency.  DRAM traffic is unchanged (every line is still fetched once); one instruction per thread.
 template <int MAXP>
 __device__ __forceinline__ void packed_prefetch_tile(const PulsePokerPacked& S, const int64_t* actions, int AP,
-                                                     long long base, long long n) {
+                                                     long long base, long long n, bool with_ev) {
   if (base >= n) return;
   const long long cnt = (n - base) < kBlock ? (n - base) : kBlock;
-  // line slots: 16 tbl, 8 tbl2, 8 actions, then per seat 4 stack + 4 crb + 4 inv + 2 hole
-  const int total = 32 + 14 * AP;
+  // line slots: 16 tbl, 8 tbl2, 8 actions, then per seat 4 stack + 4 crb + 4 inv + 2 hole (+ 8 hand-value words)
+  const int per_seat = with_ev ? 22 : 14;
+  const int total = 32 + per_seat * AP;
   for (int i = threadIdx.x; i < total; i += kBlock) {
     const char* p; long long bytes; int k;
     if (i < 16) { p = reinterpret_cast<const char*>(S.tbl + 4 * base); bytes = cnt * 16; k = i; }
     else if (i < 24) { p = reinterpret_cast<const char*>(S.tbl2 + 2 * base); bytes = cnt * 8; k = i - 16; }
     else if (i < 32) { p = reinterpret_cast<const char*>(actions + base); bytes = actions ? cnt * 8 : 0; k = i - 24; }
     else {
-      const int s = (i - 32) / 14, j = (i - 32) - 14 * s;
+      const int s = (i - 32) / per_seat, j = (i - 32) - per_seat * s;
       const long long o = (long long)s * n + base;
       if (j < 4) { p = reinterpret_cast<const char*>(S.stack + o); bytes = cnt * 4; k = j; }
       else if (j < 8) { p = reinterpret_cast<const char*>(S.crb + o); bytes = cnt * 4; k = j - 4; }
       else if (j < 12) { p = reinterpret_cast<const char*>(S.inv + o); bytes = cnt * 4; k = j - 8; }
-      else { p = reinterpret_cast<const char*>(S.hole + o); bytes = cnt * 2; k = j - 12; }
+      else if (j < 14) { p = reinterpret_cast<const char*>(S.hole + o); bytes = cnt * 2; k = j - 12; }
+      else { p = reinterpret_cast<const char*>(S.ev + o); bytes = cnt * 8; k = j - 14; }
     }
     if ((long long)k * 128 < bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + k * 128));
   }
@@ -93,8 +95,9 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
                          int starting_bbs, int max_bbs, long long n, int l2_ahead,
                          PackedPolicy pol = PackedPolicy()) {
   extern __shared__ float4 smem4[];
-  if (l2_ahead > 0)
-    packed_prefetch_tile<MAXP>(S, actions, pr.AP, ((long long)blockIdx.x + l2_ahead) * kBlock, n);
+  if (l2_ahead > 0)  // bit 30 of l2_ahead: include the hand-value words
+    packed_prefetch_tile<MAXP>(S, actions, pr.AP, ((long long)blockIdx.x + (l2_ahead & 0xFFFFF)) * kBlock, n,
+                               (l2_ahead >> 30) & 1);
   if (MT > 0) pr.M = MT;
   constexpr int WT = MT > 0 ? 13 + 3 * (MT - 1) : 13 + 3 * 15;  // row buffer size
   const int W = 13 + 3 * (pr.M - 1);
@@ -217,9 +220,17 @@ PokerParams make_params(const PulsePokerConfig* c) {
 
 // how many CTAs ahead the step kernel prefetches into L2: one resident wave (148 SMs x resident CTAs per SM);
 // PULSE_POKER_L2_AHEAD overrides (0 turns the prefetch off) for experiments
-static int l2_ahead_for(int minb) {
+static int l2_ahead_for(int minb, int max_players) {
   static const int env = getenv("PULSE_POKER_L2_AHEAD") ? atoi(getenv("PULSE_POKER_L2_AHEAD")) : -1;
-  return env >= 0 ? env : 148 * minb;
+  static const int env_ev = getenv("PULSE_POKER_L2_EV") ? atoi(getenv("PULSE_POKER_L2_EV")) : -1;
+  // measured on B200 (profiles/r1r_l2_ahead.md): two CTAs per SM ahead heads-up, one with more seats; further ahead
+  // the streamed observation writes push the prefetched lines out of L2 again before they are used
+  const int ahead = env >= 0 ? env : (max_players <= 2 ? 296 : 148);
+  (void)minb;
+  // heads-up reads both seats' hand-value words with the rest of the table, so they belong to the prefetch set;
+  // with more seats only the actor's (or the showdown's) words are read
+  const int ev = env_ev >= 0 ? env_ev : (max_players <= 2);
+  return ahead > 0 ? (ahead | (ev ? 1 << 30 : 0)) : 0;
 }
 
 static int launch_redeal(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const PokerParams& pr, uint64_t seed,
@@ -284,7 +295,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #define PKP_STEP_A(MP, MT, MINB, AUTO, SMEM)                                                              \
   poker_packed_step_kernel<MP, MT, MINB, false, AUTO><<<grid, kBlock, SMEM, stream>>>(                     \
       *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
-      (long long)cfg->n_games, l2_ahead_for(MINB))
+      (long long)cfg->n_games, l2_ahead_for(MINB, MP))
 #define PKP_STEP_B(MP, MT, MINB, SMEM)                       \
   do {                                                       \
     if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);       \
@@ -347,7 +358,7 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
 #define PKP_POL_A(MP, MT, MINB, AUTO, SMEM)                                                                \
   poker_packed_step_kernel<MP, MT, MINB, true, AUTO><<<grid, kBlock, SMEM, stream>>>(                       \
       *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,      \
-      cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB), pol)
+      cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB, MP), pol)
 #define PKP_POL(MP, MT, MINB, SMEM)                          \
   do {                                                       \
     if (auto_reset) PKP_POL_A(MP, MT, MINB, 2, SMEM);        \

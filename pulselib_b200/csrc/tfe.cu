@@ -4,6 +4,7 @@
 // coalesced stores.  HBM-bound (106 B per board-step with the int32 observation, 42 B
 // without).
 #include "tfe_body.cuh"
+#include <stdlib.h>
 
 namespace {
 constexpr int kBlock = 256;
@@ -57,24 +58,35 @@ __device__ __forceinline__ uint64_t tfe_lut_swizzle_board(uint64_t b) {
 
 template <int SIDE>
 __device__ __forceinline__ void tfe_warp_write_obs(const uint64_t* __restrict__ wboards, const uint2* __restrict__ lut,
-                                                   const long long wb, const long long n, int32_t* __restrict__ obs_out) {
+                                                   const uint32_t wb, const uint32_t n, int32_t* __restrict__ obs_out) {
   const int lane = threadIdx.x & 31;
-  const int rows = (int)((n - wb) < 32 ? (n - wb) : 32);
+  const int rows = (int)((n - wb) < 32u ? (n - wb) : 32u);
   constexpr int W = SIDE * SIDE;
   if (SIDE == 4) {
-    int4* dst = reinterpret_cast<int4*>(obs_out + wb * W);
+    // int4 index q = board * 4 + board row, and the staged boards are little-endian, so 16-bit word q of the
+    // staging slot IS that row: one conflict-free LDS.U16, then one LUT read per byte (two cells each) --
+    // LSU-pipe work instead of twelve shift/mask ops on the ALU pipe
+    const uint16_t* wrows = reinterpret_cast<const uint16_t*>(wboards);
+    int4* dst = reinterpret_cast<int4*>(obs_out + (size_t)wb * W) + lane;
+    if (rows == 32) {                                               // full warp (all but the last): no bounds checks
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {
-      const int q = it * 32 + lane;                               // int4 index = board * 4 + board row
-      if (q < rows * 4) {
-        // one board row = two bytes = two LUT reads (LSU pipe) instead of twelve shift/mask ops (ALU pipe)
-        const uint32_t r16 = (uint32_t)(wboards[q >> 2] >> (16 * (q & 3)));
-        const uint2 a = lut[r16 & 0xFFu], b = lut[__byte_perm(r16, 0, 0x4441)];
-        dst[q] = make_int4((int)a.x, (int)a.y, (int)b.x, (int)b.y);
+      for (int it = 0; it < 4; ++it) {
+        const uint32_t r16 = wrows[it * 32 + lane];
+        const uint2 a = lut[r16 & 0xFFu], b = lut[r16 >> 8];
+        dst[it * 32] = make_int4((int)a.x, (int)a.y, (int)b.x, (int)b.y);
+      }
+    } else {
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        if (it * 32 + lane < rows * 4) {
+          const uint32_t r16 = wrows[it * 32 + lane];
+          const uint2 a = lut[r16 & 0xFFu], b = lut[r16 >> 8];
+          dst[it * 32] = make_int4((int)a.x, (int)a.y, (int)b.x, (int)b.y);
+        }
       }
     }
   } else {
-    int32_t* dst = obs_out + wb * W;
+    int32_t* dst = obs_out + (size_t)wb * W;
 #pragma unroll
     for (int it = 0; it < W; ++it) {
       const int q = it * 32 + lane;
@@ -93,15 +105,11 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
                 const uint4* __restrict__ reset_chance, const uint4* __restrict__ table, uint64_t seed,
                 uint64_t env_base, uint32_t counter, uint32_t* counter_dev, int auto_reset,
                 int32_t* __restrict__ obs_out, int32_t* __restrict__ reward_out, uint8_t* done_out,
-                int64_t* __restrict__ score, long long n) {
+                int64_t* __restrict__ score, uint32_t n) {
+  // board indices are 32-bit (n_envs is an int in the ABI; g + stride stays below 2^32): one IMAD.WIDE per address
   extern __shared__ uint4 smem_raw[];
-  const uint32_t dev_ctr = pulse_counter_read(counter_dev);
-  counter += dev_ctr;
-  const long long stride = (long long)gridDim.x * kStepBlock;
-  long long g = (long long)blockIdx.x * kStepBlock + threadIdx.x;
-  // first board's inputs are requested before the table copy so their latency hides behind it
-  uint64_t b = 0; int64_t total = 0; int a = 0; bool was_done = false;
-  if (g < n) { b = boards[g]; total = score[g]; a = (int)actions[g]; was_done = auto_reset && done_out[g]; }
+  // ---- prologue: independent of every earlier kernel on the stream (the table was built and synchronised at
+  // init), so under programmatic dependent launch it overlaps the previous kernel's tail ----
   // table -> shared memory by TMA bulk copies (12 x 16 KB), issued by one thread, landing on an mbarrier
   __shared__ uint64_t table_bar;
   if (threadIdx.x == 0) pulse_mbar_init(&table_bar, 1);
@@ -114,6 +122,16 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
       pulse_bulk_g2s(reinterpret_cast<uint8_t*>(smem_raw) + off, reinterpret_cast<const uint8_t*>(table) + off, kChunk,
                      &table_bar);
   }
+  // ---- everything below reads or writes what earlier kernels may have written ----
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const uint32_t dev_ctr = pulse_counter_read(counter_dev);
+  counter += dev_ctr;
+  const uint32_t stride = gridDim.x * kStepBlock;
+  uint32_t g = blockIdx.x * kStepBlock + threadIdx.x;
+  // first board's inputs are in flight while the table copy lands
+  uint64_t b = 0; int64_t total = 0; int a = 0; bool was_done = false;
+  if (g < n) { b = boards[g]; total = score[g]; a = (int)actions[g]; was_done = auto_reset && done_out[g]; }
   bool table_ready = false;
   TfeTableRows rows;
   rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
@@ -123,10 +141,10 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   if (threadIdx.x < 256)
     lut[tfe_lut_slot(threadIdx.x)] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
   __syncthreads();
-  const int lane = threadIdx.x & 31;
+  const uint32_t lane = threadIdx.x & 31;
   for (; g - lane < n; g += stride) {                              // warp-uniform trip count
     const bool valid = g < n;
-    const long long gn = g + stride;
+    const uint32_t gn = g + stride;
     uint64_t nb_in = 0; int64_t ntotal = 0; int na = 0; bool ndone = false;
     if (gn < n) { nb_in = boards[gn]; ntotal = score[gn]; na = (int)actions[gn]; ndone = auto_reset && done_out[gn]; }
     uint64_t nb = 0;
@@ -294,15 +312,27 @@ int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, cons
   if (rc) return rc;
   const long long need = ((long long)n_envs + kStepBlock - 1) / kStepBlock;
   const int grid = (int)(need < 148 ? need : 148);  // one persistent CTA per SM
+  // Programmatic dependent launch: the kernel's prologue (table copy into shared memory, LUT) touches nothing an
+  // earlier kernel on the stream writes, so it may start while that kernel drains; everything else sits behind
+  // griddepcontrol.wait in the kernel.  PULSE_PDL=0 launches plainly.
+  static const bool pdl = !(getenv("PULSE_PDL") && atoi(getenv("PULSE_PDL")) == 0);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3((unsigned)grid); lc.blockDim = dim3(kStepBlock); lc.dynamicSmemBytes = kStepSmem; lc.stream = stream;
+  lc.attrs = attr; lc.numAttrs = pdl ? 1 : 0;
+  cudaError_t le = cudaSuccess;
 #define TFE_STEP(ACT)                                                                                          \
-  TFE_SIDE_DISPATCH(side, (tfe_step_kernel<SD, ACT><<<grid, kStepBlock, kStepSmem, stream>>>(                  \
+  TFE_SIDE_DISPATCH(side, (le = cudaLaunchKernelEx(&lc, tfe_step_kernel<SD, ACT>,                              \
                               boards, (const ACT*)actions, (const uint2*)chance2_or_null,                      \
                               (const uint4*)reset_chance4_or_null, table, seed, env_base, counter,             \
                               counter_dev_or_null, auto_reset, obs_out_or_null, reward_out, done_inout,        \
-                              score_inout, (long long)n_envs)))
+                              score_inout, (uint32_t)n_envs)))
   if (action_bytes == 1) TFE_STEP(uint8_t);
   else TFE_STEP(int64_t);
 #undef TFE_STEP
+  if (le != cudaSuccess) { pulse_set_error("pulse_tfe_step launch: %s", cudaGetErrorString(le)); return (int)le; }
   return pulse_check_launch("pulse_tfe_step");
 }
 

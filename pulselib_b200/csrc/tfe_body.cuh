@@ -158,8 +158,10 @@ struct TfeTableRows {
   const uint8_t* code;     // [65536] tfe_score_code, at tfe_row_slot(row)
   PULSE_HD uint64_t slots(uint64_t b) const { return tfe_board_slots(b); }
   PULSE_HD uint32_t at(uint32_t slot, uint32_t& score) const {
+    // exponent 0 means "no merge" and a merged tile is at least 4, so the stray 1 << 0 terms (at most 1 + 1)
+    // fall in the two low bits
     const uint32_t c = code[slot];
-    score += ((1u << (c & 15u)) & ~1u) + ((1u << (c >> 4)) & ~1u);  // exponent 0 means "no merge": 1 & ~1 = 0
+    score += ((1u << (c & 15u)) + (1u << (c >> 4))) & ~3u;
     return result[slot];
   }
   PULSE_HD uint32_t operator()(uint32_t row, uint32_t& score) const { return at(tfe_row_slot(row), score); }
