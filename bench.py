@@ -7,7 +7,7 @@ A "step" is one `env.step(actions)` over the whole batch.  Hands follow the refe
 (scripts/Poker/trainGPU.py:79-108): whole-batch reset, then HAND_LEN steps, every table counted at
 every step; the reset launches sit inside the timed region.  One JSON line is printed by rank 0.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload poker_hu|poker_6max]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload poker_hu|poker_6max|poker_10max|...]
 """
 from __future__ import annotations
 
@@ -29,6 +29,8 @@ CFG = dict(starting_bbs=100, max_bbs=1000, w1=.5, w2=.3, K=100, alpha=50)  # con
 WORKLOADS = {
     "poker_hu": dict(n_players=2, max_players=2, tables=4_194_304, algo_bytes=201, hand_len=16),
     "poker_6max": dict(n_players=6, max_players=6, tables=4_194_304, algo_bytes=401, hand_len=24),
+    # the reference's own training default (PokerGPU.py:20, scripts/Poker/trainGPU.py:177-188)
+    "poker_10max": dict(n_players=10, max_players=10, tables=4_194_304, algo_bytes=601, hand_len=32),
 }
 
 

@@ -314,8 +314,19 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
   if (pr.P <= 2 && pr.M == 2 && aligned) PKP_STEP(2, 2, PKP_SMEM4(2));
-  else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) PKP_STEP(6, 6, PKP_SMEM4(6));
-  else if (pr.P > 6 && pr.M == 10 && aligned) PKP_STEP(10, 10, PKP_SMEM4(10));
+  else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) {
+    if (minb_env == 5) PKP_STEP_B(6, 6, 5, PKP_SMEM4(6));
+    else if (minb_env == 6) PKP_STEP_B(6, 6, 6, PKP_SMEM4(6));
+    else PKP_STEP(6, 6, PKP_SMEM4(6));
+  }
+  else if (pr.P > 6 && pr.M == 10 && aligned) {
+    // ten seats: the table does not fit 64 registers (320 B of spill at 8 CTAs/SM); fewer, fatter CTAs win:
+    // 5 CTAs/SM (96 registers) measured 0.62 of HBM against 0.49 at 8 and 0.36 at 10 (profiles/r1r_exp5_minb_lines.jsonl)
+    if (minb_env == 3) PKP_STEP_B(10, 10, 3, PKP_SMEM4(10));
+    else if (minb_env == 4) PKP_STEP_B(10, 10, 4, PKP_SMEM4(10));
+    else if (minb_env >= 8) PKP_STEP(10, 10, PKP_SMEM4(10));
+    else PKP_STEP_B(10, 10, 5, PKP_SMEM4(10));
+  }
   else {
     const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
     PKP_DISPATCH(pr.P, PKP_STEP(MP, 0, smem));
