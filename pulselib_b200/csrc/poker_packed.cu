@@ -60,30 +60,37 @@ __device__ __forceinline__ void stage_obs_rows(const float (&row)[WT], float4* s
 // bound by how many loads a resident thread set can keep in flight.  Each CTA therefore asks L2 (prefetch.global.L2:
 // no register, no scoreboard) for the state lines of the tile `ahead` CTAs further on -- about one resident
 // wave, i.e. the tile that takes this CTA's slot when it retires -- so that tile's loads meet L2 latency instead
-// of DRAM latency.  DRAM traffic is unchanged (every line is still fetched once); one instruction per thread.
+// of DRAM latency.  DRAM traffic is unchanged (every line is still fetched once).
+// Issued by the CTA's first warp only (the other three skip it with one uniform branch; spreading the lines over all
+// 128 threads cost 85 instructions per warp in divergent address selection, 6.6% of an issue-bound kernel):
+// one prefetch covers tbl (lanes 0-15), tbl2 (16-23) and the actions (24-31); then one prefetch per seat covers
+// that seat's stack / crb / inv (4 lines each), hole (2) and, when asked, hand-value words (8) -- the lane's array,
+// element size and line are chosen once, outside the seat loop.
 template <int MAXP>
 __device__ __forceinline__ void packed_prefetch_tile(const PulsePokerPacked& S, const int64_t* actions, int AP,
                                                      long long base, long long n, bool with_ev) {
-  if (base >= n) return;
+  if (threadIdx.x >= 32 || base >= n) return;
+  const int lane = threadIdx.x;
   const long long cnt = (n - base) < kBlock ? (n - base) : kBlock;
-  // line slots: 16 tbl, 8 tbl2, 8 actions, then per seat 4 stack + 4 crb + 4 inv + 2 hole (+ 8 hand-value words)
-  const int per_seat = with_ev ? 22 : 14;
-  const int total = 32 + per_seat * AP;
-  for (int i = threadIdx.x; i < total; i += kBlock) {
-    const char* p; long long bytes; int k;
-    if (i < 16) { p = reinterpret_cast<const char*>(S.tbl + 4 * base); bytes = cnt * 16; k = i; }
-    else if (i < 24) { p = reinterpret_cast<const char*>(S.tbl2 + 2 * base); bytes = cnt * 8; k = i - 16; }
-    else if (i < 32) { p = reinterpret_cast<const char*>(actions + base); bytes = actions ? cnt * 8 : 0; k = i - 24; }
-    else {
-      const int s = (i - 32) / per_seat, j = (i - 32) - per_seat * s;
-      const long long o = (long long)s * n + base;
-      if (j < 4) { p = reinterpret_cast<const char*>(S.stack + o); bytes = cnt * 4; k = j; }
-      else if (j < 8) { p = reinterpret_cast<const char*>(S.crb + o); bytes = cnt * 4; k = j - 4; }
-      else if (j < 12) { p = reinterpret_cast<const char*>(S.inv + o); bytes = cnt * 4; k = j - 8; }
-      else if (j < 14) { p = reinterpret_cast<const char*>(S.hole + o); bytes = cnt * 2; k = j - 12; }
-      else { p = reinterpret_cast<const char*>(S.ev + o); bytes = cnt * 8; k = j - 14; }
-    }
-    if ((long long)k * 128 < bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + k * 128));
+  {
+    const char* p; int esz, k;
+    if (lane < 16) { p = reinterpret_cast<const char*>(S.tbl + 4 * base); esz = 16; k = lane; }
+    else if (lane < 24) { p = reinterpret_cast<const char*>(S.tbl2 + 2 * base); esz = 8; k = lane - 16; }
+    else { p = reinterpret_cast<const char*>(actions + base); esz = actions ? 8 : 0; k = lane - 24; }
+    if ((long long)k * 128 < cnt * esz) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + k * 128));
+  }
+  const char* arr; int esz, k;
+  if (lane < 4) { arr = reinterpret_cast<const char*>(S.stack); esz = 4; k = lane; }
+  else if (lane < 8) { arr = reinterpret_cast<const char*>(S.crb); esz = 4; k = lane - 4; }
+  else if (lane < 12) { arr = reinterpret_cast<const char*>(S.inv); esz = 4; k = lane - 8; }
+  else if (lane < 14) { arr = reinterpret_cast<const char*>(S.hole); esz = 2; k = lane - 12; }
+  else { arr = reinterpret_cast<const char*>(S.ev); esz = 8; k = lane - 14; }
+  if (lane < (with_ev ? 22 : 14) && (long long)k * 128 < cnt * esz) {
+    arr += base * esz + k * 128;
+    const long long seat_stride = n * esz;
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s)
+      if (s < AP) asm volatile("prefetch.global.L2 [%0];" ::"l"(arr + s * seat_stride));
   }
 }
 
@@ -301,8 +308,9 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
     if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);       \
     else PKP_STEP_A(MP, MT, MINB, 0, SMEM);                  \
   } while (0)
-  // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 8 (64) otherwise --
-  // measured on B200 (profiles/r1c_poker_launch_bounds.md); PULSE_POKER_MINB overrides for experiments
+  // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 6 / 4 for the six- / ten-seat
+  // builds (below), 8 (64) for the generic ones -- measured on B200 (profiles/r1c_poker_launch_bounds.md, r1r_exp5/6);
+  // PULSE_POKER_MINB overrides for experiments
   static const int minb_env = getenv("PULSE_POKER_MINB") ? atoi(getenv("PULSE_POKER_MINB")) : 0;
 #define PKP_STEP(MP, MT, SMEM)                                    \
   do {                                                            \
@@ -314,18 +322,20 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
   if (pr.P <= 2 && pr.M == 2 && aligned) PKP_STEP(2, 2, PKP_SMEM4(2));
+  // More seats: the table no longer fits the 64 registers of 8 CTAs/SM, and with the L2 look-ahead hiding most of the
+  // load latency, fewer and fatter CTAs win.  Measured on B200 (profiles/r1r_exp5_minb_lines.jsonl, r1r_exp6_...):
+  //   six seats: 6 CTAs/SM (80 registers) 0.83 of HBM, 8 (64) 0.80, 5 (96) 0.80, 10 (48) 0.65, 12 (40) 0.54
+  //   ten seats: 4 CTAs/SM (128 registers) 0.67, 5 (96) 0.62, 3 (160) 0.59, 8 (64, 320 B spill) 0.49, 10 (48) 0.36
   else if (pr.P > 4 && pr.P <= 6 && pr.M == 6 && aligned) {
     if (minb_env == 5) PKP_STEP_B(6, 6, 5, PKP_SMEM4(6));
-    else if (minb_env == 6) PKP_STEP_B(6, 6, 6, PKP_SMEM4(6));
-    else PKP_STEP(6, 6, PKP_SMEM4(6));
+    else if (minb_env >= 8) PKP_STEP(6, 6, PKP_SMEM4(6));
+    else PKP_STEP_B(6, 6, 6, PKP_SMEM4(6));
   }
   else if (pr.P > 6 && pr.M == 10 && aligned) {
-    // ten seats: the table does not fit 64 registers (320 B of spill at 8 CTAs/SM); fewer, fatter CTAs win:
-    // 5 CTAs/SM (96 registers) measured 0.62 of HBM against 0.49 at 8 and 0.36 at 10 (profiles/r1r_exp5_minb_lines.jsonl)
     if (minb_env == 3) PKP_STEP_B(10, 10, 3, PKP_SMEM4(10));
-    else if (minb_env == 4) PKP_STEP_B(10, 10, 4, PKP_SMEM4(10));
+    else if (minb_env == 5) PKP_STEP_B(10, 10, 5, PKP_SMEM4(10));
     else if (minb_env >= 8) PKP_STEP(10, 10, PKP_SMEM4(10));
-    else PKP_STEP_B(10, 10, 5, PKP_SMEM4(10));
+    else PKP_STEP_B(10, 10, 4, PKP_SMEM4(10));
   }
   else {
     const size_t smem = (size_t)kBlock * (W + 1) * sizeof(float);
