@@ -16,7 +16,7 @@ echo "smoke exit $?" >> $OUT/${TAG}_smoke.log
 
 : > $OUT/${TAG}_bench_lines.jsonl
 timeout 600 python bench.py >> $OUT/${TAG}_bench_lines.jsonl 2> $OUT/${TAG}_bench_default.err
-for w in poker_6max tfe_4x4 tetris particle2d blackjack poker_hu_scripted poker_hu_train_loop; do
+for w in poker_6max poker_10max tfe_4x4 tetris particle2d blackjack poker_hu_scripted poker_hu_train_loop; do
   timeout 400 python bench.py --workload $w --steps 512 --warmup 16 >> $OUT/${TAG}_bench_lines.jsonl 2> $OUT/${TAG}_bench_$w.err
 done
 timeout 400 python bench.py --impl reference --steps 8 --warmup 3 >> $OUT/${TAG}_bench_lines.jsonl 2> $OUT/${TAG}_bench_ref.err

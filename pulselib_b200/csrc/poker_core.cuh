@@ -172,7 +172,11 @@ PULSE_HD void pk_advance(PokerTable<MAXP>& t, const PokerParams& pr, const Deck&
     t.last_raise = 1;                                      // :581
     t.stage += 1;                                          // :584
     t.highest = 0;                                         // :585
-    t.agg = t.button + 1 < AP ? t.button + 1 : (t.button + 1) % AP;  // :586
+    {  // (button + 1) % AP (:586) without the division: button is a seat in [0, AP) on every path that deals
+      int b1 = t.button + 1;
+      if (b1 >= AP) { b1 -= AP; if (b1 >= AP) b1 %= AP; }  // second branch: hand-written states only
+      t.agg = b1;
+    }
     t.acted = 0;                                           // :587
 #pragma unroll
     for (int s = 0; s < MAXP; ++s) t.crb[s] = 0;           // :588

@@ -85,7 +85,7 @@ __device__ __forceinline__ void packed_prefetch_tile(const PulsePokerPacked& S, 
   else if (lane < 12) { arr = reinterpret_cast<const char*>(S.inv); esz = 4; k = lane - 8; }
   else if (lane < 14) { arr = reinterpret_cast<const char*>(S.hole); esz = 2; k = lane - 12; }
   else { arr = reinterpret_cast<const char*>(S.ev); esz = 8; k = lane - 14; }
-  if (lane < (with_ev ? 22 : 14) && (long long)k * 128 < cnt * esz) {
+  if (lane < (with_ev && S.ev ? 22 : 14) && (long long)k * 128 < cnt * esz) {
     arr += base * esz + k * 128;
     const long long seat_stride = n * esz;
 #pragma unroll
@@ -163,11 +163,26 @@ poker_packed_redeal_kernel(PulsePokerPacked S, PokerParams pr, uint64_t seed, ui
   for (long long base = (long long)blockIdx.x * kRedealTile; base < n; base += (long long)gridDim.x * kRedealTile) {
     if (threadIdx.x == 0) count = 0;
     __syncthreads();
+    // all eight counter words are requested before any is looked at (as one load-test-append per iteration the
+    // loads went out one DRAM round trip after another: two thirds of the kernel's stall samples, r1r capture);
+    // a warp appends its marked tables with one shared atomic
+    uint32_t ctr[kRedealTile / kBlock];
 #pragma unroll
     for (int k = 0; k < kRedealTile / kBlock; ++k) {
-      const int local = k * kBlock + threadIdx.x;
-      const long long g = base + local;
-      if (g < n && (S.hand_ctr[g] & PKP_REDEAL_MARK)) list[atomicAdd(&count, 1)] = local;
+      const long long g = base + k * kBlock + threadIdx.x;
+      ctr[k] = g < n ? S.hand_ctr[g] : 0u;
+    }
+    const unsigned lane = threadIdx.x & 31u;
+#pragma unroll
+    for (int k = 0; k < kRedealTile / kBlock; ++k) {
+      const bool marked = (ctr[k] & PKP_REDEAL_MARK) != 0;
+      const unsigned bal = __ballot_sync(0xFFFFFFFFu, marked);
+      if (bal) {
+        int pos = 0;
+        if (lane == 0) pos = atomicAdd(&count, __popc(bal));
+        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+        if (marked) list[pos + __popc(bal & ((1u << lane) - 1u))] = k * kBlock + (int)threadIdx.x;
+      }
     }
     __syncthreads();
     const int cnt = count;
