@@ -180,6 +180,20 @@ int emu_tfe_table_check(void) {
   }
   return bad;
 }
+// tfe_board_slots (the four rows of a board hashed at once) against tfe_row_slot row by row, and tfe_row_slot
+// as a bijection on 16 bits; returns the number of disagreements
+int emu_tfe_slot_check(const uint64_t* boards, int n) {
+  int bad = 0;
+  for (int i = 0; i < n; ++i) {
+    const uint64_t s = tfe_board_slots(boards[i]);
+    for (int r = 0; r < 4; ++r)
+      bad += (uint32_t)((s >> (16 * r)) & 0xFFFFu) != tfe_row_slot((uint32_t)((boards[i] >> (16 * r)) & 0xFFFFu));
+  }
+  static uint8_t seen[65536];
+  for (uint32_t r = 0; r < 65536; ++r) seen[r] = 0;
+  for (uint32_t r = 0; r < 65536; ++r) { const uint32_t t = tfe_row_slot(r); bad += t > 0xFFFFu || seen[t]; seen[t & 0xFFFFu] = 1; }
+  return bad;
+}
 int emu_tfe_pack(const int32_t* values, uint64_t* boards, int n, int side) {
   int bad = 0;
   for (long long g = 0; g < n; ++g) {

@@ -93,6 +93,21 @@ def test_tfe_body_matches_oracle_autoreset(side):
     assert resets > N // 2
 
 
+def test_tfe_row_table_and_slots():
+    """The staged row-move table (built at hashed slots, read through TfeTableRows) against the computed squash on
+    all 65,536 rows; the board-wide slot hash against the per-row one; the slot map is a bijection."""
+    import ctypes as C
+
+    from tests.hostemu import emu
+
+    L = emu.lib()
+    assert L.emu_tfe_table_check() == 0
+    rng = np.random.default_rng(3)
+    boards = rng.integers(0, 2**64, 1 << 16, dtype=np.uint64)
+    L.emu_tfe_slot_check.argtypes = [C.c_void_p, C.c_int]
+    assert L.emu_tfe_slot_check(boards.ctypes.data_as(C.c_void_p), C.c_int(len(boards))) == 0
+
+
 def test_tfe_body_large_tiles():
     """Hand-built boards with big tiles (random play never gets there): every move, both engines."""
     rng = np.random.default_rng(0)
