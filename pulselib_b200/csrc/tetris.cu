@@ -44,7 +44,17 @@ __device__ __forceinline__ void slab_store(uint32_t* __restrict__ g, const uint3
   }
 }
 
-struct TetScalars { int pc, nx, rp; int32_t ln; bool dn; long long a; };
+// Per-env scalars of a slab, as loaded: byte fields stay raw 32-bit registers (ld.global.u8 zero-extends, nothing is
+// masked, tested or widened here) so that no instruction consumes a prefetched value before the iteration that
+// uses it -- a `done[g] != 0` or `& 0xff` right behind the load parks the warp on the DRAM round trip the
+// prefetch exists to hide.
+struct TetScalars { uint32_t pc, dn, a8; int nx, rp; int32_t ln; long long a64; };
+
+__device__ __forceinline__ uint32_t tet_ld_u8(const uint8_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
 
 template <typename ActT>
 __device__ __forceinline__ TetScalars tet_load_scalars(const uint8_t* __restrict__ piece, const int32_t* __restrict__ lines,
@@ -52,9 +62,11 @@ __device__ __forceinline__ TetScalars tet_load_scalars(const uint8_t* __restrict
                                                        const uint8_t* __restrict__ next_piece,
                                                        const uint8_t* __restrict__ reset_piece, long long g, bool valid) {
   TetScalars s;
-  s.pc = 0; s.nx = -1; s.rp = -1; s.ln = 0; s.dn = false; s.a = 0;
+  s.pc = 0; s.nx = -1; s.rp = -1; s.ln = 0; s.dn = 0; s.a8 = 0; s.a64 = 0;
   if (valid) {
-    s.pc = piece[g]; s.ln = lines[g]; s.dn = done[g]; s.a = (long long)actions[g];
+    s.pc = tet_ld_u8(piece + g); s.ln = lines[g]; s.dn = tet_ld_u8(done + g);
+    if (sizeof(ActT) == 1) s.a8 = tet_ld_u8(reinterpret_cast<const uint8_t*>(actions) + g);
+    else s.a64 = (long long)actions[g];
     if (next_piece) s.nx = next_piece[g];
     if (reset_piece) s.rp = reset_piece[g];
   }
@@ -113,13 +125,16 @@ tetris_step_kernel(uint16_t* __restrict__ rows, uint8_t* __restrict__ piece, int
     }
     __syncthreads();                                   // slab[buf] complete (and shapes, first time round)
     if (valid) {
-      int pc = cur.pc; int32_t ln = cur.ln; bool dn = cur.dn;
+      const int pc0 = (int)(cur.pc & 0xFFu);
+      const bool dn0 = (cur.dn & 0xFFu) != 0;
+      const long long act = sizeof(ActT) == 1 ? (long long)(cur.a8 & 0xFFu) : cur.a64;
+      int pc = pc0; int32_t ln = cur.ln; bool dn = dn0;
       int32_t reward;
-      tet_step_one(reinterpret_cast<uint16_t*>(slab[buf]) + threadIdx.x * TET_H, shapes, pc, ln, dn, cur.a, nx, rp,
+      tet_step_one(reinterpret_cast<uint16_t*>(slab[buf]) + threadIdx.x * TET_H, shapes, pc, ln, dn, act, nx, rp,
                    auto_reset, reward);
-      if (pc != cur.pc) piece[g] = (uint8_t)pc;
+      if (pc != pc0) piece[g] = (uint8_t)pc;
       if (ln != cur.ln) lines[g] = ln;
-      if (dn != cur.dn) done[g] = dn;
+      if (dn != dn0) done[g] = dn;
       reward_out[g] = reward;
     }
     __syncthreads();                                   // every thread's rows are final

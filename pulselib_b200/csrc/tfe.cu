@@ -130,8 +130,10 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   const uint32_t stride = gridDim.x * kStepBlock;
   uint32_t g = blockIdx.x * kStepBlock + threadIdx.x;
   // first board's inputs are in flight while the table copy lands
-  uint64_t b = 0; int64_t total = 0; int a = 0; bool was_done = false;
-  if (g < n) { b = boards[g]; total = score[g]; a = (int)actions[g]; was_done = auto_reset && done_out[g]; }
+  // done flags are carried as the raw byte and only tested where they are used: testing one right after its load
+  // (as `auto_reset && done_out[gn]` did) parks the warp on the DRAM round trip the prefetch exists to hide
+  uint64_t b = 0; int64_t total = 0; int a = 0; uint32_t done_raw = 0;
+  if (g < n) { b = boards[g]; total = score[g]; a = (int)actions[g]; done_raw = done_out[g]; }
   bool table_ready = false;
   TfeTableRows rows;
   rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
@@ -145,10 +147,11 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   for (; g - lane < n; g += stride) {                              // warp-uniform trip count
     const bool valid = g < n;
     const uint32_t gn = g + stride;
-    uint64_t nb_in = 0; int64_t ntotal = 0; int na = 0; bool ndone = false;
-    if (gn < n) { nb_in = boards[gn]; ntotal = score[gn]; na = (int)actions[gn]; ndone = auto_reset && done_out[gn]; }
+    uint64_t nb_in = 0; int64_t ntotal = 0; int na = 0; uint32_t ndone_raw = 0;
+    if (gn < n) { nb_in = boards[gn]; ntotal = score[gn]; na = (int)actions[gn]; ndone_raw = done_out[gn]; }
     uint64_t nb = 0;
     if (valid) {
+      const bool was_done = auto_reset && done_raw != 0;
       // one chance block per board-step: the reset stream for a board being re-dealt, the spawn stream
       // otherwise -- a single Philox call either way (no second instruction stream for finished boards)
       PulseU4 c;
@@ -175,7 +178,7 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
       tfe_warp_write_obs<SIDE>(wboards, lut, g - lane, n, obs_out);
       __syncwarp();
     }
-    b = nb_in; total = ntotal; a = na; was_done = ndone;
+    b = nb_in; total = ntotal; a = na; done_raw = ndone_raw;
   }
   pulse_counter_advance(counter_dev, dev_ctr);
 }
