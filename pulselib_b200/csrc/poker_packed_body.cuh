@@ -79,11 +79,73 @@ PULSE_HD void pkp_st2(uint32_t* p, uint32_t x, uint32_t y) {
 #endif
 }
 
+// Ordered loads of the step's first-level words.  ptxas schedules for the longest dependency chain (table word ->
+// actor seat -> that seat's hand-value word), so with ordinary loads it put the first consumer of the table word
+// ahead of most per-seat loads: the warp waited for the table word, then issued the seat loads and waited again --
+// two memory round trips per tile instead of one (SASS of r1r: LOP3 on the tbl register before 16 of 24 seat LDGs).
+// Volatile loads keep program order among themselves, and the table word is loaded LAST, so nothing can consume it
+// before every other first-level load has been issued.  (These words are read once per launch: bypassing L1 costs nothing.)
+#ifdef __CUDA_ARCH__
+__device__ __forceinline__ int32_t pkp_ldv32(const int32_t* p) { return *reinterpret_cast<const volatile int32_t*>(p); }
+__device__ __forceinline__ uint32_t pkp_ldv16(const uint16_t* p) { return *reinterpret_cast<const volatile uint16_t*>(p); }
+__device__ __forceinline__ PulseU2x pkp_ldv2(const uint32_t* p) {
+  PulseU2x r;
+  asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ PulseU4x pkp_ldv4(const uint32_t* p) {
+  PulseU4x r;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+#else
+inline int32_t pkp_ldv32(const int32_t* p) { return *p; }
+inline uint32_t pkp_ldv16(const uint16_t* p) { return *p; }
+inline PulseU2x pkp_ldv2(const uint32_t* p) { return pkp_ld2(p); }
+inline PulseU4x pkp_ldv4(const uint32_t* p) { return pkp_ld4(p); }
+#endif
+
 template <int MAXP>
 PULSE_HD void packed_load(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPacked& S, long long g, long long n,
                           int AP) {
-  PulseU4x a = pkp_ld4(S.tbl + 4 * g);
-  PulseU2x b = pkp_ld2(S.tbl2 + 2 * g);
+  PulseU4x a; PulseU2x b;
+  uint32_t h[MAXP];
+  if (MAXP <= 6) {
+    // seats beyond AP re-read seat 0 and are zeroed by a select: no branch per seat, the loads form one straight line
+    int32_t st[MAXP], cr[MAXP], iv[MAXP];
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) {
+      const long long o = (long long)(s < AP ? s : 0) * n + g;
+      st[s] = pkp_ldv32(S.stack + o); cr[s] = pkp_ldv32(S.crb + o); iv[s] = pkp_ldv32(S.inv + o);
+      h[s] = pkp_ldv16(S.hole + o);
+    }
+    b = pkp_ldv2(S.tbl2 + 2 * g);
+    a = pkp_ldv4(S.tbl + 4 * g);
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) {
+      const bool on = s < AP;
+      t.stack[s] = on ? st[s] : 0; t.crb[s] = on ? cr[s] : 0; t.inv[s] = on ? iv[s] : 0; h[s] = on ? h[s] : 0xFFFFFFFFu;
+    }
+  } else {
+    // wider tables: holding every seat's words live at once costs more in spills than the strict order gains
+    // (ten seats: 0.80 ordered against 0.84 like this) -- ordinary loads, written ahead of the decode
+    a = pkp_ld4(S.tbl + 4 * g);
+    b = pkp_ld2(S.tbl2 + 2 * g);
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) {
+      t.stack[s] = t.crb[s] = t.inv[s] = 0; h[s] = 0xFFFFFFFFu;
+      if (s < AP) {
+        long long o = (long long)s * n + g;
+        t.stack[s] = S.stack[o]; t.crb[s] = S.crb[o]; t.inv[s] = S.inv[o];
+        h[s] = S.hole[o];
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {  // a seat that is not dealt in holds (-1, -1)
+    t.hole0[s] = h[s] == 0xFFFFFFFFu ? -1 : (int)(h[s] & 63u);
+    t.hole1[s] = h[s] == 0xFFFFFFFFu ? -1 : (int)((h[s] >> 6) & 63u);
+  }
   t.stage = a.x & 7; t.idx = (a.x >> 3) & 15; t.agg = (a.x >> 7) & 15; t.button = (a.x >> 11) & 15;
   t.acted = (a.x >> 15) & 31; t.done = (a.x >> 20) & 1; t.dirty = false;
   t.st = a.y; t.pot = (int32_t)a.z; t.highest = (int32_t)a.w; t.last_raise = (int32_t)b.x;
@@ -92,16 +154,6 @@ PULSE_HD void packed_load(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
 #pragma unroll
   for (int i = 0; i < 5; ++i) t.board[i] = i < vis ? (int)((fb >> (6 * i)) & 63u) : -1;
   t.deck_pos = 2 * AP + (t.stage == 0 ? 0 : t.stage == 1 ? 4 : t.stage == 2 ? 6 : 8);
-#pragma unroll
-  for (int s = 0; s < MAXP; ++s) {
-    t.stack[s] = t.crb[s] = t.inv[s] = 0; t.hole0[s] = t.hole1[s] = -1;
-    if (s < AP) {
-      long long o = (long long)s * n + g;
-      t.stack[s] = S.stack[o]; t.crb[s] = S.crb[o]; t.inv[s] = S.inv[o];
-      uint32_t h = S.hole[o];
-      t.hole0[s] = (int)(h & 63u); t.hole1[s] = (int)((h >> 6) & 63u);
-    }
-  }
 }
 
 template <int MAXP>
@@ -237,8 +289,16 @@ struct PackedEv<MAXP, true> {
   const uint64_t* ev; long long g, n;
   uint64_t w[MAXP];
   PULSE_HD void prefetch(int AP) {
+#ifdef __CUDA_ARCH__
+    // part of the step's ordered first-level loads (see packed_load): no branch, seats beyond AP re-read seat 0
 #pragma unroll
+    for (int s = 0; s < MAXP; ++s) {
+      const uint64_t v = *reinterpret_cast<const volatile uint64_t*>(ev + (long long)(s < AP ? s : 0) * n + g);
+      w[s] = s < AP ? v : 0;
+    }
+#else
     for (int s = 0; s < MAXP; ++s) w[s] = s < AP ? ev[(long long)s * n + g] : 0;
+#endif
   }
   PULSE_HD uint64_t word(int s) const {
     uint64_t v = w[0];
@@ -301,8 +361,13 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   uint32_t fb;
   PackedEv<MAXP, (MAXP <= 2)> evw{S.ev, g, n};
   evw.prefetch(AP);
+  long long a = 0;
+#ifdef __CUDA_ARCH__
+  if (!POLICY) a = *reinterpret_cast<const volatile long long*>(actions + g);  // first of the ordered first-level loads
+#else
+  if (!POLICY) a = actions[g];
+#endif
   packed_load(t, fb, S, g, n, AP);
-  long long a;
   if (POLICY) {  // build_actions: computed from the pre-step state for every table, done or not (utils.py:108-123)
     const int kind = pol->kinds.kind[t.idx & 15];
     if (kind == PULSE_AGENT_EXTERNAL) {
@@ -341,7 +406,6 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   }
   const PokerTable<MAXP> t0 = t;
   const PackedDeck deck{fb, 2 * AP};
-  if (!POLICY) a = actions[g];
   const bool prev_done = t.done;
   const int actor = t.idx;                                           // :531
   const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537

@@ -42,7 +42,8 @@ __device__ __forceinline__ void tfe_write_obs(int32_t* smem, const uint64_t b, c
 constexpr int kStepBlock = 1024;
 constexpr int kTableBytes = 65536 * 2 + 65536;                    // result u16 + score code u8
 constexpr int kLutBytes = 256 * 8;                                // byte (two cells) -> two int32 tile values
-constexpr int kStepSmem = kTableBytes + kStepBlock * 8 + kLutBytes;  // + one packed board per thread + the LUT
+constexpr int kScoreLutBytes = 256 * 4;                           // score code -> score
+constexpr int kStepSmem = kTableBytes + kStepBlock * 8 + kLutBytes + kScoreLutBytes;  // + one packed board per thread + the LUTs
 
 // The byte LUT's 8-byte entries sit in 16 bank pairs chosen by the low nibble of the index, i.e. by the
 // first cell's exponent alone; with small exponents most of a half-warp lands on 3-4 pairs.  Folding the
@@ -122,6 +123,13 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
       pulse_bulk_g2s(reinterpret_cast<uint8_t*>(smem_raw) + off, reinterpret_cast<const uint8_t*>(table) + off, kChunk,
                      &table_bar);
   }
+  uint64_t* wboards = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes) + (threadIdx.x & ~31);
+  uint2* lut = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8);
+  uint32_t* score_lut = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8 + kLutBytes);
+  if (threadIdx.x < 256) {                                          // the two small LUTs (published by the barrier below)
+    lut[tfe_lut_slot(threadIdx.x)] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
+    score_lut[threadIdx.x] = tfe_code_score(threadIdx.x);
+  }
   // ---- everything below reads or writes what earlier kernels may have written ----
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -138,10 +146,7 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   TfeTableRows rows;
   rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
   rows.code = reinterpret_cast<const uint8_t*>(smem_raw) + 65536 * 2;
-  uint64_t* wboards = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes) + (threadIdx.x & ~31);
-  uint2* lut = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8);
-  if (threadIdx.x < 256)
-    lut[tfe_lut_slot(threadIdx.x)] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
+  rows.score_of_code = score_lut;
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31;
   for (; g - lane < n; g += stride) {                              // warp-uniform trip count

@@ -171,7 +171,9 @@ int emu_tfe_table_check(void) {
   static uint16_t res[65536];
   static uint8_t code[65536];
   for (uint32_t r = 0; r < 65536; ++r) { uint32_t sc = 0; res[tfe_row_slot(r)] = (uint16_t)tfe_squash_row(r, sc); code[tfe_row_slot(r)] = (uint8_t)tfe_score_code(r); }
-  TfeTableRows t{res, code};
+  static uint32_t sc_of[256];
+  for (uint32_t c = 0; c < 256; ++c) sc_of[c] = tfe_code_score(c);
+  TfeTableRows t{res, code, sc_of};
   int bad = 0;
   for (uint32_t r = 0; r < 65536; ++r) {
     uint32_t s1 = 0, s2 = 0;
