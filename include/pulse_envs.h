@@ -172,7 +172,8 @@ typedef struct PulsePokerConfig {
 /* reset (PokerGPU.py:73-157).  prefixed_decks_or_null: int32 [N,52] copied into st->decks; NULL
  * draws each deck from the chance tape (seed, env_base + table, hand_counter).  first_reset bit 0: stacks = starting_bbs
  * (else busted/oversized stacks are refilled and rolled by `rotation`); bit 1: button = 0 (else it
- * advances modulo the table size).  The first reset of an env passes 3.  Writes the first observation [N, 13+3(M-1)]. */
+ * advances modulo the table size); bit 2 (packed layout only): restart the per-table hand index at hand_counter.
+ * The first reset of an env passes 3.  Writes the first observation [N, 13+3(M-1)]. */
 int pulse_poker_reset(const PulsePokerState* st, const PulsePokerConfig* cfg, const int32_t* prefixed_decks_or_null,
                       uint64_t seed, uint64_t env_base, uint32_t hand_counter, int rotation, int first_reset,
                       float* obs_out, pulse_stream_t stream);
@@ -210,11 +211,18 @@ typedef struct PulsePokerPacked {
   uint32_t* hand_ctr;        /* [N] hands dealt (needed for auto_reset), may be NULL otherwise */
   const int32_t* hand_ranks; /* HandRanks table (only its first 36,875 entries are read) */
   int64_t n_hand_ranks;
+  /* optional live mirrors of two reference attributes, written by reset / step / redeal when non-NULL:
+   * idx = the seat to act (info["seat_idx"], PokerGPU.py:181-186) and prev_invested (:539, :151) */
+  int32_t* idx;              /* [N] or NULL */
+  int32_t* prev_invested;    /* [N] or NULL */
 } PulsePokerPacked;
 
 /* Same contracts as pulse_poker_reset / pulse_poker_step.  auto_reset != 0 (engine extension): a
  * table already done when the step begins is dealt its next hand from the chance tape instead of
- * idling; that step returns reward 0, done 0 and the new hand's first observation. */
+ * idling; that step returns reward 0, done 0 and the new hand's first observation.
+ * The tape's hand index is monotonic per table: a reset deals hand max(hand_ctr[table] + 1, hand_counter) (first_reset
+ * bit 2 set: exactly hand_counter, restarting the tape, e.g. after reseeding), a redeal hand_ctr[table] + 1 -- so
+ * whole-batch resets mixed with per-table redeals never replay a deck. */
 int pulse_poker_packed_reset(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
                              const int32_t* prefixed_decks_or_null, uint64_t seed, uint64_t env_base,
                              uint32_t hand_counter, int rotation, int first_reset, float* obs_out_or_null,
@@ -260,9 +268,21 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
  * hands = 0.5.  An optional input for a caller's reward; the step's own reward keeps the reference's proxy. */
 int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,
                                            pulse_stream_t stream);
-/* packed -> reference-shaped tensors (decks, sb/bb, equities, prev_invested are not represented) */
+/* packed -> reference-shaped tensors.  Writes every field of `compat` whose pointer is non-NULL except decks
+ * (a pure function of the deal, see pulse_poker_unpack_full) and prev_invested.  sb / bb follow from button and
+ * active_players (PokerGPU.py:123-128); equities / equity_dirty are the reference's cache as it stands after the
+ * last step: the values of the last street on which a step began (the packed table word keeps that street in two
+ * bits), dirty where the street has changed since (:604-616). */
 int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
                        pulse_stream_t stream);
+/* The full mirror behind "Pulse-Poker-GPU-v1" (mirror on access): pulse_poker_unpack plus decks [N,52] -- copied
+ * from prefixed_decks_or_null (the tensor the last reset was given) or re-drawn from the chance tape at
+ * (seed, env_base + table, hand_ctr[table]) exactly as pulse_poker_reset draws them -- and prev_invested (from
+ * st->prev_invested when the engine keeps it, else 0).  fresh != 0: no step has run since the last reset, every
+ * table's equity cache is dirty (:145). */
+int pulse_poker_unpack_full(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                            const int32_t* prefixed_decks_or_null, uint64_t seed, uint64_t env_base, int fresh,
+                            pulse_stream_t stream);
 
 /* ---- run statistics (the vector that is all-reduced across GPUs) -------------------
  * stats4 double [4] on the device: += {n, number of done flags set, sum(reward), sum(reward^2)}.

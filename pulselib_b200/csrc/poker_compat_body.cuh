@@ -27,7 +27,7 @@ PULSE_HD void compat_load(PokerTable<MAXP>& t, const PulsePokerState& S, int g, 
 #pragma unroll
   for (int i = 0; i < 5; ++i) t.board[i] = S.board[(size_t)g * 5 + i];
   t.stage = S.stages[g]; t.idx = S.idx[g]; t.agg = S.agg[g]; t.acted = S.acted[g];
-  t.button = S.button[g]; t.deck_pos = S.deck_positions[g];
+  t.button = S.button[g]; t.deck_pos = S.deck_positions[g]; t.eq_stage = 0;
   t.done = done; t.dirty = S.equity_dirty[g] != 0;
 }
 
@@ -122,14 +122,7 @@ PULSE_HD void compat_reset_one(const PulsePokerState& S, const PokerParams& pr, 
     for (int i = 0; i < 52; ++i) deck[i] = prefixed[(size_t)g * 52 + i];  // :88-92
   } else {  // chance tape -> forward Fisher-Yates (replaces rand().argsort()+1, :86)
     uint8_t d[52];
-    for (int i = 0; i < 52; ++i) d[i] = (uint8_t)(i + 1);
-    PulseU4 blk;
-    for (int i = 0; i < 51; ++i) {
-      if ((i & 3) == 0) blk = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_POKER_DECK, hand * 16u + (uint32_t)(i >> 2));
-      uint32_t u = (i & 3) == 0 ? blk.x : (i & 3) == 1 ? blk.y : (i & 3) == 2 ? blk.z : blk.w;
-      int j = i + (int)pulse_mulhi32(u, (uint32_t)(52 - i));
-      uint8_t tmp = d[i]; d[i] = d[j]; d[j] = tmp;
-    }
+    pk_tape_deck(d, seed, env_base + (uint64_t)g, hand);
     for (int i = 0; i < 52; ++i) deck[i] = d[i];
   }
   PokerTable<MAXP> t;
@@ -166,7 +159,7 @@ PULSE_HD void compat_reset_one(const PulsePokerState& S, const PokerParams& pr, 
 #pragma unroll
   for (int i = 0; i < 5; ++i) t.board[i] = -1;
   t.stage = 0; t.idx = AP == 2 ? button : (bb + 1) % AP;    // :130-133
-  t.agg = bb; t.acted = 0; t.button = button; t.deck_pos = 2 * AP; t.done = false; t.dirty = true;
+  t.agg = bb; t.acted = 0; t.button = button; t.deck_pos = 2 * AP; t.eq_stage = 0; t.done = false; t.dirty = true;
 #pragma unroll
   for (int s = 0; s < MAXP; ++s)
     if (s < P) {

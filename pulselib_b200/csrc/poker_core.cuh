@@ -31,6 +31,7 @@ struct PokerTable {
   int32_t pot, highest, last_raise;
   int32_t board[5];  // -1 = not dealt
   int32_t stage, idx, agg, acted, button, deck_pos;
+  int32_t eq_stage;  // packed layout only: the street (1..3) the reference's equity cache was last computed on, 0 = none
   bool done, dirty;
 };
 
@@ -83,6 +84,21 @@ PULSE_HD int32_t pk_table_walk(const int32_t* __restrict__ hr, long long n, int 
   for (int i = 0; i < n_board; ++i) p = pk_hr_at(hr, n, (long long)p + board[i]);
   return p;
 }
+// The whole 52-card deck of (seed, env, hand) on the chance tape: forward Fisher-Yates, position i fixed at
+// iteration i (replaces rand().argsort() + 1, PokerGPU.py:86).  The packed deal runs the same loop for the first
+// 2 AP + 8 positions only, so its cards are this deck's prefix.
+PULSE_HD void pk_tape_deck(uint8_t (&d)[52], uint64_t seed, uint64_t env_id, uint32_t hand) {
+  for (int i = 0; i < 52; ++i) d[i] = (uint8_t)(i + 1);
+  PulseU4 blk;
+  blk.x = blk.y = blk.z = blk.w = 0;
+  for (int i = 0; i < 51; ++i) {
+    if ((i & 3) == 0) blk = pulse_tape(seed, env_id, PULSE_STREAM_POKER_DECK, hand * 16u + (uint32_t)(i >> 2));
+    uint32_t u = (i & 3) == 0 ? blk.x : (i & 3) == 1 ? blk.y : (i & 3) == 2 ? blk.z : blk.w;
+    int j = i + (int)pulse_mulhi32(u, (uint32_t)(52 - i));
+    uint8_t tmp = d[i]; d[i] = d[j]; d[j] = tmp;
+  }
+}
+
 PULSE_HD int pk_popc64(uint64_t m) { return PULSE_POPC((uint32_t)m) + PULSE_POPC((uint32_t)(m >> 32)); }
 
 // The reference's hand-strength proxy for one seat (:455-525).  stage 3: 7-card value; stage 2:

@@ -204,9 +204,10 @@ poker_packed_redeal_kernel(PulsePokerPacked S, PokerParams pr, uint64_t seed, ui
 
 template <int MAXP>
 __global__ void __launch_bounds__(kBlock)
-poker_packed_unpack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr, long long n) {
+poker_packed_unpack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr, long long n, bool with_decks,
+                           const int32_t* __restrict__ prefixed, uint64_t seed, uint64_t env_base, bool fresh) {
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock)
-    packed_unpack_one<MAXP>(S, C, pr, g, n);
+    packed_unpack_one<MAXP>(S, C, pr, g, n, with_decks, prefixed, seed, env_base, fresh);
 }
 
 // one thread per (table, seat): seat-major so a warp reads 32 consecutive tables' hole cards and table words
@@ -433,16 +434,30 @@ int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const Pul
   return pulse_check_launch("pulse_poker_packed_enumerated_strength");
 }
 
-int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
-                       cudaStream_t stream) {
+static int launch_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                         bool with_decks, const int32_t* prefixed, uint64_t seed, uint64_t env_base, bool fresh,
+                         cudaStream_t stream, const char* what) {
   int rc = check_cfg(st, cfg);
   if (rc) return rc;
   PULSE_REQUIRE(compat != nullptr, "compat state is null");
+  PULSE_REQUIRE(!compat->equities || st->ev, "equities need the packed hand-value words");
   if (cfg->n_games == 0) return PULSE_OK;
   PokerParams pr = make_params(cfg);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
-  PKP_DISPATCH(pr.P, (poker_packed_unpack_kernel<MP><<<grid, kBlock, 0, stream>>>(*st, *compat, pr,
-                                                                                  (long long)cfg->n_games)));
-  return pulse_check_launch("pulse_poker_unpack");
+  PKP_DISPATCH(pr.P, (poker_packed_unpack_kernel<MP><<<grid, kBlock, 0, stream>>>(
+                         *st, *compat, pr, (long long)cfg->n_games, with_decks, prefixed, seed, env_base, fresh)));
+  return pulse_check_launch(what);
+}
+
+int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                       cudaStream_t stream) {
+  return launch_unpack(st, compat, cfg, false, nullptr, 0, 0, false, stream, "pulse_poker_unpack");
+}
+
+int pulse_poker_unpack_full(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                            const int32_t* prefixed_decks_or_null, uint64_t seed, uint64_t env_base, int fresh,
+                            cudaStream_t stream) {
+  return launch_unpack(st, compat, cfg, true, prefixed_decks_or_null, seed, env_base, fresh != 0, stream,
+                       "pulse_poker_unpack_full");
 }
 }

@@ -1,7 +1,9 @@
 // Packed PokerGPU layout: the throughput path.  Same per-table logic as the reference-shaped
 // kernels (poker_core.cuh), different HBM layout:
 //
-//   tbl   uint4 [N]    x = meta  (stage:3 | idx:4 | agg:4 | button:4 | acted:5 | done:1)
+//   tbl   uint4 [N]    x = meta  (stage:3 | idx:4 | agg:4 | button:4 | acted:5 | done:1 | eq_stage:2)
+//                          eq_stage: the street (1..3) on which a step last began, i.e. the street the
+//                          reference's cached equities belong to (PokerGPU.py:542, :604-616); 0 = none yet
 //                      y = status bit-planes (bit s = low bit of seat s, bit 16+s = high bit)
 //                      z = pot, w = highest
 //   tbl2  uint2 [N]    x = last_raise_size, y = the hand's five board cards, 6 bits each
@@ -39,10 +41,10 @@ struct PackedDeck {
   }
 };
 
-PULSE_HD uint32_t pkp_meta(int stage, int idx, int agg, int button, int acted, bool done) {
+PULSE_HD uint32_t pkp_meta(int stage, int idx, int agg, int button, int acted, bool done, int eq_stage) {
   if (acted > 31) acted = 31;  // only ever compared with the number of ACTIVE seats (<= 10)
   return (uint32_t)stage | ((uint32_t)idx << 3) | ((uint32_t)agg << 7) | ((uint32_t)button << 11) |
-         ((uint32_t)acted << 15) | ((uint32_t)done << 20);
+         ((uint32_t)acted << 15) | ((uint32_t)done << 20) | ((uint32_t)eq_stage << 21);
 }
 
 struct PulseU4x { uint32_t x, y, z, w; };
@@ -147,7 +149,7 @@ PULSE_HD void packed_load(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
     t.hole1[s] = h[s] == 0xFFFFFFFFu ? -1 : (int)((h[s] >> 6) & 63u);
   }
   t.stage = a.x & 7; t.idx = (a.x >> 3) & 15; t.agg = (a.x >> 7) & 15; t.button = (a.x >> 11) & 15;
-  t.acted = (a.x >> 15) & 31; t.done = (a.x >> 20) & 1; t.dirty = false;
+  t.acted = (a.x >> 15) & 31; t.done = (a.x >> 20) & 1; t.eq_stage = (a.x >> 21) & 3; t.dirty = false;
   t.st = a.y; t.pot = (int32_t)a.z; t.highest = (int32_t)a.w; t.last_raise = (int32_t)b.x;
   fb = b.y;
   const int vis = t.stage == 0 ? 0 : t.stage == 1 ? 3 : t.stage == 2 ? 4 : 5;
@@ -159,8 +161,8 @@ PULSE_HD void packed_load(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
 template <int MAXP>
 PULSE_HD void packed_store(const PokerTable<MAXP>& t, const PokerTable<MAXP>& o, const PulsePokerPacked& S,
                            long long g, long long n, int AP) {
-  uint32_t m1 = pkp_meta(t.stage, t.idx, t.agg, t.button, t.acted, t.done);
-  uint32_t m0 = pkp_meta(o.stage, o.idx, o.agg, o.button, o.acted, o.done);
+  uint32_t m1 = pkp_meta(t.stage, t.idx, t.agg, t.button, t.acted, t.done, t.eq_stage);
+  uint32_t m0 = pkp_meta(o.stage, o.idx, o.agg, o.button, o.acted, o.done, o.eq_stage);
   if (m1 != m0 || t.st != o.st || t.pot != o.pot || t.highest != o.highest)
     pkp_st4(S.tbl + 4 * g, m1, t.st, (uint32_t)t.pot, (uint32_t)t.highest);
   if (t.last_raise != o.last_raise) S.tbl2[2 * g] = (uint32_t)t.last_raise;
@@ -255,7 +257,7 @@ PULSE_HD void packed_deal(PokerTable<MAXP>& t, uint32_t& fb, const PulsePokerPac
 #pragma unroll
   for (int i = 0; i < 5; ++i) t.board[i] = -1;
   t.stage = 0; t.idx = AP == 2 ? button : (bb + 1) % AP;           // :130-133
-  t.agg = bb; t.acted = 0; t.button = button; t.deck_pos = 2 * AP; t.done = false; t.dirty = false;
+  t.agg = bb; t.acted = 0; t.button = button; t.deck_pos = 2 * AP; t.eq_stage = 0; t.done = false; t.dirty = false;
   fb = (uint32_t)f0 | ((uint32_t)f1 << 6) | ((uint32_t)f2 << 12) | ((uint32_t)tn << 18) | ((uint32_t)rv << 24);
   // hand values of every dealt seat on the flop, turn and river boards of this deal
   const uint64_t flop = pe_add_card64(f2, pe_add_card64(f1, pe_add_card64(f0, 0)));
@@ -322,9 +324,11 @@ struct PackedEv<MAXP, false> {
 template <int MAXP>
 PULSE_HD void packed_store_all(const PokerTable<MAXP>& t, uint32_t fb, const PulsePokerPacked& S, long long g,
                                long long n, int P) {
-  pkp_st4(S.tbl + 4 * g, pkp_meta(t.stage, t.idx, t.agg, t.button, t.acted, t.done), t.st, (uint32_t)t.pot,
+  pkp_st4(S.tbl + 4 * g, pkp_meta(t.stage, t.idx, t.agg, t.button, t.acted, t.done, t.eq_stage), t.st, (uint32_t)t.pot,
           (uint32_t)t.highest);
   pkp_st2(S.tbl2 + 2 * g, (uint32_t)t.last_raise, fb);
+  if (S.idx) S.idx[g] = t.idx;
+  if (S.prev_invested) S.prev_invested[g] = 0;   // :151
 #pragma unroll
   for (int s = 0; s < MAXP; ++s)
     if (s < P) {
@@ -410,6 +414,10 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   const int actor = t.idx;                                           // :531
   const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537
   const int prev_inv = pk_sel(t.crb, actor);                         // :539
+  if (S.prev_invested) S.prev_invested[g] = prev_inv;
+  // the reference refreshes its equity cache here when the street has changed since the last step (:542);
+  // the packed layout only remembers for which street the cache stands
+  if (t.stage >= 1 && t.stage <= 3) t.eq_stage = t.stage;
   float e = 0.5f;
   if (legal)  // the reward is zeroed otherwise (:632), so the equity is only needed for legal actors
     e = (t.stage >= 1 && t.stage <= 3) ? pkp_equity_from(evw.word(actor), t.stage) : 0.5f;
@@ -427,6 +435,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
   reward_out[g] = legal ? pk_reward(t, pr, a, e, prev_inv) : 0.0f;   // :631-632
   done_out[g] = t.done;
   packed_store(t, t0, S, g, n, AP);
+  if (S.idx && t.idx != t0.idx) S.idx[g] = t.idx;
   pk_obs(t, pr, obs_row);                                            // :633
 }
 
@@ -439,6 +448,12 @@ PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr,
   uint32_t fb;
   int button = 0;
   if (!(first_reset & 2)) button = (int)(((S.tbl[4 * g] >> 11) & 15u) + 1u) % pr.AP;  // :121
+  // the tape's hand index never goes back for a table: whole-batch resets mixed with per-table redeals (which
+  // advance hand_ctr on their own) must not replay a deck.  first_reset bit 2 restarts the index at `hand`.
+  if (S.hand_ctr && !(first_reset & 4)) {
+    const uint32_t nxt = (S.hand_ctr[g] & ~PKP_REDEAL_MARK) + 1u;
+    if (nxt > hand) hand = nxt;
+  }
   packed_deal(t, fb, S, pr, prefixed, seed, env_base + (uint64_t)g, hand, rotation, !(first_reset & 1), button,
               starting_bbs, max_bbs, g, n, dk);
   packed_store_all(t, fb, S, g, n, pr.P);
@@ -453,7 +468,7 @@ PULSE_HD bool packed_redeal_one(const PulsePokerPacked& S, const PokerParams& pr
                                 DeckBuf& dk) {
   const uint32_t ctr = S.hand_ctr[g];
   if (!(ctr & PKP_REDEAL_MARK)) return false;
-  packed_reset_one<MAXP>(S, pr, nullptr, seed, env_base, (ctr & ~PKP_REDEAL_MARK) + 1u, 0, 0, starting_bbs, max_bbs,
+  packed_reset_one<MAXP>(S, pr, nullptr, seed, env_base, (ctr & ~PKP_REDEAL_MARK) + 1u, 0, 4, starting_bbs, max_bbs,
                          obs_row, g, n, dk);   // stores hand_ctr = new counter: the mark is cleared
   return true;
 }
@@ -502,11 +517,14 @@ PULSE_HD float packed_enumerated_strength(int stage, int h0, int h1, uint32_t fb
   return PULSE_FDIV((float)sum, PULSE_FMUL((float)count, 32765.0f));
 }
 
-// packed -> reference-shaped tensors (for inspection and parity checks); decks, sb/bb, equities and
-// prev_invested are not represented in the packed layout and are left untouched.
+// packed -> reference-shaped tensors: the mirror behind attribute access on the drop-in env class, and the
+// inspection path of the parity tests.  Every pointer of C may be NULL (field not wanted).  decks: re-drawn from the
+// tape (or copied from the prefixed decks of the last reset) when `with_decks`; equities / equity_dirty: the
+// reference's cache as it stands (header of include/pulse_envs.h); prev_invested: the engine's own mirror, else 0.
 template <int MAXP>
 PULSE_HD void packed_unpack_one(const PulsePokerPacked& S, const PulsePokerState& C, const PokerParams& pr,
-                                long long g, long long n) {
+                                long long g, long long n, bool with_decks = false, const int32_t* prefixed = nullptr,
+                                uint64_t seed = 0, uint64_t env_base = 0, bool fresh = false) {
   const int P = pr.P, AP = pr.AP;
   PokerTable<MAXP> t;
   uint32_t fb;
@@ -517,15 +535,41 @@ PULSE_HD void packed_unpack_one(const PulsePokerPacked& S, const PulsePokerState
   }
   for (int s = 0; s < P; ++s) {
     long long off = g * P + s;
-    C.stacks[off] = s < AP ? pk_sel(t.stack, s) : S.stack[(long long)s * n + g];
-    C.current_round_bet[off] = pk_sel(t.crb, s);
-    C.total_invested[off] = pk_sel(t.inv, s);
-    C.status[off] = s < P ? pk_status(t.st, s) : PK_SITOUT;
-    C.hands[2 * off] = pk_sel(t.hole0, s);
-    C.hands[2 * off + 1] = pk_sel(t.hole1, s);
+    if (C.stacks) C.stacks[off] = s < AP ? pk_sel(t.stack, s) : S.stack[(long long)s * n + g];
+    if (C.current_round_bet) C.current_round_bet[off] = pk_sel(t.crb, s);
+    if (C.total_invested) C.total_invested[off] = pk_sel(t.inv, s);
+    if (C.status) C.status[off] = s < P ? pk_status(t.st, s) : PK_SITOUT;
+    if (C.hands) { C.hands[2 * off] = pk_sel(t.hole0, s); C.hands[2 * off + 1] = pk_sel(t.hole1, s); }
   }
-  for (int i = 0; i < 5; ++i) C.board[g * 5 + i] = t.board[i];
-  C.pots[g] = t.pot; C.stages[g] = t.stage; C.highest[g] = t.highest; C.last_raise_size[g] = t.last_raise;
-  C.idx[g] = t.idx; C.agg[g] = t.agg; C.acted[g] = t.acted; C.button[g] = t.button;
-  C.deck_positions[g] = t.deck_pos; C.is_done[g] = t.done;
+  if (C.board) for (int i = 0; i < 5; ++i) C.board[g * 5 + i] = t.board[i];
+  if (C.pots) C.pots[g] = t.pot;
+  if (C.stages) C.stages[g] = t.stage;
+  if (C.highest) C.highest[g] = t.highest;
+  if (C.last_raise_size) C.last_raise_size[g] = t.last_raise;
+  if (C.idx) C.idx[g] = t.idx;
+  if (C.agg) C.agg[g] = t.agg;
+  if (C.acted) C.acted[g] = t.acted;
+  if (C.button) C.button[g] = t.button;
+  if (C.deck_positions) C.deck_positions[g] = t.deck_pos;
+  if (C.is_done) C.is_done[g] = t.done;
+  {  // blinds as reset placed them (:123-128)
+    const int b = t.button;
+    if (C.sb) C.sb[g] = AP == 2 ? b : (b + 1) % AP;
+    if (C.bb) C.bb[g] = AP == 2 ? (b + 1) % AP : (b + 2) % AP;
+  }
+  if (C.equities)
+    for (int s = 0; s < AP; ++s)
+      C.equities[g * AP + s] = t.eq_stage == 0 ? 0.5f : pkp_equity_from(S.ev[(long long)s * n + g], t.eq_stage);
+  if (C.equity_dirty) C.equity_dirty[g] = fresh || (t.stage >= 1 && t.stage <= 3 && t.stage != t.eq_stage);
+  if (C.prev_invested) C.prev_invested[g] = S.prev_invested ? S.prev_invested[g] : 0;
+  if (with_decks && C.decks) {
+    int32_t* deck = C.decks + g * 52;
+    if (prefixed) {
+      for (int i = 0; i < 52; ++i) deck[i] = prefixed[g * 52 + i];
+    } else {
+      uint8_t d[52];
+      pk_tape_deck(d, seed, env_base + (uint64_t)g, S.hand_ctr ? (S.hand_ctr[g] & ~PKP_REDEAL_MARK) : 0u);
+      for (int i = 0; i < 52; ++i) deck[i] = d[i];
+    }
+  }
 }

@@ -1,11 +1,21 @@
 """PokerGPU behind the reference's gym.Env surface, stepped by one fused CUDA launch.
 
 Drop-in for /root/reference/environments/Poker/PokerGPU.py:8-633: same constructor, same tensor
-attributes (shapes/dtypes of SURVEY.md 8(a)), same internal method names, same return tuples.  All
-state lives in torch CUDA tensors that are handed by pointer to libpulse_envs.so
-(include/pulse_envs.h: pulse_poker_reset / pulse_poker_step).  Tests of the reference overwrite
-these tensors and rebind them; the pointer table is therefore rebuilt from the live attributes on
-every call.
+attributes (shapes/dtypes of SURVEY.md 8(a)), same internal method names, same return tuples.
+
+Two classes:
+
+* `PokerGPUCompat` keeps every reference attribute as its own int32 torch tensor and hands them by pointer to
+  libpulse_envs.so (include/pulse_envs.h: pulse_poker_reset / pulse_poker_step).  Tests of the reference overwrite
+  these tensors and rebind them; the pointer table is therefore rebuilt from the live attributes on every call.
+* `PokerGPU` -- what `gym.make("Pulse-Poker-GPU-v1")` builds -- runs on the packed throughput layout
+  (envs/poker_packed.py, csrc/poker_packed*.cu*) and **mirrors on access** (SURVEY.md 7.3 item 4): reset / step /
+  info need no reference-shaped tensor at all; the first read of `env.stages`, `env.board`, ... between two calls
+  unpacks the whole state into fresh reference-shaped tensors (one launch, pulse_poker_unpack_full); if the caller
+  then writes into one of them, rebinds one, or calls one of the reference's internal methods
+  (`execute_actions`, `calculate_equities`, ...), the env carries on from those tensors on the reference-shaped
+  kernels until the next reset().  Writes are detected through torch's per-tensor version counter, so reads cost
+  one unpack and nothing else.
 """
 from __future__ import annotations
 
@@ -46,7 +56,7 @@ def device_hand_ranks(device: torch.device) -> torch.Tensor:
     return _TABLES[key]
 
 
-class PokerGPU(gym.Env):
+class PokerGPUCompat(gym.Env):
     metadata = {"render.modes": ["human"]}
     NUM_ACTIONS = 13
     ACTIVE, FOLDED, ALLIN, SITOUT = 0, 1, 2, 3
@@ -260,3 +270,204 @@ class PokerGPU(gym.Env):
 
     def close(self):
         return None
+
+
+_MIRROR = ("decks", "deck_positions", "board", "pots", "stages", "stacks", "hands", "current_round_bet",
+           "total_invested", "status", "button", "sb", "bb", "idx", "highest", "agg", "acted", "last_raise_size",
+           "prev_invested", "is_done", "equity_dirty", "equities")
+_LIVE = ("stacks", "idx", "prev_invested", "is_done")       # real tensors the packed kernels keep current
+_DERIVED = ("button_pos", "prev_stacks", "raise_amounts", "active_player_idx")
+_MIRROR_SET = frozenset(_MIRROR)
+_LAZY_SET = frozenset(_MIRROR + _DERIVED) - frozenset(_LIVE)
+
+
+class PokerGPU(PokerGPUCompat):
+    """`Pulse-Poker-GPU-v1`: the reference's env surface on the packed throughput layout, mirror on access.
+
+    Packed mode (default after every reset): `stacks` is a live [N, P] view of the engine's seat-major stack array,
+    `idx` / `prev_invested` / `is_done` are the tensors the step kernel writes, `obs` the observation buffer; every
+    other reference attribute appears when it is first read (a snapshot that is dropped by the next reset/step).
+    Reference-shaped mode: entered when a mirrored tensor was written or rebound, an internal method is called, or
+    `calculate_equities` was replaced on the instance; also for good when `hand_ranks` is given (a caller-supplied
+    table defines the hand values, the packed engine computes them) or `layout="compat"`."""
+
+    def __init__(self, device, agents, n_players=6, max_players=10, n_games=100, starting_bbs=100, max_bbs=1000,
+                 w1=.5, w2=.5, K=20, alpha=300, seed=0, env_base=0, hand_ranks=None, layout="packed"):
+        d = self.__dict__
+        d["_mode"], d["_eng"], d["_eng_live"] = "compat", None, False
+        d["_ver"], d["_materialised"], d["_touched"] = {}, None, False
+        super().__init__(device, agents, n_players, max_players, n_games, starting_bbs, max_bbs, w1, w2, K, alpha,
+                         seed, env_base, hand_ranks)
+        if layout not in ("packed", "compat"):
+            raise ValueError("layout must be 'packed' or 'compat'")
+        d["_force_compat"] = hand_ranks is not None or layout == "compat"
+
+    # ---- attribute plumbing ----------------------------------------------------------------------------------
+    def __getattr__(self, name):               # only reached when normal lookup fails
+        d = self.__dict__
+        if name in _LAZY_SET and d.get("_mode") == "packed" and d.get("_eng_live"):
+            self._materialise()
+            if name in d:
+                return d[name]
+        raise AttributeError(name)
+
+    def __setattr__(self, name, value):
+        d = self.__dict__
+        if name in _MIRROR_SET and d.get("_mode") == "packed" and d.get("_eng_live"):
+            self._materialise()                # the rest of the state must exist when this one is overridden
+            d["_touched"] = True
+        super().__setattr__(name, value)
+
+    def packed_engine(self):
+        """The PokerGPUPacked engine while it is authoritative (helpers such as HandStats read it directly)."""
+        if self._mode == "packed" and self._eng_live:
+            self._sync()
+        return self._eng if self._mode == "packed" and self._eng_live else None
+
+    def _record_live(self):
+        d, ver = self.__dict__, self.__dict__["_ver"]
+        for n in _LIVE:
+            t = d[n]
+            ver[n] = (t, t._version)
+
+    def _materialise(self):
+        d = self.__dict__
+        if d["_materialised"] is not None:
+            return
+        eng = d["_eng"]
+        names = tuple(n for n in _MIRROR if n not in _LIVE)
+        out = eng.unpack_into(eng.alloc_mirror(names, full=True), full=True)
+        for n, t in out.items():
+            d[n] = t
+            d["_ver"][n] = (t, t._version)
+        N, i32 = self.n_games, dict(dtype=torch.int32, device=self.device)
+        d["button_pos"] = out["button"][0]
+        d["prev_stacks"], d["raise_amounts"] = torch.zeros(N, **i32), torch.zeros(N, **i32)
+        d["active_player_idx"] = torch.arange(int(self.active_players), **i32)
+        d["_materialised"] = names
+
+    def _sync(self):
+        """Start of every call in packed mode: did the caller write to / rebind any exposed tensor?  Yes -> carry on
+        from the reference-shaped tensors.  No -> drop the snapshot (the next packed launch makes it stale)."""
+        d = self.__dict__
+        changed = d["_touched"]
+        if not changed:
+            for n, (t, v) in d["_ver"].items():
+                if d.get(n) is not t or t._version != v:
+                    changed = True
+                    break
+        if changed:
+            self._go_compat()
+            return
+        if d["_materialised"] is not None:
+            for n in d["_materialised"]:
+                d.pop(n, None)
+                d["_ver"].pop(n, None)
+            for n in _DERIVED:
+                d.pop(n, None)
+            d["_materialised"] = None
+
+    def _go_compat(self):
+        d = self.__dict__
+        if d["_mode"] != "packed" or not d["_eng_live"]:
+            return
+        self._materialise()
+        d["_mode"], d["_touched"], d["_materialised"] = "compat", False, None
+        d["_ver"] = {}
+        d["stacks"] = d["stacks"].contiguous()   # [N, P] row-major copy of the seat-major view
+        if d["prev_invested"] is None:
+            d["prev_invested"] = torch.zeros(self.n_games, dtype=torch.int32, device=self.device)
+
+    # ---- reset / step -------------------------------------------------------------------------------------------
+    def reset(self, seed=None, options=None, rotation=0):
+        d = self.__dict__
+        if d["_force_compat"]:
+            return super().reset(seed=seed, options=options, rotation=rotation)
+        from .poker_packed import PokerGPUPacked
+
+        N, dev = self.n_games, self.device
+        if d["_eng"] is None:
+            d["_eng"] = PokerGPUPacked(dev, agents=None, n_players=self.n_players, max_players=self.max_players,
+                                       n_games=N, starting_bbs=self.starting_bbs, max_bbs=self.max_bbs, seed=self.seed_value,
+                                       env_base=self.env_base, live_info=True, track_prev_invested=True)
+        eng = d["_eng"]
+        if d["_mode"] == "packed" and d["_eng_live"]:
+            self._sync()
+        flags = 0
+        if d["_mode"] == "compat":
+            # what persists across resets in the reference: the stacks (:101-110) and the button (:121)
+            stacks = d.get("stacks")
+            if stacks is None:
+                flags |= 1
+            else:
+                eng._stack.copy_(self._tensor("stacks", torch.int32).t())
+            if "button_pos" in d:
+                eng._tbl[:, 0] = (self._tensor("button", torch.int32) & 15) << 11
+            else:
+                flags |= 2
+        for n in ("w1", "w2", "K", "alpha"):
+            setattr(eng, n, d["_host_" + n])
+        eng._hand_counter = self._hand_counter
+        eng.obs = torch.empty((N, self.obs_size), dtype=torch.float32, device=dev)   # fresh every reset, as the reference
+        if seed is not None:
+            d["seed_value"] = int(seed)
+        eng.reset(seed=seed, options=options, rotation=rotation, first_flags=flags)
+        d["_hand_counter"] = eng._hand_counter
+        for n in _MIRROR + _DERIVED:
+            d.pop(n, None)
+        d["_ver"], d["_materialised"], d["_touched"] = {}, None, False
+        d["active_players"] = eng.active_players
+        d["stacks"], d["idx"], d["prev_invested"] = eng._stack.t(), eng._idx, eng._prev_inv
+        d["is_done"] = torch.zeros(N, dtype=torch.bool, device=dev)
+        d["obs"] = eng.obs
+        d["_mode"], d["_eng_live"] = "packed", True
+        self._record_live()
+        return self.obs, self.get_info()
+
+    def step(self, actions):
+        d = self.__dict__
+        if d["_mode"] == "packed" and d["_eng_live"]:
+            if "calculate_equities" in d:      # replaced per instance: it must be what step() calls
+                self._go_compat()
+            else:
+                self._sync()
+        if d["_mode"] == "compat":
+            return super().step(actions)
+        a = self._actions(actions)
+        eng, N, dev = d["_eng"], self.n_games, self.device
+        rewards = torch.empty(N, dtype=torch.float32, device=dev)
+        done = torch.empty(N, dtype=torch.bool, device=dev)   # the reference rebinds is_done every step (:623)
+        for n in ("w1", "w2", "K", "alpha"):
+            setattr(eng, n, d["_host_" + n])
+        eng.step_into(a, d["obs"], rewards, done)
+        d["is_done"] = done
+        d["_ver"]["is_done"] = (done, done._version)
+        return d["obs"], rewards, done, self.is_truncated, self.get_info()
+
+    # ---- the reference's internal methods: white-box callers work on the reference-shaped tensors ----------------
+    def get_obs(self):
+        if self._mode == "packed" and self._eng_live:
+            self._sync()
+            if self._mode == "packed":
+                return self.obs            # current by construction: nothing was written since the last launch
+        return super().get_obs()
+
+    def calculate_equities(self):
+        self._go_compat()
+        return super().calculate_equities()
+
+    def execute_actions(self, actions):
+        self._go_compat()
+        return super().execute_actions(actions)
+
+    def resolve_fold_winners(self):
+        self._go_compat()
+        return super().resolve_fold_winners()
+
+    def resolve_terminated_games(self):
+        self._go_compat()
+        return super().resolve_terminated_games()
+
+    def poker_reward_gpu(self, actions, actor_idx):
+        self._go_compat()
+        return super().poker_reward_gpu(actions, actor_idx)

@@ -1,9 +1,14 @@
 """PokerGPU on the packed HBM layout: same rules, same reset/step API and return tuples as
 `pulselib_b200.envs.poker.PokerGPU` (the drop-in for /root/reference/environments/Poker/PokerGPU.py),
 but the per-table state is kept in the 52 B (heads-up) packed structure-of-arrays form described in
-csrc/poker_packed_body.cuh instead of one int32 tensor per field.  This is the throughput path:
-training loops that only consume (obs, reward, done, info) can use it unchanged; code that reaches
-into env.stacks / env.status etc. gets read-only snapshots through `unpack()` / attribute access.
+csrc/poker_packed_body.cuh instead of one int32 tensor per field.  This is the throughput engine:
+training loops that only consume (obs, reward, done, info) can use it unchanged -- info["stacks"] is a
+live [N, P] view of the seat-major stack array and info["seat_idx"] a live int32 [N] tensor the step
+kernel keeps current, so `info["seat_idx"] == q_seat` and build_actions
+(/root/reference/environments/Poker/utils.py:108-123) work as they do on the reference.  Code that
+reaches into env.status / env.board etc. gets read-only snapshots through `unpack()` / attribute access;
+the registered drop-in `Pulse-Poker-GPU-v1` (envs/poker.py::PokerGPU) wraps this engine and adds
+writable mirrors of every reference attribute.
 """
 from __future__ import annotations
 
@@ -20,7 +25,7 @@ from .poker import _Config, _State, _STATE_FIELDS, device_hand_ranks
 
 class _Packed(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "ev", "hand_ctr", "hand_ranks")] + \
-               [("n_hand_ranks", C.c_int64)]
+               [("n_hand_ranks", C.c_int64), ("idx", C.c_void_p), ("prev_invested", C.c_void_p)]
 
 
 _SNAPSHOT = ("stacks", "status", "idx", "agg", "acted", "highest", "last_raise_size", "current_round_bet",
@@ -33,7 +38,8 @@ class PokerGPUPacked(gym.Env):
     ACTIVE, FOLDED, ALLIN, SITOUT = 0, 1, 2, 3
 
     def __init__(self, device, agents=None, n_players=6, max_players=10, n_games=100, starting_bbs=100, max_bbs=1000,
-                 w1=.5, w2=.5, K=20, alpha=300, seed=0, env_base=0, auto_reset=False):
+                 w1=.5, w2=.5, K=20, alpha=300, seed=0, env_base=0, auto_reset=False, live_info=True,
+                 track_prev_invested=False):
         super().__init__()
         self.device = dev = _lib.require_cuda(device)
         self._lib = _lib.load()
@@ -63,10 +69,18 @@ class PokerGPUPacked(gym.Env):
         self._ev = torch.zeros((P, N), dtype=torch.int64, device=dev)
         self.obs = torch.zeros((N, self.obs_size), dtype=torch.float32, device=dev)
         self.is_truncated = torch.zeros(N, dtype=torch.bool, device=dev)
-        self._first = True
+        self._first = self._restart_tape = True
+        # live mirrors the step kernel keeps current: the seat to act (info["seat_idx"], 4 B per table-step) and,
+        # for the drop-in class only, the reference's prev_invested scratch (PokerGPU.py:539)
+        self._idx = torch.zeros(N, dtype=torch.int32, device=dev) if live_info else None
+        self._prev_inv = torch.zeros(N, dtype=torch.int32, device=dev) if track_prev_invested else None
+        self._prefixed = None
+        self._stepped = False
         self._packed = _Packed(self._tbl.data_ptr(), self._tbl2.data_ptr(), self._stack.data_ptr(),
                                self._crb.data_ptr(), self._inv.data_ptr(), self._hole.data_ptr(), self._ev.data_ptr(),
-                               self._hand_ctr.data_ptr(), self.hand_ranks.data_ptr(), self.hand_ranks.numel())
+                               self._hand_ctr.data_ptr(), self.hand_ranks.data_ptr(), self.hand_ranks.numel(),
+                               self._idx.data_ptr() if live_info else None,
+                               self._prev_inv.data_ptr() if track_prev_invested else None)
 
     def set_agents(self, agents):
         self.agents = agents
@@ -78,9 +92,11 @@ class PokerGPUPacked(gym.Env):
     def state_bytes_per_table(self) -> int:
         return 24 + 22 * self.n_players  # 14 B/seat touched every step + 8 B/seat of per-deal hand values
 
-    def reset(self, seed=None, options=None, rotation=0):
+    def reset(self, seed=None, options=None, rotation=0, first_flags=None):
+        """first_flags (internal, used by the drop-in class): overrides bits 0-1 of pulse_poker_packed_reset's
+        first_reset (bit 0 fresh stacks, bit 1 button 0)."""
         if seed is not None:
-            self.seed_value, self._hand_counter = int(seed), 0
+            self.seed_value, self._hand_counter, self._restart_tape = int(seed), 0, True
         options = options or {}
         N, P, dev = self.n_games, self.n_players, self.device
         if options.get("active_players", False):
@@ -94,15 +110,18 @@ class PokerGPUPacked(gym.Env):
             if tuple(prefixed.shape) != (N, 52):
                 raise ValueError(f"prefixed_decks must have shape {(N, 52)}, got {tuple(prefixed.shape)}")
             prefixed = prefixed.contiguous()
-        rot = 0 if self._first else int(options.get("rotation", rotation))
+        flags = (3 if self._first else 0) if first_flags is None else int(first_flags)
+        rot = 0 if flags & 1 else int(options.get("rotation", rotation))
         cfg = self._config()
         with _lib.device_guard(dev):
             _lib.check(self._lib.pulse_poker_packed_reset(
                 C.byref(self._packed), C.byref(cfg), ptr(prefixed), c_u64(self.seed_value), c_u64(self.env_base),
-                c_u32(self._hand_counter), c_i(rot), c_i(3 if self._first else 0), ptr(self.obs),
-                _lib.cuda_stream(dev)), "pulse_poker_packed_reset")
-        self._first = False
+                c_u32(self._hand_counter), c_i(rot), c_i(flags | (4 if self._restart_tape else 0)),
+                ptr(self.obs), _lib.cuda_stream(dev)), "pulse_poker_packed_reset")
+        self._first = self._restart_tape = False
         self._hand_counter += 1
+        self._prefixed = prefixed   # the mirror's decks come from here (or from the tape)
+        self._stepped = False
         return self.obs, self.get_info()
 
     def step_into(self, actions, obs, rewards, done):
@@ -113,6 +132,7 @@ class PokerGPUPacked(gym.Env):
                 C.byref(self._packed), C.byref(cfg), ptr(actions), ptr(obs), ptr(rewards), ptr(done),
                 c_i(1 if self.auto_reset else 0), c_u64(self.seed_value), c_u64(self.env_base),
                 _lib.cuda_stream(self.device)), "pulse_poker_packed_step")
+        self._stepped = True
 
     def step(self, actions):
         a = torch.as_tensor(actions, device=self.device)
@@ -165,6 +185,7 @@ class PokerGPUPacked(gym.Env):
                 ptr(chosen), ptr(seat), ptr(obs), ptr(rewards), ptr(done), c_i(1 if self.auto_reset else 0),
                 c_u64(self.seed_value), c_u64(self.env_base), _lib.cuda_stream(dev)), "pulse_poker_packed_step_policy")
         self._done = done
+        self._stepped = True
         info = self.get_info()
         info["actions"] = chosen
         if return_seat:
@@ -183,31 +204,56 @@ class PokerGPUPacked(gym.Env):
         return out
 
     def get_info(self):
-        # seat_idx / stacks are what build_actions and the trainers read (environments/Poker/utils.py:108-123)
-        return {"active_players": self.active_players, "stacks": _Lazy(self, "stacks"), "seat_idx": _Lazy(self, "idx")}
+        # what build_actions and the trainers read (environments/Poker/utils.py:108-123, scripts/Poker/trainGPU.py:75-96):
+        # real tensors -- `info["seat_idx"] == q_seat` is a bool tensor, `info["stacks"][:, q_seat]` a row of the
+        # seat-major stack array
+        seat = self._idx if self._idx is not None else self.unpack(("idx",))["idx"]
+        return {"active_players": self.active_players, "stacks": self._stack.t(), "seat_idx": seat}
 
-    def unpack(self) -> dict:
-        """Reference-shaped int32 snapshot of the packed state (one kernel launch)."""
+    def alloc_mirror(self, fields=None, full=False) -> dict:
+        """Fresh reference-shaped tensors (shapes / dtypes of SURVEY.md 8(a)) for `fields`."""
         N, P, dev = self.n_games, self.n_players, self.device
+        AP = int(self.active_players)
         i32 = dict(dtype=torch.int32, device=dev)
-        out = {n: torch.zeros(N, **i32) for n in ("deck_positions", "pots", "stages", "button", "sb", "bb", "idx",
-                                                  "highest", "agg", "acted", "last_raise_size", "prev_invested")}
-        out.update({n: torch.zeros((N, P), **i32) for n in ("stacks", "current_round_bet", "total_invested", "status")})
-        out["decks"] = torch.zeros((1,), **i32)
-        out["board"] = torch.zeros((N, 5), **i32)
-        out["hands"] = torch.zeros((N, P, 2), **i32)
-        out["is_done"] = torch.zeros(N, dtype=torch.bool, device=dev)
-        out["equity_dirty"] = torch.zeros(1, dtype=torch.bool, device=dev)
-        out["equities"] = torch.zeros(1, dtype=torch.float32, device=dev)
+        shapes = {n: (N,) for n in ("deck_positions", "pots", "stages", "button", "sb", "bb", "idx", "highest", "agg",
+                                    "acted", "last_raise_size", "prev_invested")}
+        shapes.update({n: (N, P) for n in ("stacks", "current_round_bet", "total_invested", "status")})
+        shapes.update(board=(N, 5), hands=(N, P, 2))
+        if full:
+            shapes["decks"] = (N, 52)
+        names = fields if fields is not None else tuple(shapes) + ("is_done", "equity_dirty", "equities")
+        out = {}
+        for n in names:
+            if n in ("is_done", "equity_dirty"):
+                out[n] = torch.empty(N, dtype=torch.bool, device=dev)
+            elif n == "equities":
+                out[n] = torch.empty((N, AP), dtype=torch.float32, device=dev)
+            else:
+                out[n] = torch.empty(shapes[n], **i32)
+        return out
+
+    def unpack_into(self, out: dict, full=False):
+        """Fills the given reference-shaped tensors from the packed state (one launch).  full: also decks (re-drawn
+        from the tape or copied from the last reset's prefixed decks) -- pulse_poker_unpack_full."""
         s = _State()
         for name in _STATE_FIELDS:
-            setattr(s, name, (self.hand_ranks if name == "hand_ranks" else out[name]).data_ptr())
+            t = self.hand_ranks if name == "hand_ranks" else out.get(name)
+            setattr(s, name, None if t is None else t.data_ptr())
         s.n_hand_ranks = self.hand_ranks.numel()
-        cfg = self._config()
+        cfg, dev = self._config(), self.device
         with _lib.device_guard(dev):
-            _lib.check(self._lib.pulse_poker_unpack(C.byref(self._packed), C.byref(s), C.byref(cfg),
-                                                    _lib.cuda_stream(dev)), "pulse_poker_unpack")
-        return {k: out[k] for k in _SNAPSHOT}
+            if full:
+                _lib.check(self._lib.pulse_poker_unpack_full(
+                    C.byref(self._packed), C.byref(s), C.byref(cfg), ptr(self._prefixed), c_u64(self.seed_value),
+                    c_u64(self.env_base), c_i(0 if self._stepped else 1), _lib.cuda_stream(dev)), "pulse_poker_unpack_full")
+            else:
+                _lib.check(self._lib.pulse_poker_unpack(C.byref(self._packed), C.byref(s), C.byref(cfg),
+                                                        _lib.cuda_stream(dev)), "pulse_poker_unpack")
+        return out
+
+    def unpack(self, fields=None) -> dict:
+        """Reference-shaped int32 snapshot of the packed state (one kernel launch)."""
+        return self.unpack_into(self.alloc_mirror(fields if fields is not None else _SNAPSHOT))
 
     def __getattr__(self, name):
         if name in _SNAPSHOT:
@@ -216,24 +262,3 @@ class PokerGPUPacked(gym.Env):
 
     def close(self):
         return None
-
-
-class _Lazy:
-    """info['stacks'] / info['seat_idx'] materialised only if the caller actually reads them."""
-
-    def __init__(self, env, field):
-        self._env, self._field = env, field
-
-    def _get(self):
-        return getattr(self._env, self._field)
-
-    def __getattr__(self, name):
-        return getattr(self._get(), name)
-
-    def __getitem__(self, i):
-        return self._get()[i]
-
-    @classmethod
-    def __torch_function__(cls, func, types, args=(), kwargs=None):
-        args = tuple(a._get() if isinstance(a, _Lazy) else a for a in args)
-        return func(*args, **(kwargs or {}))

@@ -63,11 +63,19 @@ class HandStats:
         self.vec = torch.zeros(LEN, dtype=torch.float64, device=self.device)
         self.terminated = torch.zeros(env.n_games, dtype=torch.bool, device=self.device)
         self.initial = torch.zeros(env.n_games, dtype=torch.int32, device=self.device)
-        self._packed = hasattr(env, "_packed")
+
+    def _engine(self):
+        """The packed engine behind `env` while it is authoritative (PokerGPUPacked itself, or the drop-in PokerGPU
+        in packed mode), else None: the reference-shaped tensors are read."""
+        env = self.env
+        if hasattr(env, "packed_engine"):
+            return env.packed_engine()
+        return env if hasattr(env, "_packed") else None
 
     def _q_stacks(self):
-        if self._packed:
-            return self.env._stack[self.q_seat]
+        eng = self._engine()
+        if eng is not None:
+            return eng._stack[self.q_seat]
         return self.env.stacks[:, self.q_seat]
 
     def begin_hand(self):
@@ -84,10 +92,11 @@ class HandStats:
             rearm = bool(getattr(self.env, "auto_reset", False))
         env, dev = self.env, self.device
         done = done if done.dtype == torch.bool and done.is_contiguous() else done.to(torch.bool).contiguous()
+        eng = self._engine()
         with _lib.device_guard(dev):
-            if self._packed:
-                cfg = env._config()
-                rc = self._lib.pulse_poker_packed_hand_stats(C.byref(env._packed), C.byref(cfg), ptr(done),
+            if eng is not None:
+                cfg = eng._config()
+                rc = self._lib.pulse_poker_packed_hand_stats(C.byref(eng._packed), C.byref(cfg), ptr(done),
                                                              ptr(self.terminated), ptr(self.initial), c_i(self.q_seat),
                                                              c_i(1 if rearm else 0), ptr(self.vec), _lib.cuda_stream(dev))
             else:

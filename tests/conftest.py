@@ -10,6 +10,7 @@ if str(ROOT) not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "refslow: re-runs the live reference head to head (build container, PULSE_REFSLOW=1)")
 
 
 @pytest.fixture(scope="session")

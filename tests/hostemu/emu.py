@@ -94,7 +94,7 @@ class EmuPoker:
 
 class PackedStruct(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("tbl", "tbl2", "stack", "crb", "inv", "hole", "ev", "hand_ctr", "hand_ranks")] + \
-               [("n_hand_ranks", C.c_int64)]
+               [("n_hand_ranks", C.c_int64), ("idx", C.c_void_p), ("prev_invested", C.c_void_p)]
 
 
 class EmuPokerPacked(EmuPoker):
@@ -113,6 +113,9 @@ class EmuPokerPacked(EmuPoker):
         self.hand_ctr = np.zeros(N, np.uint32)
         self.pev = np.zeros((P, N), np.uint64)
         self.auto_reset, self.seed, self.env_base = auto_reset, seed, env_base
+        self.live_idx = np.zeros(N, np.int32)
+        self.live_prev_inv = np.zeros(N, np.int32)
+        self._prefixed, self._stepped = None, False
 
     def _packed(self):
         s = PackedStruct()
@@ -121,22 +124,29 @@ class EmuPokerPacked(EmuPoker):
         s.hand_ctr = self.hand_ctr.ctypes.data
         s.ev = self.pev.ctypes.data
         s.hand_ranks, s.n_hand_ranks = self.hand_ranks.ctypes.data, self.hand_ranks.size
+        s.idx, s.prev_invested = self.live_idx.ctypes.data, self.live_prev_inv.ctypes.data
         return s
 
     def _unpack(self):
+        """the full mirror (pulse_poker_unpack_full): every reference attribute, decks included"""
         s, c = self._packed(), self._state()
-        lib().emu_poker_unpack(C.byref(s), C.byref(c), C.byref(self.cfg))
+        lib().emu_poker_unpack_full(C.byref(s), C.byref(c), C.byref(self.cfg), p(self._prefixed), C.c_uint64(self.seed),
+                                    C.c_uint64(self.env_base), C.c_int(0 if self._stepped else 1))
 
     def reset(self, decks=None, active_players=None, rotation=0, seed=None, env_base=None, hand=0):
         self.active_players = active_players or self.n_players
         self.cfg.active_players = self.active_players
         s = self._packed()
         d = None if decks is None else np.ascontiguousarray(decks, dtype=np.int32)
-        lib().emu_poker_packed_reset(C.byref(s), C.byref(self.cfg), p(d),
-                                     C.c_uint64(self.seed if seed is None else seed),
-                                     C.c_uint64(self.env_base if env_base is None else env_base), C.c_uint32(hand),
-                                     C.c_int(rotation), C.c_int(3 if self._first else 0), p(self.obs))
+        if seed is not None:
+            self.seed = seed
+        if env_base is not None:
+            self.env_base = env_base
+        lib().emu_poker_packed_reset(C.byref(s), C.byref(self.cfg), p(d), C.c_uint64(self.seed),
+                                     C.c_uint64(self.env_base), C.c_uint32(hand),
+                                     C.c_int(rotation), C.c_int(7 if self._first else 0), p(self.obs))
         self._first = False
+        self._prefixed, self._stepped = d, False
         self._unpack()
         return self.obs
 
@@ -145,6 +155,7 @@ class EmuPokerPacked(EmuPoker):
         s = self._packed()
         lib().emu_poker_packed_step(C.byref(s), C.byref(self.cfg), p(a), p(self.obs), p(self.rewards), p(self.is_done),
                                     C.c_int(self.auto_reset), C.c_uint64(self.seed), C.c_uint64(self.env_base))
+        self._stepped = True
         self._unpack()
         return self.obs, self.rewards, self.is_done.astype(bool)
 

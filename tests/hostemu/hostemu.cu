@@ -101,6 +101,14 @@ int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, 
     EMU_DISPATCH(pr.P, (packed_unpack_one<MP>(*st, *compat, pr, g, (long long)cfg->n_games)));
   return 0;
 }
+int emu_poker_unpack_full(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
+                          const int32_t* prefixed, uint64_t seed, uint64_t env_base, int fresh) {
+  PokerParams pr = mk(cfg);
+  for (long long g = 0; g < cfg->n_games; ++g)
+    EMU_DISPATCH(pr.P, (packed_unpack_one<MP>(*st, *compat, pr, g, (long long)cfg->n_games, true, prefixed, seed,
+                                              env_base, fresh != 0)));
+  return 0;
+}
 
 // ---- Blackjack ----
 int emu_blackjack_reset(uint32_t* st, uint8_t* deck, const uint8_t* injected, uint64_t seed, uint64_t env_base,

@@ -94,7 +94,12 @@ def golden_kwargs(name):
                 w1=float(z["w"][0]), w2=float(z["w"][1]))
 
 
-def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, alpha=50, check_equities=True):
+# every reference attribute the packed layout's mirror rebuilds (pulse_poker_unpack_full)
+MIRROR_FIELDS = INT_N + INT_NP + ("board", "hands", "sb", "bb", "prev_invested", "decks", "equity_dirty")
+
+
+def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, alpha=50, check_equities=True,
+                           fields=INT_N + INT_NP + ("board", "hands")):
     """Runs engines a and b on the same decks/actions; all integer state must match exactly."""
     for h in range(hands):
         ap = int(rng.integers(2, P + 1)) if vary_ap else P
@@ -103,13 +108,13 @@ def random_rollout_compare(a, b, rng, P, N, hands, steps, vary_ap=False, rot=0, 
         oa = a.reset(decks, active_players=ap, rotation=r)
         ob = b.reset(decks, active_players=ap, rotation=r)
         np.testing.assert_array_equal(to_np(oa), to_np(ob), err_msg=f"reset obs hand {h}")
-        compare_state(a, b, f"reset hand {h}")
+        compare_state(a, b, f"reset hand {h}", fields)
         for t in range(steps):
             acts = rng.integers(0, 13, N).astype(np.int64)
             oa, ra, da = a.step(acts)
             ob, rb, db = b.step(acts)
             tag = f"hand {h} step {t}"
-            compare_state(a, b, tag)
+            compare_state(a, b, tag, fields)
             np.testing.assert_array_equal(to_np(da).astype(bool), to_np(db).astype(bool), err_msg=tag + " done")
             np.testing.assert_array_equal(to_np(oa), to_np(ob), err_msg=tag + " obs")
             if check_equities:

@@ -63,7 +63,8 @@ def test_reference_live_if_available(hr_table):
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
 def test_packed_kernel_body_hostbuild_matches_reference_golden(name, hr_table):
-    pu.replay_golden(name, EmuPokerPacked(hr_table, **pu.golden_kwargs(name)), check_equities=False)
+    # the packed layout keeps no equity tensor: its mirror (pulse_poker_unpack_full) rebuilds the reference's cache
+    pu.replay_golden(name, EmuPokerPacked(hr_table, **pu.golden_kwargs(name)))
 
 
 @pytest.mark.parametrize("P,M,N,vary,rot", [(2, 2, 3000, False, 0), (6, 6, 1500, False, 1), (10, 10, 800, True, 3),
@@ -72,4 +73,4 @@ def test_packed_kernel_body_hostbuild_matches_oracle_random(P, M, N, vary, rot, 
     kw = dict(n_players=P, max_players=M, n_games=N, starting_bbs=50, max_bbs=200, w1=.5, w2=.3, K=100, alpha=50)
     rng = np.random.default_rng(P * 10 + M)
     pu.random_rollout_compare(EmuPokerPacked(hr_table, **kw), pyoracle.OraclePoker(hr_table, **kw), rng, P, N, 5, 45,
-                              vary_ap=vary, rot=rot, check_equities=False)
+                              vary_ap=vary, rot=rot, fields=pu.MIRROR_FIELDS)
