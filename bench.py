@@ -31,6 +31,11 @@ WORKLOADS = {
     "poker_6max": dict(n_players=6, max_players=6, tables=4_194_304, algo_bytes=401, hand_len=24),
     # the reference's own training default (PokerGPU.py:20, scripts/Poker/trainGPU.py:177-188)
     "poker_10max": dict(n_players=10, max_players=10, tables=4_194_304, algo_bytes=601, hand_len=32),
+    # the same heads-up workload through the registered drop-in: gym.make("Pulse-Poker-GPU-v1") and the env-facing
+    # part of the reference's loop body (scripts/Poker/trainGPU.py:79-96): the q-seat mask from info["seat_idx"],
+    # env.step(actions) returning fresh reward / done tensors, terminated |= dones.  +4 B per table-step: the live
+    # seat index the step kernel keeps for info["seat_idx"], and 4 B for the reference's prev_invested attribute.
+    "poker_hu_dropin": dict(n_players=2, max_players=2, tables=4_194_304, algo_bytes=201, hand_len=16, dropin=True),
 }
 
 
@@ -80,6 +85,33 @@ class ClockSampler(threading.Thread):
                 pass
             self.stop_flag.wait(0.1)
 
+    def sample_once(self):
+        """One synchronous sample (taken under load, right before the timed region starts), so the record is never
+        empty even when the timed region is shorter than the sampler's period."""
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons") \
+                else pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            flags = [bool(r & pynvml.nvmlClocksThrottleReasonHwSlowdown), bool(r & pynvml.nvmlClocksThrottleReasonHwThermalSlowdown),
+                     bool(r & pynvml.nvmlClocksThrottleReasonSwThermalSlowdown), bool(r & pynvml.nvmlClocksThrottleReasonSwPowerCap)]
+            self.samples.append([str(sm), str(mx)] + ["Active" if f else "Not Active" for f in flags])
+            return
+        except Exception:
+            pass
+        try:
+            out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                  "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+            f = [x.strip() for x in out.strip().split(",")]
+            if len(f) >= 6:
+                self.samples.append(f)
+        except Exception:
+            pass
+
     def summary(self):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -88,6 +120,15 @@ class ClockSampler(threading.Thread):
         reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
                 "samples": len(sm)}
+
+
+def workload_config(name, wl, tables):
+    """`config` of the JSON line: identical for this repo's arm and for --impl reference (engine details live in
+    the line's other keys)."""
+    return {"workload": f"{name}: PokerGPU n_players={wl['n_players']}, {tables} tables/GPU, uniform random actions 0..12, "
+                        f"whole-batch reset every {wl['hand_len']} steps inside the timed region (reference step "
+                        f"convention: every table counted every step)",
+            "tables_per_gpu": tables, "hand_len": wl["hand_len"]}
 
 
 def cpu_baseline(wl, min_seconds=10.0, tables=1 << 20):
@@ -129,13 +170,13 @@ def run_reference(args, wl, name):
     if rank != 0:
         return
     per_step = max(1.0, 20.0 / max(1, args.steps + args.warmup))
-    base, spent, steps = cpu_baseline(wl, min_seconds=min(60.0, per_step * (args.steps + args.warmup)))
+    tables = int(args.tables or wl["tables"])            # the full configuration, as this repo's arm
+    base, spent, steps = cpu_baseline(wl, min_seconds=min(60.0, per_step * (args.steps + args.warmup)), tables=tables)
     line = {"impl": "reference", "metric": "env-steps/sec (PokerGPU NLHE)", "value": base["value"],
             "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * spent / max(1, steps) * wl["tables"], "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": 1e3 * spent / max(1, steps) * tables, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": {"workload": f"{name}: PokerGPU n_players={wl['n_players']}, {wl['tables']} tables/GPU, "
-                                   f"uniform random actions 0..12, hands of {wl['hand_len']} steps"},
+            "config": workload_config(name, wl, tables),
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -176,7 +217,16 @@ def run_gpu(args, wl, name):
 
     N, L = int(args.tables or wl["tables"]), wl["hand_len"]
     P, M = wl["n_players"], wl["max_players"]
-    env = PokerGPUPacked(dev, n_players=P, max_players=M, n_games=N, seed=SEED, env_base=rank * N, **CFG)
+    dropin = bool(wl.get("dropin"))
+    if dropin:
+        from pulselib_b200 import registration
+        from pulselib_b200.gym_compat import gym
+
+        registration.register_all()
+        env = gym.make("Pulse-Poker-GPU-v1", device=dev, agents=[], n_players=P, max_players=M, n_games=N, seed=SEED,
+                       env_base=rank * N, **CFG)
+    else:
+        env = PokerGPUPacked(dev, n_players=P, max_players=M, n_games=N, seed=SEED, env_base=rank * N, live_info=False, **CFG)
     gen = torch.Generator(device=dev)
     gen.manual_seed(SEED + rank)
     actions = torch.randint(0, 13, (L, N), dtype=torch.int64, device=dev, generator=gen)
@@ -186,16 +236,34 @@ def run_gpu(args, wl, name):
     stream = torch.cuda.current_stream(dev)
     launches = [0]
 
+    loop = {"info": None, "terminated": torch.zeros(N, dtype=torch.bool, device=dev), "done": done}
+
+    def one_step(j):
+        if dropin:      # the env-facing part of the reference's loop body
+            q_mask = loop["info"]["seat_idx"] == 0
+            _, _, d, _, loop["info"] = env.step(actions[j])
+            loop["terminated"] |= d
+            loop["done"], loop["q_mask"] = d, q_mask
+        else:
+            env.step_into(actions[j], obs, rew, done)
+
+    def one_reset():
+        if dropin:
+            _, loop["info"] = env.reset(options={"active_players": False, "rotation": 0})
+            loop["terminated"].zero_()
+        else:
+            env.reset()
+
     def run_steps(k, start, pairs=None):
         for i in range(k):
             j = (start + i) % L
             if j == 0:
-                env.reset()
+                one_reset()
                 launches[0] += 1
             if pairs is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
-            env.step_into(actions[j], obs, rew, done)
+            one_step(j)
             launches[0] += 1
             if pairs is not None:
                 e1.record(stream)
@@ -208,16 +276,17 @@ def run_gpu(args, wl, name):
         torch.cuda.synchronize(dev)
 
     # live-step fraction of the workload (untimed): tables not yet done when each step begins
-    env.reset()
+    one_reset()
     live = 0.0
     for j in range(L):
-        live += 1.0 if j == 0 else float((~done).float().mean())
-        env.step_into(actions[j], obs, rew, done)
+        live += 1.0 if j == 0 else float((~loop["done"]).float().mean())
+        one_step(j)
     live_fraction = live / L
 
     run_steps(args.warmup, 0)
-    barrier()
     sampler = ClockSampler(local)
+    sampler.sample_once()        # while the warm-up steps are still running on the device
+    barrier()
     sampler.start()
     launches[0] = 0
     pairs = []
@@ -236,45 +305,82 @@ def run_gpu(args, wl, name):
     total_ms, kernel_ms = float(ms.item()), float(kern_ms.item())
     n_launch = launches[0]
 
-    # end to end through the public API with HOST buffers: pinned actions -> device, env.step(),
-    # obs/reward/done -> pinned host, every step, `chunks` independent envs on their own streams so
-    # the PCIe copies of one chunk overlap the step of another.
-    chunks = max(1, args.e2e_chunks)
-    Nc = N // chunks
-    e2e_steps = min(args.steps, 2 * L)
-    envs = [PokerGPUPacked(dev, n_players=P, max_players=M, n_games=Nc, seed=SEED, env_base=rank * N + c * Nc, **CFG)
-            for c in range(chunks)]
-    streams = [torch.cuda.Stream(dev) for _ in range(chunks)]
-    h_act = torch.randint(0, 13, (L, chunks, Nc), dtype=torch.int64).pin_memory()
-    h_obs = torch.empty((chunks, Nc, env.obs_size), dtype=torch.float32).pin_memory()
-    h_rew = torch.empty((chunks, Nc), dtype=torch.float32).pin_memory()
-    h_done = torch.empty((chunks, Nc), dtype=torch.bool).pin_memory()
-    d_act = [torch.empty(Nc, dtype=torch.int64, device=dev) for _ in range(chunks)]
+    # End to end with HOST buffers through the repo's host-buffer API (pulselib_b200.host_env.PokerHostEnv ->
+    # pulse_poker_host_step): numpy actions in, the reference's float32 observations / rewards / dones out in numpy
+    # arrays, every step, host<->device copies inside the timed region.  1 B per table goes in, one packed record per
+    # live table comes back and is expanded by native host threads (csrc/host_env.cu).  Host-synchronous API, so the
+    # region is timed by wall clock with a device synchronise on both sides.
+    import numpy as np
 
-    def e2e_steps_run(k, start):
+    from pulselib_b200.host_env import PokerHostEnv
+
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    threads = args.e2e_threads or max(1, avail // max(1, local_world))
+    e2e_steps = min(args.steps, 4 * L)
+    # The path's only collective: one more hand on the device with the run statistics accumulated by
+    # pulse_stats_accumulate every step, then ONE sum all-reduce of the vector over NCCL, checked against an
+    # all_gather of the per-rank vectors.  Outside every timed region.
+    from pulselib_b200.sharding import RunStats
+
+    rs = RunStats(dev)
+    one_reset()
+    for j in range(L):
+        one_step(j)
+        if dropin:
+            pass                                          # the drop-in's step returns fresh reward tensors; not kept here
+        else:
+            rs.update(rew, done)
+    dev_stats = rs.all_reduce()
+    if dist is not None and not dropin:
+        parts = [torch.zeros_like(rs.vec) for _ in range(world)]
+        dist.all_gather(parts, rs.vec)
+        assert torch.equal(torch.stack(parts).sum(0), dev_stats), "NCCL all-reduce of RunStats != sum of gathered vectors"
+    if not dropin:
+        assert int(dev_stats[0].item()) == world * N * L, "env_steps of the reduced statistics != ranks * tables * steps"
+    dev_stats = dev_stats.tolist()
+    del obs, rew, done, actions                       # the device-timed leg's buffers
+    torch.cuda.empty_cache()
+    henv = PokerHostEnv(dev, n_players=P, max_players=M, n_games=N, seed=SEED, env_base=rank * N, chunks=args.e2e_chunks,
+                        threads=threads, **CFG)
+    h_act = np.random.default_rng(SEED + rank).integers(0, 13, (L, N)).astype(np.uint8)
+    h2d = d2h = 0
+
+    def host_steps(k, start, count=False):
+        nonlocal h2d, d2h
         for i in range(k):
             j = (start + i) % L
-            for c in range(chunks):
-                with torch.cuda.stream(streams[c]):
-                    if j == 0:
-                        envs[c].reset()
-                    d_act[c].copy_(h_act[j, c], non_blocking=True)
-                    o, r, d, _, _ = envs[c].step(d_act[c])
-                    h_obs[c].copy_(o, non_blocking=True)
-                    h_rew[c].copy_(r, non_blocking=True)
-                    h_done[c].copy_(d, non_blocking=True)
+            if j == 0:
+                henv.reset()
+                if count:
+                    d2h += henv.info()["last_d2h_bytes"]
+            henv.step(h_act[j])
+            if count:
+                inf = henv.info()
+                h2d += inf["last_h2d_bytes"]; d2h += inf["last_d2h_bytes"]
 
-    e2e_steps_run(3, 0)
+    host_steps(L, 0)
     barrier()
     w0 = time.perf_counter()
-    e2e_steps_run(e2e_steps, 0)
-    for s in streams:
-        s.synchronize()
+    host_steps(e2e_steps, 0, count=True)
+    torch.cuda.synchronize(dev)
     e2e_ms = torch.tensor([(time.perf_counter() - w0) * 1e3], dtype=torch.float64, device=dev)
     barrier()
     if dist is not None:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
-    e2e_value = world * Nc * chunks * e2e_steps / (float(e2e_ms.item()) * 1e-3)
+    e2e_value = world * N * e2e_steps / (float(e2e_ms.item()) * 1e-3)
+    # the statistics vector of this leg, summed over ranks with the one collective the path has
+    stats_local = torch.tensor([float(N * e2e_steps), float(henv.dones.sum()), float(henv.rewards.astype(np.float64).sum())],
+                               dtype=torch.float64, device=dev)
+    stats_all = stats_local.clone()
+    if dist is not None:
+        dist.all_reduce(stats_all, op=dist.ReduceOp.SUM)
+        gathered = [torch.zeros_like(stats_local) for _ in range(world)]
+        dist.all_gather(gathered, stats_local)
+        assert torch.allclose(torch.stack(gathered).sum(0), stats_all), "all-reduce of the run statistics disagrees with the gathered sum"
+    assert int(stats_all[0].item()) == world * N * e2e_steps
+    hinfo = henv.info()
+    henv.close()
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -290,15 +396,25 @@ def run_gpu(args, wl, name):
             "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int32", "data": "synthetic",
-            "config": {"workload": f"{name}: PokerGPU n_players={P}, {N} tables/GPU, uniform random actions 0..12, "
-                                   f"whole-batch reset every {L} steps inside the timed region (reference step "
-                                   f"convention: every table counted every step)",
-                       "tables_per_gpu": N, "hand_len": L, "layout": "packed", "parallelism": f"env-sharded x{world}",
-                       "l2": "inputs larger than L2 (state+obs+actions per step > 126 MB)",
-                       "live_step_fraction": round(live_fraction, 4)},
-            "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": N * 8,
-                    "d2h_bytes_per_step": N * (4 * env.obs_size + 4 + 1), "steps": e2e_steps, "chunks": chunks,
-                    "timing": "wall clock around the host loop, all streams synchronised"},
+            "config": workload_config(name, wl, N),
+            "engine": {"layout": "packed",
+                       "api": "gym.make('Pulse-Poker-GPU-v1') + the env-facing loop body of scripts/Poker/trainGPU.py:79-96"
+                       if dropin else "PokerGPUPacked.step_into", "parallelism": f"env-sharded x{world}",
+                       "l2": "inputs larger than L2 (state+obs+actions per step > 126 MB)"},
+            "live_step_fraction": round(live_fraction, 4),
+            "live_env_steps_per_s": world * N * args.steps / (total_ms * 1e-3) * live_fraction,
+            "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d / e2e_steps,
+                    "d2h_bytes_per_step": d2h / e2e_steps, "steps": e2e_steps, "chunks": hinfo["chunks"],
+                    "host_threads": hinfo["threads"], "record_bytes": hinfo["row_bytes"],
+                    "api": "pulselib_b200.host_env.PokerHostEnv.step (pulse_poker_host_step): numpy uint8 actions in, "
+                           "float32 obs [N,%d] + float32 reward + bool done out in host memory every step, whole-batch "
+                           "reset every %d steps; records of live tables only cross PCIe and are expanded by host threads" % (env.obs_size, L),
+                    "reference_contract_bytes_per_table_step": 8 + 4 * env.obs_size + 4 + 1,
+                    "timing": "wall clock around the host loop (the API is host-synchronous), device synchronised on both sides"},
+            "run_stats_device": dict(zip(("env_steps", "episodes_done", "reward_sum", "reward_sq_sum"), dev_stats)),
+            "run_stats_allreduce": {"env_steps": stats_all[0].item(), "done_flags_at_end": stats_all[1].item(),
+                                    "reward_sum_at_end": stats_all[2].item(), "ranks": world,
+                                    "collective": "nccl all_reduce(sum) of the statistics vector, checked against all_gather" if world > 1 else "single rank"},
             "gpu_launches": n_launch,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "poker_packed_step_kernel", "kernel_ms": kernel_ms,
@@ -408,7 +524,8 @@ def main():
                     choices=sorted(WORKLOADS) + ["tfe_4x4", "tetris", "particle2d", "blackjack", "poker_hu_scripted", "poker_hu_train_loop"])
     ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` block of the poker line")
     ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")
-    ap.add_argument("--e2e-chunks", type=int, default=4)
+    ap.add_argument("--e2e-chunks", type=int, default=8)
+    ap.add_argument("--e2e-threads", type=int, default=0, help="host expander threads per rank (0 = online CPUs / local ranks)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU-baseline sample length (0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -81,6 +81,11 @@ int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, cons
                    uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
                    uint8_t* done_inout, int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
 int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, int side, pulse_stream_t stream);
+/* Domain audit of the packed boards (tile exponents up to 15 = 32768; two 32768 tiles meeting stay unmerged where the
+ * reference would make 65536).  counts2 int [2] on the device, accumulated: [0] += boards holding a 32768 tile,
+ * [1] += boards holding two or more (one move away from leaving the packed domain).  Random play never gets near
+ * (a 32768 tile takes > 10^4 moves); long-running learned policies should poll it. */
+int pulse_tfe_domain_check(const uint64_t* boards, int* counts2, int n_envs, pulse_stream_t stream);
 /* int32 tile values -> packed boards (+ their game-over flags); *bad_count_or_null is incremented for
  * every board holding a value that is not 0 or a power of two in 2..32768 */
 int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, uint8_t* done_out_or_null, int* bad_count_or_null,
@@ -283,6 +288,39 @@ int pulse_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat
 int pulse_poker_unpack_full(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg,
                             const int32_t* prefixed_decks_or_null, uint64_t seed, uint64_t env_base, int fresh,
                             pulse_stream_t stream);
+
+/* ---- PokerGPU with HOST buffers (the end-to-end path) -----------------------------------------------
+ * The reference's step contract (PokerGPU.py:527-633: int64 actions in; float32 [N, 13 + 3 (M - 1)] observations,
+ * float32 rewards, bool dones out) for callers whose arrays live in host memory.  Per table-step 1 B goes to the
+ * device (the action id) and, only for tables that were live when the step began, one packed record comes back
+ * (csrc/poker_wire.cuh: 24 / 40 / 56 B for 2 / 6 / 10 seats, compacted in table order); a pool of host threads
+ * expands the records into the caller's arrays.  A table that was already finished keeps its row in obs_host (the
+ * reference returns the same row for it), reward 0, done 1 -- so the SAME obs / reward / done arrays must be passed to
+ * every call of one env (the reference's `self.obs` is one buffer too, :176-179).  The arrays may be pageable.
+ * The handle owns device state, pinned staging buffers, streams (one per chunk: copies and kernels of chunk c+1 overlap
+ * the expansion of chunk c) and threads.  Unlike the rest of this header these calls allocate (create), block until
+ * the outputs are complete (reset / step) and use their own streams.  Whole-batch hands only (no auto_reset).
+ * Requires n_players * max_bbs < 16384 (every chip count must fit the record) and (n_players, max_players) in
+ * {(2,2), (3..4,4), (5..6,6), (7..10,10)}; other shapes use the device-buffer API above.
+ * host_hand_ranks: the HandRanks table (pulse_handranks_generate), at least its first 36,875 entries.
+ * n_chunks / n_threads < 1: 1 chunk / one thread per online CPU. */
+typedef struct PulsePokerHostEnv PulsePokerHostEnv;
+int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg, const int32_t* host_hand_ranks,
+                            size_t n_hand_ranks, uint64_t seed, uint64_t env_base, int device, int n_chunks,
+                            int n_threads);
+void pulse_poker_host_destroy(PulsePokerHostEnv* env);
+/* reset (PokerGPU.py:73-157) with decks from the chance tape; active_players = the table size of this hand */
+int pulse_poker_host_reset(PulsePokerHostEnv* env, int active_players, int rotation, float* obs_host,
+                           float* reward_host_or_null, uint8_t* done_host_or_null);
+/* step (:527-633); actions_host: uint8 [N] (action_bytes 1) or int64 [N] (action_bytes 8) */
+int pulse_poker_host_step(PulsePokerHostEnv* env, const void* actions_host, int action_bytes, float* obs_host,
+                          float* reward_host, uint8_t* done_host);
+/* record size, observation width, chunk / thread counts, and the bytes the last call moved over PCIe */
+int pulse_poker_host_info(const PulsePokerHostEnv* env, int* row_bytes, int* obs_width, int* chunks, int* threads,
+                          long long* last_h2d_bytes, long long* last_d2h_bytes);
+/* pure host function: n_rows packed records -> float32 rows [n_rows, 13 + 3 (M - 1)], rewards, dones */
+int pulse_poker_wire_expand_host(const uint64_t* rows, long long n_rows, int active_players, int max_players,
+                                 float* obs_out, float* reward_out, uint8_t* done_out);
 
 /* ---- run statistics (the vector that is all-reduced across GPUs) -------------------
  * stats4 double [4] on the device: += {n, number of done flags set, sum(reward), sum(reward^2)}.

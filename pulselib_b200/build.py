@@ -51,17 +51,33 @@ def is_stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
+    """Serialised across processes by a file lock (torchrun starts one process per GPU, every one of which may find
+    the library stale): the first builds, the others wait and find it fresh."""
     if not force and not is_stale():
         return LIB_PATH
-    nvcc = _nvcc()
+    import fcntl
+
     OBJ_DIR.mkdir(exist_ok=True)
+    with open(OBJ_DIR / ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not is_stale():      # another process built it while this one waited
+                return LIB_PATH
+            return _build_locked(force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(force: bool, verbose: bool) -> Path:
+    nvcc = _nvcc()
     hdr_t = _headers_mtime()
 
     def compile_one(src: Path) -> Path:
         obj = OBJ_DIR / (src.stem + ".o")
         if not force and obj.exists() and obj.stat().st_mtime > max(src.stat().st_mtime, hdr_t):
             return obj
-        cmd = [nvcc, *NVCC_FLAGS, "-x", "cu", "-c", str(src), "-o", str(obj)]
+        tmp_obj = OBJ_DIR / f"{src.stem}.{os.getpid()}.o.tmp"
+        cmd = [nvcc, *NVCC_FLAGS, "-x", "cu", "-c", str(src), "-o", str(tmp_obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)
@@ -69,12 +85,13 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             raise RuntimeError(f"nvcc failed for {src.name}:\n{r.stdout}\n{r.stderr}")
         if verbose:
             sys.stderr.write(r.stderr)
+        os.replace(tmp_obj, obj)
         return obj
 
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         objs = list(ex.map(compile_one, _sources()))
-    tmp = LIB_PATH.with_suffix(".so.tmp")
-    cmd = [nvcc, "-shared", "-o", str(tmp), *map(str, objs), "-Xcompiler", "-fPIC", "-lcudart"]
+    tmp = LIB_PATH.with_suffix(f".so.{os.getpid()}.tmp")
+    cmd = [nvcc, "-shared", "-o", str(tmp), *map(str, objs), "-Xcompiler", "-fPIC", "-lcudart", "-lpthread"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -3,6 +3,8 @@
 #include <stdarg.h>
 #include <stdio.h>
 
+#include <atomic>
+
 static thread_local char g_err[512] = "";
 
 void pulse_set_error(const char* fmt, ...) {
@@ -21,8 +23,19 @@ int pulse_check_launch(const char* what) {
   return PULSE_OK;
 }
 
+int pulse_sm_count(void) {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n > 0) return n;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  cache[dev].store(n, std::memory_order_relaxed);
+  return n;
+}
+
 extern "C" {
-int pulse_version(void) { return 100; }
+int pulse_version(void) { return 200; }
 const char* pulse_last_error(void) { return g_err; }
 
 // Fills out[0..3] with one block of the chance tape (host side; used by callers that want to

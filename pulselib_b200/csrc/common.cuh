@@ -5,7 +5,7 @@
 //   philox4x32_10(counter = {env_id_lo, env_id_hi, draw_counter, stream_tag},
 //                 key     = {seed_lo, seed_hi})
 // so results depend only on (seed, global env id, counter) and never on grid shape,
-// GPU count or launch order.  oracle/pulse_oracle.c holds an independent restatement.
+// GPU count or launch order.  oracle/oracle_core.c holds an independent restatement.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -23,6 +23,7 @@
 
 void pulse_set_error(const char* fmt, ...);
 int pulse_check_launch(const char* what);
+int pulse_sm_count(void);   // multiprocessors of the current device (cudaDevAttrMultiProcessorCount, cached); 148 on B200
 
 #define PULSE_REQUIRE(cond, msg)                      \
   do {                                                \
@@ -151,11 +152,11 @@ __device__ __forceinline__ void pulse_mbar_wait(uint64_t* bar, uint32_t phase) {
 }
 #endif
 
-// Grid sizing: B200 has 148 SMs; grids are a whole number of waves where the problem is big
-// enough, otherwise just enough CTAs to cover it.
+// Grid sizing: grids are a whole number of waves (SM count x resident CTAs; 148 SMs on B200) where the problem is
+// big enough, otherwise just enough CTAs to cover it.
 static inline int pulse_grid_for(long long n, int block, int ctas_per_sm = 8) {
   long long need = (n + block - 1) / block;
-  long long wave = 148LL * ctas_per_sm;
+  long long wave = (long long)pulse_sm_count() * ctas_per_sm;
   if (need <= wave) return (int)(need > 0 ? need : 1);
   long long waves = (need + wave - 1) / wave;
   return (int)(waves * wave);  // grid-stride loops absorb the tail

@@ -1,0 +1,463 @@
+// PokerGPU with HOST buffers: the end-to-end path (include/pulse_envs.h, "host-buffer PokerGPU").
+//
+// The reference's step contract -- int64 actions in, float32 [N, 13 + 3 (M - 1)] observations, float32 rewards and
+// bool done flags out (/root/reference/environments/Poker/PokerGPU.py:527-633) -- for callers whose arrays live in host
+// memory.  What crosses PCIe is not that contract (8 B in, 69 B out per table-step heads-up) but:
+//   in   1 B per table (the action id, 0..12) + 4 B per 32 tables (where the warp's records go)
+//   out  one packed record (poker_wire.cuh: 24 B heads-up) per table that was LIVE when the step began, compacted
+// and a pool of host threads expands the records into the caller's arrays with streaming stores.  A table that was
+// already finished repeats its row (the caller's buffer keeps it), reward 0, done 1 -- exactly what the reference
+// returns for it.  The batch is cut into chunks, each on its own stream: chunk c+1's copies and step kernel run while
+// the threads expand chunk c.
+//
+// The handle owns its device state (the packed layout of poker_packed_body.cuh), pinned staging buffers, streams and
+// threads; the caller's arrays may be pageable.  One handle = one env on one GPU; calls on one handle are serial.
+#include "poker_packed_body.cuh"
+
+#include <emmintrin.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <new>
+#include <thread>
+#include <vector>
+
+namespace {
+
+constexpr int kBlock = 128;
+
+// ---- device side ------------------------------------------------------------------------------------------------
+// Step in wire mode: uint8 actions, no float32 observation / reward / done arrays at all; a table that was live when
+// the step began writes its record to slot warp_off[warp] + (rank among the warp's live lanes).  The host knows which
+// tables are live (it expanded the previous step's done flags) and sends the offsets with the actions, so the device
+// needs no scan, the records are in table order, and the host knows the copy size before the kernel has run.
+template <int MAXP, int MT, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB)
+poker_host_step_kernel(PulsePokerPacked S, PokerParams pr, const uint8_t* __restrict__ actions,
+                       const uint32_t* __restrict__ warp_off, uint64_t* __restrict__ wire, int starting_bbs,
+                       int max_bbs, long long first, long long last, long long n) {
+  // one chunk of the batch: tables first .. last-1 (first a multiple of 1024); the seat-major arrays keep the whole
+  // batch's stride n; warp_off and wire are the chunk's own
+  constexpr int R = (18 + 4 * (MT - 1) + 7) / 8;
+  pr.M = MT;
+  const unsigned lane = threadIdx.x & 31u;
+  for (long long base = first + (long long)blockIdx.x * kBlock; base < last; base += (long long)gridDim.x * kBlock) {
+    const long long g = base + threadIdx.x;
+    uint64_t w[R];
+    bool live = false;
+    uint32_t off = 0;
+    if (g < last) {
+      off = warp_off[(g - first) >> 5];
+      PokerTable<MAXP> t;
+      const PackedStepResult r = packed_step_core<MAXP, false, 0, uint8_t>(S, pr, actions, 0, 0, 0, starting_bbs, max_bbs,
+                                                                           g, n, nullptr, t);
+      live = !r.was_done;
+      if (live) pkw_pack_row<MAXP, MT>(t, pr, r.reward, w);
+    }
+    const unsigned bal = __ballot_sync(0xFFFFFFFFu, live);
+    if (live) {
+      uint64_t* dst = wire + ((size_t)off + __popc(bal & ((1u << lane) - 1u))) * R;
+#pragma unroll
+      for (int i = 0; i < R; ++i) dst[i] = w[i];
+    }
+  }
+}
+
+// After a whole-batch deal: every table's record, uncompacted (slot = table), reward 0.
+template <int MAXP, int MT>
+__global__ void __launch_bounds__(kBlock)
+poker_host_rows_kernel(PulsePokerPacked S, PokerParams pr, uint64_t* __restrict__ wire, long long n) {
+  constexpr int R = (18 + 4 * (MT - 1) + 7) / 8;
+  pr.M = MT;
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
+    PokerTable<MAXP> t;
+    uint32_t fb;
+    packed_load(t, fb, S, g, n, pr.AP);
+    uint64_t w[R];
+    pkw_pack_row<MAXP, MT>(t, pr, 0.0f, w);
+#pragma unroll
+    for (int i = 0; i < R; ++i) wire[(size_t)g * R + i] = w[i];
+  }
+}
+
+// ---- host side: a small persistent thread pool ------------------------------------------------------------------
+class Pool {
+ public:
+  explicit Pool(int n) : n_(n < 1 ? 1 : n) {
+    for (int i = 1; i < n_; ++i) th_.emplace_back([this, i] { loop(i); });
+  }
+  ~Pool() {
+    { std::lock_guard<std::mutex> lk(m_); stop_ = true; ++gen_; }
+    cv_.notify_all();
+    for (auto& t : th_) t.join();
+  }
+  int size() const { return n_; }
+  // fn(worker) on every worker, the caller being worker 0; returns when all are done
+  void run(const std::function<void(int)>& fn) {
+    if (n_ == 1) { fn(0); return; }
+    { std::lock_guard<std::mutex> lk(m_); fn_ = &fn; pending_ = n_ - 1; ++gen_; }
+    cv_.notify_all();
+    fn(0);
+    std::unique_lock<std::mutex> lk(m_);
+    done_cv_.wait(lk, [this] { return pending_ == 0; });
+  }
+
+ private:
+  void loop(int id) {
+    unsigned long long seen = 0;
+    for (;;) {
+      const std::function<void(int)>* fn;
+      {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [&] { return gen_ != seen; });
+        seen = gen_;
+        if (stop_) return;
+        fn = fn_;
+      }
+      (*fn)(id);
+      { std::lock_guard<std::mutex> lk(m_); if (--pending_ == 0) done_cv_.notify_one(); }
+    }
+  }
+  int n_;
+  std::vector<std::thread> th_;
+  std::mutex m_;
+  std::condition_variable cv_, done_cv_;
+  const std::function<void(int)>* fn_ = nullptr;
+  unsigned long long gen_ = 0;
+  int pending_ = 0;
+  bool stop_ = false;
+};
+
+inline void store16(float* p, __m128 v, bool nt) {
+  if (nt) _mm_stream_ps(p, v); else _mm_storeu_ps(p, v);
+}
+
+// heads-up record (3 words) -> 16 floats; 64 B rows go out as four 16 B (streaming) stores
+inline void expand_hu(const uint64_t* w, float* o, float* reward, uint8_t* done, bool nt) {
+  const uint64_t h = w[0], a = w[1], b = w[2];
+  auto card = [](uint64_t x) { int c = (int)(x & 63u); return c ? c : -1; };
+  const __m128i v0 = _mm_set_epi32(card(h >> 18), card(h >> 12), card(h >> 6), card(h));
+  const __m128i v1 = _mm_set_epi32((int)((h >> 42) & 7u), card(h >> 36), card(h >> 30), card(h >> 24));
+  const __m128i v2 = _mm_set_epi32((int)((a >> 32) & 0xFFFFu), (int)((a >> 16) & 0xFFFFu), (int)(a & 0xFFFFu), (int)((h >> 45) & 15u));
+  const uint32_t s = (uint32_t)(a >> 48);
+  const __m128i v3 = _mm_set_epi32((int)(b & 0xFFFFu), (int)(s >> 14), (int)(s & 0x3FFFu), (int)((h >> 49) & 3u));
+  store16(o, _mm_cvtepi32_ps(v0), nt); store16(o + 4, _mm_cvtepi32_ps(v1), nt);
+  store16(o + 8, _mm_cvtepi32_ps(v2), nt); store16(o + 12, _mm_cvtepi32_ps(v3), nt);
+  union { float f; uint32_t x; } rb;
+  rb.x = (uint32_t)(b >> 32);
+  *reward = rb.f;
+  *done = (uint8_t)((h >> 51) & 1u);
+}
+
+}  // namespace
+
+struct PulsePokerHostEnv {
+  PulsePokerConfig cfg;
+  int device = 0, chunks = 1, R = 3, W = 16;
+  uint64_t seed = 0, env_base = 0;
+  uint32_t hand_counter = 0;
+  bool first = true;
+  long long N = 0, Nc = 0;                 // tables, tables per chunk (a multiple of 1024; the last chunk may be short)
+  PulsePokerPacked st{};
+  std::vector<void*> dev_allocs, pin_allocs;
+  uint8_t* d_act = nullptr; uint32_t* d_off = nullptr; uint64_t* d_wire = nullptr;
+  uint8_t* h_act = nullptr; uint32_t* h_off = nullptr; uint64_t* h_wire = nullptr;
+  std::vector<uint32_t> live;              // bit b of live[w]: table 32 w + b was not done after the last call
+  std::vector<long long> chunk_rows;       // live tables per chunk at the start of the next step
+  std::vector<cudaStream_t> streams;
+  std::vector<cudaEvent_t> events;
+  Pool* pool = nullptr;
+  long long last_h2d = 0, last_d2h = 0;
+  ~PulsePokerHostEnv() {
+    delete pool;
+    cudaSetDevice(device);
+    for (auto s : streams) cudaStreamDestroy(s);
+    for (auto e : events) cudaEventDestroy(e);
+    for (auto p : dev_allocs) cudaFree(p);
+    for (auto p : pin_allocs) cudaFreeHost(p);
+  }
+};
+
+namespace {
+
+#define HE_CUDA(call)                                                       \
+  do {                                                                      \
+    cudaError_t e_ = (call);                                                \
+    if (e_ != cudaSuccess) {                                                \
+      pulse_set_error("%s: %s", #call, cudaGetErrorString(e_));             \
+      return (int)e_;                                                       \
+    }                                                                       \
+  } while (0)
+
+template <class T>
+int dev_alloc(PulsePokerHostEnv* e, T** p, size_t count) {
+  HE_CUDA(cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T) + 256));
+  e->dev_allocs.push_back(*p);
+  HE_CUDA(cudaMemset(*p, 0, count * sizeof(T)));
+  return 0;
+}
+template <class T>
+int pin_alloc(PulsePokerHostEnv* e, T** p, size_t count) {
+  HE_CUDA(cudaMallocHost(reinterpret_cast<void**>(p), count * sizeof(T) + 256));
+  e->pin_allocs.push_back(*p);
+  return 0;
+}
+
+PokerParams params_of(const PulsePokerConfig& c) {
+  PokerParams p; p.w1 = c.w1; p.w2 = c.w2; p.K = c.K; p.alpha = c.alpha;
+  p.P = c.n_players; p.AP = c.active_players; p.M = c.max_players;
+  return p;
+}
+
+#define HE_DISPATCH(P, M, CALL)                                                   \
+  do {                                                                            \
+    if ((P) <= 2 && (M) == 2) { constexpr int MP = 2, MT = 2; CALL; }             \
+    else if ((P) <= 4 && (M) == 4) { constexpr int MP = 4, MT = 4; CALL; }        \
+    else if ((P) <= 6 && (M) == 6) { constexpr int MP = 6, MT = 6; CALL; }        \
+    else if ((P) <= 10 && (M) == 10) { constexpr int MP = 10, MT = 10; CALL; }    \
+    else { pulse_set_error("host env: unsupported (n_players, max_players)"); return PULSE_EUNSUPPORTED; } \
+  } while (0)
+
+// Expands the records of tables [g0, g1) (g0 a multiple of 32) of one chunk.  rows: the chunk's records; off: the
+// chunk's per-warp offsets (nullptr: uncompacted, slot = table - chunk start).  Rewrites the live mask.
+void expand_range(PulsePokerHostEnv* e, long long chunk_first, long long g0, long long g1, const uint64_t* rows,
+                  const uint32_t* off, float* obs, float* reward, uint8_t* done, bool fresh) {
+  const int R = e->R, W = e->W, AP = e->cfg.active_players, M = e->cfg.max_players;
+  const bool hu = (R == 3 && W == 16 && AP == 2);
+  const bool nt = hu && ((reinterpret_cast<uintptr_t>(obs) & 15u) == 0);
+  for (long long wg = g0 >> 5; wg < ((g1 + 31) >> 5); ++wg) {
+    const long long gb = wg << 5;
+    const int cnt = (int)((g1 - gb) < 32 ? (g1 - gb) : 32);
+    const uint32_t mask = fresh ? 0xFFFFFFFFu : e->live[wg];
+    uint32_t next = 0;
+    size_t slot = off ? off[wg - (chunk_first >> 5)] : (size_t)(gb - chunk_first);
+    for (int b = 0; b < cnt; ++b) {
+      const long long g = gb + b;
+      if ((mask >> b) & 1u) {
+        const uint64_t* w = rows + slot * R;
+        ++slot;
+        uint8_t d;
+        if (hu) expand_hu(w, obs + g * 16, reward + g, &d, nt);
+        else pkw_expand_row(w, AP, M, obs + g * W, reward + g, &d);
+        done[g] = d;
+        next |= (uint32_t)(d ? 0u : 1u) << b;
+      } else {
+        reward[g] = 0.0f;                                  // PokerGPU.py:632; done stays 1, the row stays as it is
+      }
+    }
+    e->live[wg] = next;
+  }
+  if (nt) _mm_sfence();
+}
+
+// per-warp offsets of every chunk for the NEXT step, and the chunks' record counts
+void rebuild_offsets(PulsePokerHostEnv* e) {
+  e->pool->run([e](int wk) {
+    for (int c = wk; c < e->chunks; c += e->pool->size()) {
+      const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
+      uint32_t* off = e->h_off + (first >> 5) + c;           // each chunk has (Nc / 32 + 1) entries
+      uint32_t acc = 0;
+      for (long long wg = first >> 5; wg < ((last + 31) >> 5); ++wg) {
+        off[wg - (first >> 5)] = acc;
+        acc += (uint32_t)__builtin_popcount(e->live[wg]);
+      }
+      off[((last + 31) >> 5) - (first >> 5)] = acc;
+      e->chunk_rows[c] = acc;
+    }
+  });
+}
+
+template <int MP, int MT>
+void launch_step_t(PulsePokerHostEnv* e, const PokerParams& pr, long long first, long long cnt, const uint32_t* d_off,
+                   uint64_t* d_rows, cudaStream_t s) {
+  constexpr int MINB = MP <= 2 ? 8 : MP <= 6 ? 6 : 4;   // resident CTAs per SM, as for the float32-row step
+  poker_host_step_kernel<MP, MT, MINB><<<pulse_grid_for(cnt, kBlock), kBlock, 0, s>>>(
+      e->st, pr, e->d_act, d_off, d_rows, e->cfg.starting_bbs, e->cfg.max_bbs, first, first + cnt, e->N);
+}
+
+int launch_step(PulsePokerHostEnv* e, const PokerParams& pr, long long first, long long cnt, const uint32_t* d_off,
+                uint64_t* d_rows, cudaStream_t s) {
+  HE_DISPATCH(pr.P, pr.M, (launch_step_t<MP, MT>(e, pr, first, cnt, d_off, d_rows, s)));
+  return pulse_check_launch("pulse_poker_host_step");
+}
+
+int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* reward, uint8_t* done, bool fresh) {
+  for (int c = 0; c < e->chunks; ++c) {
+    HE_CUDA(cudaEventSynchronize(e->events[c]));
+    const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
+    const uint64_t* rows = e->h_wire + (size_t)first * e->R;
+    const uint32_t* off = compacted ? e->h_off + (first >> 5) + c : nullptr;
+    e->pool->run([=](int wk) {
+      const int T = e->pool->size();
+      const long long per = (((last - first) + T - 1) / T + 31) & ~31LL;
+      const long long g0 = first + wk * per, g1 = (g0 + per < last) ? g0 + per : last;
+      if (g0 < g1) expand_range(e, first, g0, g1, rows, off, obs, reward, done, fresh);
+    });
+  }
+  rebuild_offsets(e);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg, const int32_t* host_hand_ranks,
+                            size_t n_hand_ranks, uint64_t seed, uint64_t env_base, int device, int n_chunks,
+                            int n_threads) {
+  PULSE_REQUIRE(out && cfg, "null argument");
+  *out = nullptr;
+  PULSE_REQUIRE(cfg->n_players >= 2 && cfg->n_players <= 10, "n_players must be in 2..10");
+  PULSE_REQUIRE(cfg->active_players >= 2 && cfg->active_players <= cfg->n_players, "active_players must be in 2..n_players");
+  PULSE_REQUIRE(cfg->n_games > 0, "n_games must be positive");
+  PULSE_REQUIRE((long long)cfg->n_players * cfg->max_bbs < 16384 && cfg->starting_bbs <= cfg->max_bbs,
+                "n_players * max_bbs must be below 16384 for the packed records (use the device-buffer API otherwise)");
+  PULSE_REQUIRE(host_hand_ranks && n_hand_ranks >= 36875, "the HandRanks table (at least its first 36,875 entries) is required");
+  const int P = cfg->n_players, M = cfg->max_players;
+  if (!((P <= 2 && M == 2) || (P > 2 && P <= 4 && M == 4) || (P > 4 && P <= 6 && M == 6) || (P > 6 && M == 10))) {
+    pulse_set_error("host env supports max_players 2, 4, 6 or 10 with n_players in the matching bracket");
+    return PULSE_EUNSUPPORTED;
+  }
+  PulsePokerHostEnv* e = new (std::nothrow) PulsePokerHostEnv();
+  PULSE_REQUIRE(e != nullptr, "out of memory");
+  e->cfg = *cfg; e->device = device; e->seed = seed; e->env_base = env_base;
+  e->N = cfg->n_games; e->R = pkw_row_words(M); e->W = 13 + 3 * (M - 1);
+  if (n_chunks < 1) n_chunks = 1;
+  long long nc = ((e->N + n_chunks - 1) / n_chunks + 1023) & ~1023LL;
+  e->Nc = nc; e->chunks = (int)((e->N + nc - 1) / nc);
+  if (n_threads < 1) { n_threads = (int)std::thread::hardware_concurrency(); if (n_threads < 1) n_threads = 1; }
+  int rc = 0;
+  auto fail = [&](int code) { delete e; return code; };
+  if (cudaSetDevice(device) != cudaSuccess) { pulse_set_error("cudaSetDevice(%d) failed", device); return fail(PULSE_EINVAL); }
+  const size_t N = (size_t)e->N, PN = N * P;
+  int32_t* hr = nullptr;
+  if ((rc = dev_alloc(e, &e->st.tbl, 4 * N)) || (rc = dev_alloc(e, &e->st.tbl2, 2 * N)) || (rc = dev_alloc(e, &e->st.stack, PN)) ||
+      (rc = dev_alloc(e, &e->st.crb, PN)) || (rc = dev_alloc(e, &e->st.inv, PN)) || (rc = dev_alloc(e, &e->st.hole, PN)) ||
+      (rc = dev_alloc(e, &e->st.ev, PN)) || (rc = dev_alloc(e, &e->st.hand_ctr, N)) || (rc = dev_alloc(e, &hr, 36875)) ||
+      (rc = dev_alloc(e, &e->d_act, N)) || (rc = dev_alloc(e, &e->d_off, N / 32 + 2 * e->chunks + 2)) ||
+      (rc = dev_alloc(e, &e->d_wire, N * e->R)) || (rc = pin_alloc(e, &e->h_act, N)) ||
+      (rc = pin_alloc(e, &e->h_off, N / 32 + 2 * e->chunks + 2)) || (rc = pin_alloc(e, &e->h_wire, N * e->R)))
+    return fail(rc);
+  if (cudaMemcpy(hr, host_hand_ranks, 36875 * sizeof(int32_t), cudaMemcpyHostToDevice) != cudaSuccess) {
+    pulse_set_error("uploading the HandRanks prefix failed"); return fail(PULSE_EINVAL);
+  }
+  e->st.hand_ranks = hr; e->st.n_hand_ranks = 36875; e->st.idx = nullptr; e->st.prev_invested = nullptr;
+  e->live.assign(N / 32 + 2, 0u);
+  e->chunk_rows.assign(e->chunks, 0);
+  for (int c = 0; c < e->chunks; ++c) {
+    cudaStream_t s; cudaEvent_t ev;
+    if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) {
+      pulse_set_error("stream / event creation failed"); return fail(PULSE_EINVAL);
+    }
+    e->streams.push_back(s); e->events.push_back(ev);
+  }
+  e->pool = new Pool(n_threads);
+  *out = e;
+  return PULSE_OK;
+}
+
+void pulse_poker_host_destroy(PulsePokerHostEnv* env) { delete env; }
+
+int pulse_poker_host_reset(PulsePokerHostEnv* e, int active_players, int rotation, float* obs_host, float* reward_host_or_null,
+                           uint8_t* done_host_or_null) {
+  PULSE_REQUIRE(e && obs_host, "null argument");
+  PULSE_REQUIRE(active_players >= 2 && active_players <= e->cfg.n_players, "active_players must be in 2..n_players");
+  HE_CUDA(cudaSetDevice(e->device));
+  e->cfg.active_players = active_players;
+  const PokerParams pr = params_of(e->cfg);
+  // the deal (no float32 observation), then every table's record
+  int rc = pulse_poker_packed_reset(&e->st, &e->cfg, nullptr, e->seed, e->env_base, e->hand_counter, e->first ? 0 : rotation,
+                                    (e->first ? 3 : 0) | (e->first ? 4 : 0), nullptr, e->streams[0]);
+  if (rc) return rc;
+  e->first = false;
+  e->hand_counter += 1;
+  const int grid = pulse_grid_for(e->N, kBlock);
+  HE_DISPATCH(pr.P, pr.M, (poker_host_rows_kernel<MP, MT><<<grid, kBlock, 0, e->streams[0]>>>(e->st, pr, e->d_wire, e->N)));
+  rc = pulse_check_launch("pulse_poker_host_reset");
+  if (rc) return rc;
+  HE_CUDA(cudaEventRecord(e->events[0], e->streams[0]));
+  for (int c = 0; c < e->chunks; ++c) {
+    const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
+    if (c > 0) HE_CUDA(cudaStreamWaitEvent(e->streams[c], e->events[0], 0));
+    HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, e->d_wire + (size_t)first * e->R, (size_t)cnt * e->R * 8,
+                            cudaMemcpyDeviceToHost, e->streams[c]));
+  }
+  // events[0] must complete after chunk 0's copy: re-record in order
+  for (int c = 0; c < e->chunks; ++c) HE_CUDA(cudaEventRecord(e->events[c], e->streams[c]));
+  e->last_h2d = 0; e->last_d2h = (long long)e->N * e->R * 8;
+  // reward / done scratch when the caller does not want them
+  std::vector<float> rtmp; std::vector<uint8_t> dtmp;
+  float* rw = reward_host_or_null; uint8_t* dn = done_host_or_null;
+  if (!rw) { rtmp.resize((size_t)e->N); rw = rtmp.data(); }
+  if (!dn) { dtmp.resize((size_t)e->N); dn = dtmp.data(); }
+  return expand_chunks(e, false, obs_host, rw, dn, true);
+}
+
+int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int action_bytes, float* obs_host,
+                          float* reward_host, uint8_t* done_host) {
+  PULSE_REQUIRE(e && actions_host && obs_host && reward_host && done_host, "null argument");
+  PULSE_REQUIRE(action_bytes == 1 || action_bytes == 8, "action_bytes must be 1 (uint8) or 8 (int64)");
+  PULSE_REQUIRE(!e->first, "reset first");
+  HE_CUDA(cudaSetDevice(e->device));
+  const PokerParams pr = params_of(e->cfg);
+  // stage the actions in pinned memory as bytes
+  e->pool->run([=](int wk) {
+    const int T = e->pool->size();
+    const long long per = ((e->N + T - 1) / T + 63) & ~63LL;
+    const long long a = wk * per, b = (a + per < e->N) ? a + per : e->N;
+    if (action_bytes == 1) {
+      if (a < b) memcpy(e->h_act + a, static_cast<const uint8_t*>(actions_host) + a, (size_t)(b - a));
+    } else {
+      const int64_t* src = static_cast<const int64_t*>(actions_host);
+      // ids above 12 all behave like 13 (a raise of nothing, PokerGPU.py:255-273), negative ids match no branch (255)
+      for (long long i = a; i < b; ++i) { const int64_t v = src[i]; e->h_act[i] = v < 0 ? (uint8_t)255 : v > 12 ? (uint8_t)13 : (uint8_t)v; }
+    }
+  });
+  long long h2d = 0, d2h = 0;
+  for (int c = 0; c < e->chunks; ++c) {
+    const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
+    const long long n_off = ((cnt + 31) >> 5) + 1;
+    cudaStream_t s = e->streams[c];
+    uint32_t* d_off = e->d_off + (first >> 5) + c;
+    HE_CUDA(cudaMemcpyAsync(e->d_act + first, e->h_act + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
+    HE_CUDA(cudaMemcpyAsync(d_off, e->h_off + (first >> 5) + c, (size_t)n_off * 4, cudaMemcpyHostToDevice, s));
+    h2d += cnt + n_off * 4;
+    uint64_t* d_rows = e->d_wire + (size_t)first * e->R;
+    int rc = launch_step(e, pr, first, cnt, d_off, d_rows, s);
+    if (rc) return rc;
+    const size_t bytes = (size_t)e->chunk_rows[c] * e->R * 8;
+    if (bytes) HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, d_rows, bytes, cudaMemcpyDeviceToHost, s));
+    d2h += (long long)bytes;
+    HE_CUDA(cudaEventRecord(e->events[c], s));
+  }
+  e->last_h2d = h2d; e->last_d2h = d2h;
+  return expand_chunks(e, true, obs_host, reward_host, done_host, false);
+}
+
+int pulse_poker_host_info(const PulsePokerHostEnv* e, int* row_bytes, int* obs_width, int* chunks, int* threads,
+                          long long* last_h2d_bytes, long long* last_d2h_bytes) {
+  PULSE_REQUIRE(e != nullptr, "null env");
+  if (row_bytes) *row_bytes = e->R * 8;
+  if (obs_width) *obs_width = e->W;
+  if (chunks) *chunks = e->chunks;
+  if (threads) *threads = e->pool->size();
+  if (last_h2d_bytes) *last_h2d_bytes = e->last_h2d;
+  if (last_d2h_bytes) *last_d2h_bytes = e->last_d2h;
+  return PULSE_OK;
+}
+
+// pure host function (no GPU): one record -> the reference's float32 row; exported for tests and for callers that
+// keep the compact records and expand rows on demand
+int pulse_poker_wire_expand_host(const uint64_t* rows, long long n_rows, int active_players, int max_players,
+                                 float* obs_out, float* reward_out, uint8_t* done_out) {
+  PULSE_REQUIRE(rows && obs_out && reward_out && done_out, "null argument");
+  PULSE_REQUIRE(max_players >= 2 && max_players <= 16 && active_players >= 2 && active_players <= max_players, "bad table size");
+  const int R = pkw_row_words(max_players), W = 13 + 3 * (max_players - 1);
+  for (long long i = 0; i < n_rows; ++i)
+    pkw_expand_row(rows + (size_t)i * R, active_players, max_players, obs_out + (size_t)i * W, reward_out + i, done_out + i);
+  return PULSE_OK;
+}
+}

@@ -28,6 +28,7 @@
 #pragma once
 #include "poker_core.cuh"
 #include "poker_policy.cuh"
+#include "poker_wire.cuh"
 
 #define PKP_REDEAL_MARK 0x80000000u  // top bit of hand_ctr: table waits for the redeal pass
 
@@ -354,28 +355,34 @@ struct PackedPolicy {
 // AUTO: what a table that was already done when the step began does -- 0 nothing (stays done), 1 deal inline
 // (host emulation of the semantics), 2 mark for the redeal pass (device).  A compile-time choice so the plain
 // step kernel carries no shuffle / evaluator code at all.
-template <int MAXP, bool POLICY = false, int AUTO = 1>
-PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, const int64_t* __restrict__ actions,
-                              float* __restrict__ obs_row, float* __restrict__ reward_out,
-                              uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
-                              int starting_bbs, int max_bbs, long long g, long long n,
-                              const PackedPolicy* pol = nullptr) {
+// Result of packed_step_core: what the step did to one table, for the caller to write out (float32 observation row
+// + reward + done arrays, or one compact wire row).
+struct PackedStepResult {
+  float reward;
+  bool was_done;   // the table was already finished when the step began (PokerGPU.py:530)
+  bool done;       // done flag to report
+};
+
+template <int MAXP, bool POLICY = false, int AUTO = 1, class ActT = int64_t>
+PULSE_HD PackedStepResult packed_step_core(const PulsePokerPacked& S, const PokerParams& pr, const ActT* __restrict__ actions,
+                                           int auto_reset, uint64_t seed, uint64_t env_base, int starting_bbs, int max_bbs,
+                                           long long g, long long n, const PackedPolicy* pol, PokerTable<MAXP>& t) {
   const int P = pr.P, AP = pr.AP;
-  PokerTable<MAXP> t;
   uint32_t fb;
   PackedEv<MAXP, (MAXP <= 2)> evw{S.ev, g, n};
   evw.prefetch(AP);
   long long a = 0;
 #ifdef __CUDA_ARCH__
-  if (!POLICY) a = *reinterpret_cast<const volatile long long*>(actions + g);  // first of the ordered first-level loads
+  if (!POLICY) a = (long long)*reinterpret_cast<const volatile ActT*>(actions + g);  // first of the ordered first-level loads
 #else
-  if (!POLICY) a = actions[g];
+  if (!POLICY) a = (long long)actions[g];
 #endif
+  if (sizeof(ActT) == 1 && a == 255) a = -1;   // byte-wide action ids: 255 stands for "negative" (matches no branch)
   packed_load(t, fb, S, g, n, AP);
   if (POLICY) {  // build_actions: computed from the pre-step state for every table, done or not (utils.py:108-123)
     const int kind = pol->kinds.kind[t.idx & 15];
     if (kind == PULSE_AGENT_EXTERNAL) {
-      a = actions[g];
+      a = (long long)actions[g];
     } else {
       uint32_t w0, w1;
       if (pol->chance2) { w0 = pol->chance2[2 * g]; w1 = pol->chance2[2 * g + 1]; }
@@ -391,10 +398,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
     // kernel's register budget and make every warp with one finished table wait for it (measured: 1.7 ms per
     // 4M-table step when half the tables redeal, against 0.16 + 0.2 ms for step + redeal pass).
     S.hand_ctr[g] |= PKP_REDEAL_MARK;
-    reward_out[g] = 0.0f;
-    done_out[g] = 0;
-    pk_obs(t, pr, obs_row);   // placeholder row of the finished hand; the redeal pass overwrites it
-    return;
+    return PackedStepResult{0.0f, true, false};   // the row of the finished hand is a placeholder the redeal pass overwrites
   }
   if (AUTO == 1 && auto_reset && t.done) {
     uint32_t hand = S.hand_ctr[g] + 1u;
@@ -403,10 +407,7 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
     packed_deal(t, fb, S, pr, nullptr, seed, env_base + (uint64_t)g, hand, 0, 1, t.button + 1 < AP ? t.button + 1 : (t.button + 1) % AP,
                 starting_bbs, max_bbs, g, n, dk);
     packed_store_all(t, fb, S, g, n, P);
-    reward_out[g] = 0.0f;
-    done_out[g] = 0;
-    pk_obs(t, pr, obs_row);
-    return;
+    return PackedStepResult{0.0f, true, false};
   }
   const PokerTable<MAXP> t0 = t;
   const PackedDeck deck{fb, 2 * AP};
@@ -432,11 +433,25 @@ PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, 
     for (int s = 0; s < MAXP; ++s) { t.crb[s] = 0; t.inv[s] = 0; }
     t.highest = 0;
   }
-  reward_out[g] = legal ? pk_reward(t, pr, a, e, prev_inv) : 0.0f;   // :631-632
-  done_out[g] = t.done;
+  const float reward = legal ? pk_reward(t, pr, a, e, prev_inv) : 0.0f;   // :631-632
   packed_store(t, t0, S, g, n, AP);
   if (S.idx && t.idx != t0.idx) S.idx[g] = t.idx;
-  pk_obs(t, pr, obs_row);                                            // :633
+  return PackedStepResult{reward, prev_done, t.done};
+}
+
+// The step with the reference's own outputs: float32 observation row (:633), reward and done arrays.
+template <int MAXP, bool POLICY = false, int AUTO = 1>
+PULSE_HD void packed_step_one(const PulsePokerPacked& S, const PokerParams& pr, const int64_t* __restrict__ actions,
+                              float* __restrict__ obs_row, float* __restrict__ reward_out,
+                              uint8_t* __restrict__ done_out, int auto_reset, uint64_t seed, uint64_t env_base,
+                              int starting_bbs, int max_bbs, long long g, long long n,
+                              const PackedPolicy* pol = nullptr) {
+  PokerTable<MAXP> t;
+  const PackedStepResult r = packed_step_core<MAXP, POLICY, AUTO>(S, pr, actions, auto_reset, seed, env_base,
+                                                                  starting_bbs, max_bbs, g, n, pol, t);
+  reward_out[g] = r.reward;
+  done_out[g] = r.done;
+  pk_obs(t, pr, obs_row);
 }
 
 template <int MAXP, class DeckBuf>

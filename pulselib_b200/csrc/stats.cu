@@ -47,7 +47,7 @@ extern "C" int pulse_stats_accumulate(const void* reward, int reward_is_float, c
   if (n == 0) return PULSE_OK;
   PULSE_REQUIRE(reward && stats4, "null buffer");
   long long need = (n + kBlock - 1) / kBlock;
-  const int grid = (int)(need < 148 * 4 ? need : 148 * 4);
+  const int grid = (int)(need < pulse_sm_count() * 4 ? need : pulse_sm_count() * 4);
   if (reward_is_float) stats_kernel<float><<<grid, kBlock, 0, stream>>>((const float*)reward, done_or_null, stats4, n);
   else stats_kernel<int32_t><<<grid, kBlock, 0, stream>>>((const int32_t*)reward, done_or_null, stats4, n);
   return pulse_check_launch("pulse_stats_accumulate");
@@ -140,7 +140,7 @@ int launch_hand_stats(View v, const uint8_t* done, uint8_t* terminated, int32_t*
                       int active_players, int rearm_starting, int rearm_max, double* stats, long long n,
                       cudaStream_t stream, const char* what) {
   long long need = (n + kBlock - 1) / kBlock;
-  const int grid = (int)(need < 148 * 8 ? need : 148 * 8);
+  const int grid = (int)(need < pulse_sm_count() * 8 ? need : pulse_sm_count() * 8);
   hand_stats_kernel<View><<<grid, kBlock, 0, stream>>>(v, done, terminated, initial_q, q_seat, active_players,
                                                        rearm_starting, rearm_max, stats, n);
   return pulse_check_launch(what);

@@ -181,7 +181,8 @@ int pulse_tetris_step(uint16_t* rows, uint8_t* piece, int32_t* lines, uint8_t* d
   PULSE_REQUIRE(rows && piece && lines && done && actions && reward_out, "null buffer");
   PULSE_REQUIRE((reinterpret_cast<uintptr_t>(rows) & 15u) == 0, "rows must be 16-byte aligned");
   const long long need = ((long long)n_envs + kBlock - 1) / kBlock;
-  const int grid = (int)(need < 148LL * kCtasPerSm ? need : 148LL * kCtasPerSm);  // persistent CTAs
+  const long long cap = (long long)pulse_sm_count() * kCtasPerSm;
+  const int grid = (int)(need < cap ? need : cap);  // persistent CTAs
   if (action_bytes == 1)
     tetris_step_kernel<uint8_t><<<grid, kBlock, 0, stream>>>(rows, piece, lines, done, (const uint8_t*)actions,
                                                              next_piece_or_null, reset_piece_or_null, seed, env_base,

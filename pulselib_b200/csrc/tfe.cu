@@ -240,6 +240,21 @@ tfe_pack_kernel(const int32_t* __restrict__ values, uint64_t* __restrict__ board
     if (done) done[g] = tfe_game_over<SIDE>(b);
   }
 }
+// Domain audit: the packed board holds tile exponents up to 15 (32768); two 32768 tiles meeting stay unmerged where
+// the reference would make 65536 (tfe_body.cuh).  counts[0] += boards holding a 32768 tile, counts[1] += boards
+// holding two or more -- the latter are one move away from leaving the packed domain.
+__global__ void __launch_bounds__(kBlock)
+tfe_domain_kernel(const uint64_t* __restrict__ boards, int* __restrict__ counts, long long n) {
+  int one = 0, two = 0;
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
+    uint64_t x = boards[g];
+    x &= x >> 1; x &= x >> 2; x &= 0x1111111111111111ULL;      // 1 in every nibble that is 15
+    const int k = __popcll(x);
+    one += k >= 1; two += k >= 2;
+  }
+  one = __reduce_add_sync(0xFFFFFFFFu, one); two = __reduce_add_sync(0xFFFFFFFFu, two);
+  if ((threadIdx.x & 31) == 0) { if (one) atomicAdd(counts, one); if (two) atomicAdd(counts + 1, two); }
+}
 }  // namespace
 
 #define TFE_SIDE_DISPATCH(side, CALL)                 \
@@ -250,10 +265,11 @@ tfe_pack_kernel(const int32_t* __restrict__ values, uint64_t* __restrict__ board
   } while (0)
 
 // ---- per-device row-move table ------------------------------------------------------------------------
+#include <atomic>
 #include <mutex>
 namespace {
 std::mutex g_table_mutex;
-uint4* g_table[64] = {nullptr};
+std::atomic<uint4*> g_table[64];   // published with release / read with acquire: the fast path takes no lock
 
 template <int SIDE, typename ActT>
 cudaError_t allow_smem() {
@@ -266,9 +282,17 @@ int tfe_ensure_table(cudaStream_t stream, const uint4** out) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess || dev < 0 || dev >= 64) { pulse_set_error("cudaGetDevice failed"); return e ? (int)e : PULSE_EINVAL; }
-  if (!g_table[dev]) {
+  uint4* have = g_table[dev].load(std::memory_order_acquire);
+  if (!have) {
+    // building allocates and synchronises: refuse while the stream is being captured into a CUDA graph
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) {
+      pulse_set_error("the 2048 row table of this device is not built yet: call pulse_tfe_init before capturing a graph");
+      return PULSE_ENOTREADY;
+    }
     std::lock_guard<std::mutex> lock(g_table_mutex);
-    if (!g_table[dev]) {
+    have = g_table[dev].load(std::memory_order_acquire);
+    if (!have) {
       uint4* t = nullptr;
       if ((e = cudaMalloc(&t, kTableBytes)) != cudaSuccess) { pulse_set_error("cudaMalloc(row table): %s", cudaGetErrorString(e)); return (int)e; }
       tfe_build_table_kernel<<<65536 / 256, 256, 0, stream>>>(reinterpret_cast<uint16_t*>(t),
@@ -276,10 +300,11 @@ int tfe_ensure_table(cudaStream_t stream, const uint4** out) {
       if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) { pulse_set_error("row table build: %s", cudaGetErrorString(e)); cudaFree(t); return (int)e; }
       allow_smem<4, uint8_t>(); allow_smem<4, int64_t>(); allow_smem<3, uint8_t>(); allow_smem<3, int64_t>();
       allow_smem<2, uint8_t>(); allow_smem<2, int64_t>();
-      g_table[dev] = t;
+      g_table[dev].store(t, std::memory_order_release);
+      have = t;
     }
   }
-  *out = g_table[dev];
+  *out = have;
   return PULSE_OK;
 }
 }  // namespace
@@ -319,7 +344,7 @@ int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, cons
   int rc = tfe_ensure_table(stream, &table);
   if (rc) return rc;
   const long long need = ((long long)n_envs + kStepBlock - 1) / kStepBlock;
-  const int grid = (int)(need < 148 ? need : 148);  // one persistent CTA per SM
+  const int grid = (int)(need < pulse_sm_count() ? need : pulse_sm_count());  // one persistent CTA per SM
   // Programmatic dependent launch: the kernel's prologue (table copy into shared memory, LUT) touches nothing an
   // earlier kernel on the stream writes, so it may start while that kernel drains; everything else sits behind
   // griddepcontrol.wait in the kernel.  PULSE_PDL=0 launches plainly.
@@ -351,6 +376,14 @@ int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, in
   TFE_SIDE_DISPATCH(side, (tfe_unpack_kernel<SD><<<pulse_grid_for(n_envs, kBlock), kBlock, 0, stream>>>(
                               boards, values_out, (long long)n_envs)));
   return pulse_check_launch("pulse_tfe_unpack");
+}
+
+int pulse_tfe_domain_check(const uint64_t* boards, int* counts2, int n_envs, cudaStream_t stream) {
+  PULSE_REQUIRE(n_envs >= 0, "n_envs < 0");
+  if (n_envs == 0) return PULSE_OK;
+  PULSE_REQUIRE(boards && counts2, "null buffer");
+  tfe_domain_kernel<<<pulse_grid_for(n_envs, kBlock), kBlock, 0, stream>>>(boards, counts2, (long long)n_envs);
+  return pulse_check_launch("pulse_tfe_domain_check");
 }
 
 int pulse_tfe_pack(const int32_t* values, uint64_t* boards_out, uint8_t* done_out_or_null, int* bad_count_or_null,

@@ -306,7 +306,7 @@ class PokerGPU(PokerGPUCompat):
     def __getattr__(self, name):               # only reached when normal lookup fails
         d = self.__dict__
         if name in _LAZY_SET and d.get("_mode") == "packed" and d.get("_eng_live"):
-            self._materialise()
+            self._materialise(decks=name == "decks")
             if name in d:
                 return d[name]
         raise AttributeError(name)
@@ -314,9 +314,16 @@ class PokerGPU(PokerGPUCompat):
     def __setattr__(self, name, value):
         d = self.__dict__
         if name in _MIRROR_SET and d.get("_mode") == "packed" and d.get("_eng_live"):
-            self._materialise()                # the rest of the state must exist when this one is overridden
+            self._materialise(decks=True)      # the rest of the state must exist when this one is overridden
             d["_touched"] = True
         super().__setattr__(name, value)
+
+    def __delattr__(self, name):
+        d = self.__dict__
+        if name in _LAZY_SET and d.get("_mode") == "packed" and d.get("_eng_live"):
+            self._materialise(decks=True)      # e.g. `del env.button_pos` in a white-box test
+            d["_touched"] = True
+        super().__delattr__(name)
 
     def packed_engine(self):
         """The PokerGPUPacked engine while it is authoritative (helpers such as HandStats read it directly)."""
@@ -330,21 +337,30 @@ class PokerGPU(PokerGPUCompat):
             t = d[n]
             ver[n] = (t, t._version)
 
-    def _materialise(self):
+    def _materialise(self, decks=False):
+        """Snapshot of the packed state as reference-shaped tensors, one launch.  The decks (52 tape draws per table to
+        re-derive, or a copy of the prefixed ones) only when somebody asks for them."""
         d = self.__dict__
-        if d["_materialised"] is not None:
-            return
         eng = d["_eng"]
-        names = tuple(n for n in _MIRROR if n not in _LIVE)
-        out = eng.unpack_into(eng.alloc_mirror(names, full=True), full=True)
+        if d["_materialised"] is None:
+            names = tuple(n for n in _MIRROR if n not in _LIVE and n != "decks")
+            out = eng.unpack_into(eng.alloc_mirror(names), full=True)   # no decks tensor given: none written
+            N, i32 = self.n_games, dict(dtype=torch.int32, device=self.device)
+            out["button_pos"] = out["button"][0]
+            out["prev_stacks"], out["raise_amounts"] = torch.zeros(N, **i32), torch.zeros(N, **i32)
+            out["active_player_idx"] = torch.arange(int(self.active_players), **i32)
+            d["_materialised"] = names + _DERIVED
+        elif decks and "decks" not in d:
+            out = {}
+        else:
+            return
+        if decks and "decks" not in d:
+            out.update(eng.unpack_into(eng.alloc_mirror(("decks",), full=True), full=True))
+            d["_materialised"] += ("decks",)
         for n, t in out.items():
             d[n] = t
-            d["_ver"][n] = (t, t._version)
-        N, i32 = self.n_games, dict(dtype=torch.int32, device=self.device)
-        d["button_pos"] = out["button"][0]
-        d["prev_stacks"], d["raise_amounts"] = torch.zeros(N, **i32), torch.zeros(N, **i32)
-        d["active_player_idx"] = torch.arange(int(self.active_players), **i32)
-        d["_materialised"] = names
+            if n in _MIRROR_SET:
+                d["_ver"][n] = (t, t._version)
 
     def _sync(self):
         """Start of every call in packed mode: did the caller write to / rebind any exposed tensor?  Yes -> carry on
@@ -363,15 +379,13 @@ class PokerGPU(PokerGPUCompat):
             for n in d["_materialised"]:
                 d.pop(n, None)
                 d["_ver"].pop(n, None)
-            for n in _DERIVED:
-                d.pop(n, None)
             d["_materialised"] = None
 
     def _go_compat(self):
         d = self.__dict__
         if d["_mode"] != "packed" or not d["_eng_live"]:
             return
-        self._materialise()
+        self._materialise(decks=True)
         d["_mode"], d["_touched"], d["_materialised"] = "compat", False, None
         d["_ver"] = {}
         d["stacks"] = d["stacks"].contiguous()   # [N, P] row-major copy of the seat-major view

@@ -221,6 +221,8 @@ class PokerGPUPacked(gym.Env):
         shapes.update(board=(N, 5), hands=(N, P, 2))
         if full:
             shapes["decks"] = (N, 52)
+        if fields is not None and "decks" in fields:
+            shapes["decks"] = (N, 52)
         names = fields if fields is not None else tuple(shapes) + ("is_done", "equity_dirty", "equities")
         out = {}
         for n in names:

@@ -129,6 +129,20 @@ class TFEBatched(gym.Env):
             raise ValueError("board values must be 0 or a power of two in 2..32768")
         self._started = True
 
+    def domain_check(self, raise_on_overflow=True):
+        """(boards holding a 32768 tile, boards holding two or more).  The packed board stores tile exponents up to 15;
+        two 32768 tiles would stay unmerged where the reference makes 65536 (csrc/tfe_body.cuh) -- this is the flag
+        that says a batch is about to leave the domain in which the engine is bit-exact."""
+        counts = torch.zeros(2, dtype=torch.int32, device=self.device)
+        with _lib.device_guard(self.device):
+            _lib.check(self._lib.pulse_tfe_domain_check(ptr(self.boards), ptr(counts), c_i(self.n_envs),
+                                                        _lib.cuda_stream(self.device)), "pulse_tfe_domain_check")
+        one, two = (int(v) for v in counts.tolist())
+        if two and raise_on_overflow:
+            raise _lib.PulseError(f"{two} board(s) hold two 32768 tiles: the next merge would leave the packed domain "
+                                  "(tiles above 32768 are not representable in 4 bits per cell)")
+        return one, two
+
     def is_game_over(self):
         return self.done
 
@@ -171,5 +185,7 @@ class TFE(gym.Env):
         a = torch.tensor([int(action)], dtype=torch.int64, device=self._env.device)
         obs, rew, done, _, info = self._env.step(a)
         np.copyto(self.board, obs[0].cpu().numpy())   # same array object every step, like the reference (:181)
+        if self.board.max() >= 32768:                 # a single board: the audit is free here
+            self._env.domain_check()
         self.total_score = int(info["score"][0].item())
         return self.get_obs(), int(rew[0].item()), bool(done[0].item()), False, self.get_info()

@@ -1,0 +1,101 @@
+"""PokerGPU with host (numpy) buffers: the end-to-end path of the engine.
+
+`PokerHostEnv` keeps the reference's step contract -- actions in, float32 observations [N, 13 + 3 (M - 1)], float32
+rewards and bool dones out (/root/reference/environments/Poker/PokerGPU.py:527-633) -- with every array in HOST
+memory.  It binds `pulse_poker_host_*` (include/pulse_envs.h, csrc/host_env.cu): 1 B per table goes to the GPU, one
+packed 24 B record per LIVE table comes back, and a pool of native threads expands the records into `self.obs`,
+`self.rewards`, `self.dones` -- the same three arrays on every call, as the reference reuses `self.obs`.
+bench.py's `e2e` number is this class."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, handranks
+from .envs.poker import _Config
+
+
+class PokerHostEnv:
+    NUM_ACTIONS = 13
+
+    def __init__(self, device=0, n_players=6, max_players=10, n_games=100, starting_bbs=100, max_bbs=1000, w1=.5, w2=.5,
+                 K=20, alpha=300, seed=0, env_base=0, chunks=8, threads=0):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise _lib.PulseError("PokerHostEnv needs a CUDA device: the engine has no CPU fallback")
+        self._lib = _lib.load()
+        dev = torch.device(device) if not isinstance(device, int) else torch.device("cuda", device)
+        self.device_index = dev.index if dev.index is not None else torch.cuda.current_device()
+        self.n_players, self.max_players, self.n_games = int(n_players), int(max_players), int(n_games)
+        self.active_players = self.n_players
+        self.obs_size = 13 + 3 * (self.max_players - 1)
+        cfg = _Config(self.n_games, self.n_players, self.n_players, self.max_players, int(starting_bbs), int(max_bbs),
+                      int(K), int(alpha), float(w1), float(w2))
+        table = handranks.load_table()
+        self._h = C.c_void_p()
+        _lib.check(self._lib.pulse_poker_host_create(C.byref(self._h), C.byref(cfg), C.c_void_p(table.ctypes.data),
+                                                     C.c_size_t(table.size), C.c_uint64(int(seed)), C.c_uint64(int(env_base)),
+                                                     C.c_int(self.device_index), C.c_int(int(chunks)), C.c_int(int(threads))),
+                   "pulse_poker_host_create")
+        # 64-byte aligned so heads-up rows (64 B) are whole cache lines for the expander's streaming stores
+        self.obs = _aligned((self.n_games, self.obs_size), np.float32)
+        self.rewards = _aligned((self.n_games,), np.float32)
+        self.dones = _aligned((self.n_games,), np.uint8)
+
+    def reset(self, active_players=None, rotation=0):
+        ap = self.n_players if active_players is None else int(active_players)
+        _lib.check(self._lib.pulse_poker_host_reset(self._h, C.c_int(ap), C.c_int(int(rotation)), _p(self.obs),
+                                                    _p(self.rewards), _p(self.dones)), "pulse_poker_host_reset")
+        self.active_players = ap
+        return self.obs, {"active_players": ap}
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions)
+        if a.dtype not in (np.uint8, np.int64):
+            a = a.astype(np.int64)
+        if a.shape != (self.n_games,):
+            raise ValueError(f"actions must have shape {(self.n_games,)}, got {a.shape}")
+        _lib.check(self._lib.pulse_poker_host_step(self._h, _p(a), C.c_int(a.dtype.itemsize), _p(self.obs), _p(self.rewards),
+                                                   _p(self.dones)), "pulse_poker_host_step")
+        return self.obs, self.rewards, self.dones.view(np.bool_), False, {"active_players": self.active_players}
+
+    def info(self) -> dict:
+        v = [C.c_int() for _ in range(4)] + [C.c_longlong(), C.c_longlong()]
+        _lib.check(self._lib.pulse_poker_host_info(self._h, *[C.byref(x) for x in v]), "pulse_poker_host_info")
+        return dict(row_bytes=v[0].value, obs_width=v[1].value, chunks=v[2].value, threads=v[3].value,
+                    last_h2d_bytes=v[4].value, last_d2h_bytes=v[5].value)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.pulse_poker_host_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+def _aligned(shape, dtype, align=64):
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    raw = np.zeros(n + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n].view(dtype).reshape(shape)
+
+
+def expand_rows(rows: np.ndarray, active_players: int, max_players: int):
+    """Packed step records (uint64 [n, words]) -> (obs float32 [n, W], reward float32 [n], done uint8 [n]); host only."""
+    lib = _lib.load()
+    rows = np.ascontiguousarray(rows, dtype=np.uint64)
+    n, W = rows.shape[0], 13 + 3 * (max_players - 1)
+    obs, rew, done = np.zeros((n, W), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8)
+    _lib.check(lib.pulse_poker_wire_expand_host(_p(rows), C.c_longlong(n), C.c_int(active_players), C.c_int(max_players),
+                                                _p(obs), _p(rew), _p(done)), "pulse_poker_wire_expand_host")
+    return obs, rew, done

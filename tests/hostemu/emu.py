@@ -160,6 +160,15 @@ class EmuPokerPacked(EmuPoker):
         return self.obs, self.rewards, self.is_done.astype(bool)
 
 
+    def wire_rows(self):
+        """the compact step record (csrc/poker_wire.cuh) of every table, reward = self.rewards"""
+        words = (18 + 4 * (self.max_players - 1) + 7) // 8
+        rows = np.zeros((self.n_games, words), np.uint64)
+        s = self._packed()
+        rc = lib().emu_poker_wire_rows(C.byref(s), C.byref(self.cfg), p(self.rewards), p(rows))
+        assert rc == 0
+        return rows
+
     def step_policy(self, kinds, chance2=None, counter=0, actions=None):
         """packed step with the scripted seats evaluated inside; returns the played actions too"""
         k = np.ascontiguousarray(kinds, dtype=np.uint8)

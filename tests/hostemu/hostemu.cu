@@ -10,6 +10,7 @@
 
 void pulse_set_error(const char*, ...) {}
 int pulse_check_launch(const char*) { return 0; }
+int pulse_sm_count(void) { return 148; }
 
 static PokerParams mk(const PulsePokerConfig* c) {
   PokerParams p; p.w1 = c->w1; p.w2 = c->w2; p.K = c->K; p.alpha = c->alpha;
@@ -92,6 +93,26 @@ int emu_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerCon
     EMU_DISPATCH(pr.P, (packed_step_one<MP, true>(*st, pr, actions, obs_out + g * W, reward_out, done_out, auto_reset,
                                                   seed, env_base, cfg->starting_bbs, cfg->max_bbs, g,
                                                   (long long)cfg->n_games, &pol)));
+  return 0;
+}
+// the compact step record (poker_wire.cuh) of every table of a packed batch, reward taken from `rewards`
+int emu_poker_wire_rows(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const float* rewards, uint64_t* rows) {
+  PokerParams pr = mk(cfg);
+  const long long n = cfg->n_games;
+#define EMU_WIRE(MPV, MTV)                                                         \
+  for (long long g = 0; g < n; ++g) {                                              \
+    PokerTable<MPV> t; uint32_t fb;                                                \
+    packed_load(t, fb, *st, g, n, pr.AP);                                          \
+    uint64_t w[(18 + 4 * (MTV - 1) + 7) / 8];                                      \
+    pkw_pack_row<MPV, MTV>(t, pr, rewards[g], w);                                  \
+    for (int i = 0; i < (18 + 4 * (MTV - 1) + 7) / 8; ++i) rows[g * ((18 + 4 * (MTV - 1) + 7) / 8) + i] = w[i]; \
+  }
+  if (pr.P <= 2 && pr.M == 2) { EMU_WIRE(2, 2) }
+  else if (pr.P <= 4 && pr.M == 4) { EMU_WIRE(4, 4) }
+  else if (pr.P <= 6 && pr.M == 6) { EMU_WIRE(6, 6) }
+  else if (pr.M == 10) { EMU_WIRE(10, 10) }
+  else return -1;
+#undef EMU_WIRE
   return 0;
 }
 float emu_enumerated_strength(int stage, int h0, int h1, uint32_t fb) { return packed_enumerated_strength(stage, h0, h1, fb); }

@@ -301,3 +301,21 @@ def test_tetris_full_size_properties(cuda_device):
         assert bool(prev_done.any())
         sums.append(int(chk))
     assert sums[0] == sums[1]
+
+
+def test_tfe_domain_check_flags_32768_tiles(cuda_device):
+    """tiles above 32768 are outside the packed board's domain (4 bits per cell): the audit must say so"""
+    import torch
+    from pulselib_b200 import _lib
+    from pulselib_b200.envs.tfe import TFEBatched
+
+    env = TFEBatched(cuda_device, 64, side=4, seed=1)
+    env.reset()
+    assert env.domain_check() == (0, 0)
+    vals = env.board_values().clone()
+    vals[3, 0, 0] = 32768
+    vals[5, 0, 0] = 32768; vals[5, 0, 1] = 32768
+    env.set_board_values(vals)
+    assert env.domain_check(raise_on_overflow=False) == (2, 1)
+    with pytest.raises(_lib.PulseError):
+        env.domain_check()

@@ -1,0 +1,85 @@
+"""GPU suite: the host-buffer env (pulselib_b200/host_env.py, csrc/host_env.cu: byte actions in, compacted packed
+records out, native threads expanding them) must hand back exactly what the float32-row engine returns -- observation
+rows bit for bit, reward bits, done flags -- over whole hands, for every supported table shape, with batches that are
+not multiples of the chunk / warp sizes, and against the oracle."""
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+CFG = dict(starting_bbs=100, max_bbs=1000, w1=.5, w2=.3, K=100, alpha=50)
+
+
+@pytest.mark.parametrize("P,M,ap,N,chunks,threads", [(2, 2, 2, 50_000, 3, 4), (2, 2, 2, 1 << 20, 8, 0), (6, 6, 6, 33_333, 4, 3),
+                                                      (6, 6, 3, 4097, 1, 2), (10, 10, 10, 20_001, 5, 0), (4, 4, 4, 999, 2, 1)])
+def test_host_env_matches_float32_engine(P, M, ap, N, chunks, threads, cuda_device):
+    import torch
+    from unittest import mock
+
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+    from pulselib_b200.host_env import PokerHostEnv
+
+    seed, base = 20260401, 4242
+    henv = PokerHostEnv(cuda_device, n_players=P, max_players=M, n_games=N, seed=seed, env_base=base, chunks=chunks,
+                        threads=threads, **CFG)
+    denv = PokerGPUPacked(cuda_device, n_players=P, max_players=M, n_games=N, seed=seed, env_base=base, **CFG)
+    rng = np.random.default_rng(N)
+    steps = 14 if P == 2 else 26
+    for hand in range(3):
+        rot = hand % P
+        obs_h, _ = henv.reset(active_players=ap, rotation=rot)
+        opts = {"rotation": rot}
+        if ap != P:
+            opts["active_players"] = True
+            with mock.patch("torch.randint", lambda *a, **k: torch.tensor([ap])):
+                obs_d, _ = denv.reset(options=opts)
+        else:
+            obs_d, _ = denv.reset(options=opts)
+        np.testing.assert_array_equal(obs_h, obs_d.cpu().numpy(), err_msg=f"hand {hand} reset obs")
+        assert not henv.dones.any() and not henv.rewards.any()
+        for t in range(steps):
+            a = rng.integers(0, 13, N)
+            a_host = a.astype(np.uint8) if t % 2 else a.astype(np.int64)        # both action widths
+            if t == 3:
+                a_host = a.astype(np.int64); a_host[::7] = -1; a_host[1::7] = 13; a = a_host   # ids the reference ignores / treats alike
+            o1, r1, d1, _, _ = henv.step(a_host)
+            o2, r2, d2, _, _ = denv.step(torch.from_numpy(a.astype(np.int64)).to(cuda_device))
+            tag = f"P{P} hand {hand} step {t}"
+            np.testing.assert_array_equal(o1, o2.cpu().numpy(), err_msg=tag + " obs")
+            np.testing.assert_array_equal(r1.view(np.uint32), r2.cpu().numpy().view(np.uint32), err_msg=tag + " reward bits")
+            np.testing.assert_array_equal(d1, d2.cpu().numpy(), err_msg=tag + " done")
+        inf = henv.info()
+        assert inf["row_bytes"] == 8 * ((18 + 4 * (M - 1) + 7) // 8)
+        assert inf["last_d2h_bytes"] <= N * inf["row_bytes"] and inf["last_h2d_bytes"] >= N
+    henv.close()
+
+
+def test_host_env_matches_oracle(cuda_device, hr_table):
+    from pulselib_b200.host_env import PokerHostEnv
+
+    N = 200_000
+    henv = PokerHostEnv(cuda_device, n_players=2, max_players=2, n_games=N, seed=5, env_base=99, chunks=4, **CFG)
+    orc = pyoracle.OraclePoker(hr_table, n_players=2, max_players=2, n_games=N, **CFG)
+    rng = np.random.default_rng(1)
+    for hand in range(2):
+        orc.tape_decks(5, 99, hand)
+        np.testing.assert_array_equal(henv.reset()[0], orc.reset(None))
+        for t in range(16):
+            a = rng.integers(0, 13, N)
+            o1, r1, d1, _, _ = henv.step(a.astype(np.uint8))
+            o2, r2, d2 = orc.step(a)
+            np.testing.assert_array_equal(o1, o2, err_msg=f"hand {hand} step {t}")
+            np.testing.assert_array_equal(d1, d2)
+            np.testing.assert_allclose(r1, r2, rtol=2e-6, atol=50 * 4e-7)
+    henv.close()
+
+
+def test_host_env_refuses_unrepresentable_configs(cuda_device):
+    from pulselib_b200 import _lib
+    from pulselib_b200.host_env import PokerHostEnv
+
+    with pytest.raises(_lib.PulseError):
+        PokerHostEnv(cuda_device, n_players=10, max_players=10, n_games=64, max_bbs=5000)   # 50,000 chips do not fit 14 bits
+    with pytest.raises(_lib.PulseError):
+        PokerHostEnv(cuda_device, n_players=3, max_players=10, n_games=64)                  # shape outside the specialised set

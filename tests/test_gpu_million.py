@@ -103,3 +103,84 @@ def test_blackjack_million_envs(cuda_device):
             np.testing.assert_array_equal(o1.cpu().numpy(), o2, err_msg=f"ep {episode} t{t} obs")
             np.testing.assert_array_equal(r1.cpu().numpy(), r2, err_msg=f"ep {episode} t{t} reward")
             np.testing.assert_array_equal(d1.cpu().numpy().astype(bool), np.asarray(d2).astype(bool))
+
+
+# ---- the same trajectories the REFERENCE stepped (tests/golden/make_digests_1m.py), digest for digest -------------
+class _CudaPokerEngine:
+    def __init__(self, dev, name):
+        from pulselib_b200.envs.poker_packed import PokerGPUPacked
+        from tests import digest_util as du
+
+        c = du.CASES[name]
+        self.dev, self.c = dev, c
+        self.env = PokerGPUPacked(dev, n_players=c["P"], max_players=c["M"], n_games=c["runs"] * c["n_run"],
+                                  seed=c["seed"], env_base=0, **c["cfg"])
+
+    def reset(self, hand, ap, rot):
+        import torch
+        from unittest import mock
+
+        opts = {"rotation": rot}
+        if ap != self.c["P"]:
+            opts["active_players"] = True
+            with mock.patch("torch.randint", lambda *a, **k: torch.tensor([ap])):
+                obs, _ = self.env.reset(options=opts)
+        else:
+            obs, _ = self.env.reset(options=opts)
+        self._snap = None
+        return obs.cpu().numpy()
+
+    def step(self, a):
+        import torch
+
+        o, r, d, _, _ = self.env.step(torch.from_numpy(a).to(self.dev))
+        self._snap = None
+        return o.cpu().numpy(), r.cpu().numpy(), d.cpu().numpy()
+
+    def get(self, f):
+        if self._snap is None:
+            self._snap = {k: v.cpu().numpy() for k, v in self.env.unpack().items()}
+        return self._snap[f]
+
+
+@pytest.mark.parametrize("name", ["poker_hu", "poker_6max", "poker_10max"])
+def test_poker_digests_from_reference(name, cuda_device):
+    from tests import digest_util as du
+
+    assert du.check_poker_case(name, _CudaPokerEngine(cuda_device, name)) >= 1 << 20
+
+
+def test_blackjack_digests_from_reference(cuda_device):
+    import torch
+    from pulselib_b200.envs.blackjack import BlackJack
+    from tests import digest_util as du
+
+    c, want = du.CASES["blackjack"], du.load_digests()["blackjack"]["episode"]
+    n = c["runs"] * c["n_run"]
+    env = BlackJack(device=cuda_device, batch_size=n, seed=c["seed"], env_base=0)
+    obs, _ = env.reset()
+    assert du.hexd(du.digest(obs.cpu().numpy())) == want["reset_obs"]
+    acts = du.case_actions("blackjack")
+    for t in range(c["steps"]):
+        o, r, d, _, _ = env.step(torch.from_numpy(acts[t]).to(cuda_device))
+        w = want["steps"][t]
+        assert du.hexd(du.digest(o.cpu().numpy())) == w["obs"] and du.hexd(du.digest(r.cpu().numpy())) == w["rewards"], f"step {t}"
+        dn = d.cpu().numpy().astype(np.uint8)
+        assert du.hexd(du.digest(dn)) == w["terminated"] and int(dn.sum()) == w["terminated_count"]
+
+
+def test_tfe_digests_from_reference(cuda_device):
+    import torch
+    from pulselib_b200.envs.tfe import TFEBatched
+    from tests import digest_util as du
+
+    c, want = du.CASES["tfe_4x4"], du.load_digests()["tfe_4x4"]["episode"]
+    env = TFEBatched(cuda_device, c["n"], side=c["side"], seed=c["seed"], env_base=0, auto_reset=False)
+    assert du.hexd(du.digest(env.reset()[0].cpu().numpy())) == want["reset_boards"]
+    acts = du.case_actions("tfe_4x4")
+    for t in range(c["steps"]):
+        obs, rew, done, _, info = env.step(torch.from_numpy(acts[t]).to(cuda_device).to(torch.uint8))
+        w = want["steps"][t]
+        assert du.hexd(du.digest(obs.cpu().numpy())) == w["boards"] and du.hexd(du.digest(rew.cpu().numpy())) == w["rewards"], f"step {t}"
+        assert du.hexd(du.digest(done.cpu().numpy().astype(np.uint8))) == w["done"]
+        assert du.hexd(du.digest(info["score"].cpu().numpy())) == w["scores"]

@@ -159,3 +159,16 @@ def test_oracle_reproduces_reference_unit_tests(hr_table):
 def test_kernel_bodies_hostbuild_reproduce_reference_unit_tests(hr_table):
     n = pu.replay_reference_kat(lambda ctor: EmuKat(hr_table, ctor))
     assert n >= 280
+
+
+def test_dropin_class_reproduces_reference_unit_tests_on_host_bodies():
+    """The registered drop-in class (packed engine, mirror on access) replays all records too -- here on the
+    host-compiled kernel bodies, in tests/test_gpu_reference_kat.py on the B200."""
+    import torch
+
+    from tests.hostemu.shim import hostemu_backend
+    from tests.kat_dropin import DropinKat
+
+    with hostemu_backend():
+        n = pu.replay_reference_kat(lambda ctor: DropinKat(torch.device("cpu"), ctor))
+    assert n >= 280
