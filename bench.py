@@ -361,6 +361,7 @@ def run_gpu(args, wl, name):
 
     host_steps(L, 0)
     barrier()
+    henv.timing(reset=True)
     w0 = time.perf_counter()
     host_steps(e2e_steps, 0, count=True)
     torch.cuda.synchronize(dev)
@@ -380,6 +381,7 @@ def run_gpu(args, wl, name):
         assert torch.allclose(torch.stack(gathered).sum(0), stats_all), "all-reduce of the run statistics disagrees with the gathered sum"
     assert int(stats_all[0].item()) == world * N * e2e_steps
     hinfo = henv.info()
+    htime = henv.timing()
     henv.close()
 
     if rank == 0:
@@ -410,6 +412,7 @@ def run_gpu(args, wl, name):
                            "float32 obs [N,%d] + float32 reward + bool done out in host memory every step, whole-batch "
                            "reset every %d steps; records of live tables only cross PCIe and are expanded by host threads" % (env.obs_size, L),
                     "reference_contract_bytes_per_table_step": 8 + 4 * env.obs_size + 4 + 1,
+                    "host_ms_per_step": {k: round(1e3 * v / max(1.0, htime["calls"]), 4) for k, v in htime.items() if k != "calls"},
                     "timing": "wall clock around the host loop (the API is host-synchronous), device synchronised on both sides"},
             "run_stats_device": dict(zip(("env_steps", "episodes_done", "reward_sum", "reward_sq_sum"), dev_stats)),
             "run_stats_allreduce": {"env_steps": stats_all[0].item(), "done_flags_at_end": stats_all[1].item(),
@@ -487,6 +490,13 @@ def run_env_workload(args, name):
                          "kernel_time": m["kernel_time"], "algorithmic_bytes_per_env_step": A, "peak_source": peak_src},
             "clocks": sampler.summary(),
         }
+        if spec.get("moved_bytes"):      # the fixed algorithmic figure counts bytes this layout never moves: say so
+            mb = spec["moved_bytes"]
+            line["roofline"]["moved_bytes_per_env_step"] = mb
+            line["roofline"]["frac_by_moved_bytes"] = mb * n / (kernel_ms * 1e-3) / 1e9 / peak
+        if m.get("live_fraction") is not None:
+            line["live_step_fraction"] = round(m["live_fraction"], 4)
+            line["live_env_steps_per_s"] = line["value"] * m["live_fraction"]
         if world == 1 and args.cpu_seconds > 0:
             line["cpu_baseline"] = be.cpu_baseline(name, args.cpu_seconds)[0]
         print(json.dumps(line))
@@ -500,7 +510,7 @@ def extra_workloads(dev, rank, steps=256):
 
     peak, _ = peaks()
     out = {}
-    for name in ("tfe_4x4", "tetris", "particle2d", "blackjack", "poker_hu_scripted"):
+    for name in ("tfe_4x4", "tfe_4x4_rollout", "tetris", "particle2d", "blackjack", "poker_hu_autoreset", "poker_hu_scripted"):
         try:
             m = be.measure(name, dev, rank, 1, steps, 3)
             A = be.SPECS[name]["algo_bytes"]
@@ -509,6 +519,18 @@ def extra_workloads(dev, rank, steps=256):
                          "ms_per_step": m["total_ms"] / steps, "launch_mode": m["mode"],
                          "roofline": {"achieved": ach, "frac": ach / peak, "unit": "GB/s",
                                       "algorithmic_bytes_per_env_step": A, "kernel": be.SPECS[name]["kernel"]}}
+            if be.SPECS[name].get("moved_bytes"):
+                mb = be.SPECS[name]["moved_bytes"]
+                out[name]["roofline"]["moved_bytes_per_env_step"] = mb
+                out[name]["roofline"]["frac_by_moved_bytes"] = mb * m["n"] / (m["kernel_ms"] * 1e-3) / 1e9 / peak
+            if m.get("live_fraction") is not None:
+                out[name]["live_step_fraction"] = round(m["live_fraction"], 4)
+                out[name]["live_env_steps_per_s"] = m["value"] * m["live_fraction"]
+            if name == "tfe_4x4":      # the metric's second env: end to end and the CPU port beside it
+                e = be.e2e(name, dev, rank, 64)
+                out[name]["e2e"] = {"value": e["value"], "unit": "env-steps/s", "h2d_bytes_per_step": e["h2d_bytes_per_step"],
+                                    "d2h_bytes_per_step": e["d2h_bytes_per_step"], "steps": e["steps"], "chunks": e["chunks"]}
+                out[name]["cpu_baseline"] = be.cpu_baseline(name, 5.0)[0]
         except Exception as ex:  # an extra must never take the headline down with it
             out[name] = {"error": f"{type(ex).__name__}: {ex}"}
     return out
@@ -521,7 +543,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=32)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="poker_hu",
-                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tetris", "particle2d", "blackjack", "poker_hu_scripted", "poker_hu_train_loop"])
+                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tfe_4x4_rollout", "tetris", "particle2d", "blackjack", "blackjack_per_step", "poker_hu_autoreset", "poker_hu_scripted", "poker_hu_train_loop"])
     ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` block of the poker line")
     ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")
     ap.add_argument("--e2e-chunks", type=int, default=8)

@@ -15,10 +15,20 @@ L2_BYTES = 126e6
 
 SPECS = {
     # algo_bytes: SURVEY.md 8(d) "algorithmic bytes per env-step" (fixed there; DESIGN.md 4.x derives them)
-    "tfe_4x4": dict(n=1 << 20, algo_bytes=106, kernel="tfe_step_kernel<4, uint8_t>", graph=32, actions=16,
+    "tfe_4x4": dict(n=1 << 20, algo_bytes=106, replicas=4, kernel="tfe_step_kernel<4, uint8_t>", graph=32, actions=16,
                     desc="2048 4x4, {n} boards/GPU, uniform random moves (uint8), spawns from the chance tape, "
                          "auto-reset on game over, int32 4x4 observation written every step"),
-    "tetris": dict(n=1 << 21, algo_bytes=134, kernel="tetris_step_kernel<uint8_t>", graph=32, actions=16,
+    # open-loop action tapes, 16 steps per launch (pulse_tfe_rollout): the row table is staged once per 16 steps and a
+    # board stays in registers between its steps -- action 1 + obs 64 + reward 4 + done 1 = 70 B per board-step plus
+    # 32 B of state per 16 steps; reported against the same fixed 106 B
+    "tfe_4x4_rollout": dict(n=1 << 20, algo_bytes=106, moved_bytes=72, replicas=4, kernel="tfe_rollout_kernel<4, uint8_t>",
+                            graph=0, actions=16,
+                            desc="2048 4x4, {n} boards/GPU, uniform random moves (uint8) supplied as a [16, N] tape, 16 steps per "
+                                 "launch, spawns from the chance tape, auto-reset on game over, int32 4x4 observations of "
+                                 "every step written ([16, N, 4, 4])"),
+    # moved_bytes: what the kernel can actually move per env-step -- the rows tensor IS the observation (no 40 B copy):
+    # rows 40 in + 40 out, piece 1 + 1, lines 4 + 4, done 1 + 1, action 1, reward 4 = 97 B; reported next to the fixed 134 B
+    "tetris": dict(n=1 << 21, algo_bytes=134, moved_bytes=97, replicas=4, kernel="tetris_step_kernel<uint8_t>", graph=32, actions=16,
                    desc="Tetris 10x20, {n} envs/GPU, uniform random placements over 40 actions (uint8), pieces from "
                         "the chance tape, auto-reset on lock-out, rows tensor is the observation"),
     "particle2d": dict(n=1 << 24, algo_bytes=70, kernel="particle2d_step_kernel", graph=0, actions=4,
@@ -31,6 +41,12 @@ SPECS = {
                               desc="PokerGPU heads-up, {n} tables/GPU, seats played by the scripted TightAggressive and "
                                    "SmallBall rules inside the step kernel (no action tensor), draws from the chance "
                                    "tape, per-table auto-reset"),
+    # SURVEY 8(d) config 3, convention (ii): supplied uniform random actions, per-table auto-reset -- no table ever
+    # idles; a table that finished is dealt its next hand by the step that follows (that step plays no action for it).
+    "poker_hu_autoreset": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_step_kernel<2, 2, 10, false, 2> + redeal pass",
+                               graph=0, actions=16,
+                               desc="PokerGPU heads-up, {n} tables/GPU, uniform random actions 0..12 supplied (int64), "
+                                    "per-table auto-reset: every table-step is live or deals the table's next hand"),
     # SURVEY 8(f) N1+N2+N3 together: what one iteration of the reference's training loop does around the step
     # (scripts/Poker/trainGPU_performance.py:176-206) with everything on the device: scripted opponent inside the
     # step, learning seat's actions supplied, hand statistics folded, learning-seat transitions appended to the
@@ -41,9 +57,14 @@ SPECS = {
                                 desc="PokerGPU heads-up, {n} tables/GPU, seat 0 = learner (uniform random actions supplied), "
                                      "seat 1 = TightAggressive rule inside the step kernel, per-table auto-reset, hand "
                                      "statistics and the learner's transitions (ring of 8M) gathered on the device every step"),
-    "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_step_kernel", graph=0, actions=8,
-                      desc="Blackjack, {n} envs/GPU (the reference's CPU-sized config), uniform hit/stand, whole-batch "
-                           "reset every 8 steps inside the timed region; working set is L2-resident by construction"),
+    "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_rollout_kernel<long>", graph=0, actions=8,
+                      desc="Blackjack, {n} envs/GPU (the reference's CPU-sized config), uniform hit/stand, hands of 8 steps: "
+                           "ONE launch deals the hand and plays its 8 steps (pulse_blackjack_rollout, outputs [8, N, ...]); "
+                           "working set is L2-resident by construction"),
+    # the same config one launch per step (the reference's call pattern, blackjack.py:179-186)
+    "blackjack_per_step": dict(n=4096, algo_bytes=50, kernel="blackjack_step_kernel", graph=0, actions=8,
+                               desc="Blackjack, {n} envs/GPU, uniform hit/stand, one launch per step, whole-batch reset every "
+                                    "8 steps inside the timed region"),
 }
 
 
@@ -64,6 +85,20 @@ def _make(name, dev, n, rank, e2e=False):
         def step(e, a):
             o, r, d, _, _ = e.step(a)
             return o, r, d
+    elif name == "tfe_4x4_rollout":
+        from pulselib_b200.envs.tfe import TFEBatched
+
+        env = TFEBatched(dev, n, side=4, seed=SEED, env_base=rank * n, auto_reset=True)
+        acts = torch.randint(0, 4, (L, n), dtype=torch.uint8, device=dev, generator=gen)
+        env._bench_k, env._bench_out = 0, None
+
+        def step(e, a):
+            k = e._bench_k % L
+            if k == 0:                                   # one launch plays the next L steps of every board
+                e._bench_out = e.rollout(acts)
+            e._bench_k += 1
+            o, r, d = e._bench_out
+            return o[k], r[k], d[k]
     elif name == "tetris":
         from pulselib_b200.envs.tetris import TetrisBatched
 
@@ -94,6 +129,18 @@ def _make(name, dev, n, rank, e2e=False):
         def step(e, a):
             o, r, d, _, info = e.step_policy(kinds)
             return o, r, d, info["actions"]
+    elif name == "poker_hu_autoreset":
+        from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+        env = PokerGPUPacked(dev, n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3,
+                             K=100, alpha=50, seed=SEED, env_base=rank * n, auto_reset=True, live_info=False)
+        acts = torch.randint(0, 13, (L, n), dtype=torch.int64, device=dev, generator=gen)
+        env._rew = torch.empty(n, dtype=torch.float32, device=dev)
+        env._done = torch.empty(n, dtype=torch.bool, device=dev)
+
+        def step(e, a):
+            e.step_into(a, e.obs, e._rew, e._done)
+            return e.obs, e._rew, e._done
     elif name == "poker_hu_train_loop":
         from pulselib_b200 import policy
         from pulselib_b200.envs.poker_packed import PokerGPUPacked
@@ -117,6 +164,20 @@ def _make(name, dev, n, rank, e2e=False):
             e._k += 1
             return o, r, d
     elif name == "blackjack":
+        from pulselib_b200.envs.blackjack import BlackJack
+
+        env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
+        acts = torch.randint(0, 2, (L, n), dtype=torch.int64, device=dev, generator=gen)
+        env._bench_k, env._bench_out = 0, None
+
+        def step(e, a):
+            k = e._bench_k % 8
+            if k == 0:                                   # one launch: deal + the hand's 8 steps
+                e._bench_out = e.rollout(acts, reset_first=True)
+            e._bench_k += 1
+            o, r, t = e._bench_out[:3]
+            return o[k], r[k], t[k]
+    elif name == "blackjack_per_step":
         from pulselib_b200.envs.blackjack import BlackJack
 
         env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
@@ -145,7 +206,9 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
     spec = SPECS[name]
     n = int(n or spec["n"])
     per_step_bytes = spec["algo_bytes"] * n
-    replicas = 1 if name == "blackjack" else max(1, int(-(-2.5 * L2_BYTES // per_step_bytes)))
+    # independent env batches stepped in rotation, so a batch's state was evicted from the 126 MB L2 before it is
+    # touched again (explicit where the state is much smaller than the algorithmic bytes: Tetris rows are 84 MB)
+    replicas = 1 if name.startswith("blackjack") else max(spec.get("replicas", 1), int(-(-2.5 * L2_BYTES // per_step_bytes)))
     made = [_make(name, dev, n, rank * 64 + r) for r in range(replicas)]
     envs, acts, step = [m[0] for m in made], made[0][1], made[0][2]
     L = acts.shape[0]
@@ -190,6 +253,15 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    live_fraction = None
+    if name in ("poker_hu_autoreset", "poker_hu_scripted"):
+        # tables that finish on a step are dealt by the next one instead of playing: live share of the table-steps
+        fin = 0.0
+        for j in range(32):
+            out = step(envs[0], acts[j % L])
+            fin += float(out[2].float().mean())
+        live_fraction = 1.0 - fin / 32
+
     barrier()
     pairs = []
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -205,8 +277,8 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
     barrier()
     total_ms = t0.elapsed_time(t1)
     kernel_ms = (sum(a.elapsed_time(b) for a, b in pairs) / len(pairs)) if pairs else total_ms / steps
-    launches = steps + (steps // 8 + 1 if name == "blackjack" else 0)
-    return dict(n=n, total_ms=total_ms, kernel_ms=kernel_ms, launches=launches, replicas=replicas,
+    launches = steps // 16 + 1 if name == "tfe_4x4_rollout" else steps // 8 + 1 if name == "blackjack" else steps + (steps // 8 + 1 if name == "blackjack_per_step" else 0)
+    return dict(n=n, total_ms=total_ms, kernel_ms=kernel_ms, launches=launches, replicas=replicas, live_fraction=live_fraction,
                 mode=f"cuda graph of {chunk} steps" if graph is not None else "eager launches",
                 kernel_time="graph time / steps (includes inter-kernel gaps)" if graph is not None
                 else "CUDA events around each step launch",
@@ -220,6 +292,8 @@ def e2e(name, dev, rank, steps, n=None, chunks=4):
 
     spec = SPECS[name]
     n = int(n or spec["n"])
+    if name == "blackjack":
+        return _e2e_blackjack_rollout(dev, rank, steps, n)
     chunks = chunks if n >= 1 << 16 else 1
     nc = n // chunks
     made = [_make(name, dev, nc, rank * 64 + 32 + c, e2e=True) for c in range(chunks)]
@@ -254,6 +328,35 @@ def e2e(name, dev, rank, steps, n=None, chunks=4):
                 d2h_bytes_per_step=d2h)
 
 
+def _e2e_blackjack_rollout(dev, rank, steps, n):
+    """Hands of 8 steps with HOST buffers: the hand's [8, N] action tape goes to the device, one launch deals and plays
+    the hand, the [8, N, ...] outputs come back -- per hand, inside the timed region."""
+    import torch
+    from pulselib_b200.envs.blackjack import BlackJack
+
+    env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
+    hands = max(1, steps // 8)
+    h_act = torch.randint(0, 2, (8, n), dtype=torch.uint8).pin_memory()
+    d_act = torch.empty((8, n), dtype=torch.uint8, device=dev)
+    h_obs = torch.empty((8, n, 3), dtype=torch.int32).pin_memory()
+    h_rew = torch.empty((8, n), dtype=torch.int32).pin_memory()
+    h_term = torch.empty((8, n), dtype=torch.bool).pin_memory()
+
+    def run(k):
+        for _ in range(k):
+            d_act.copy_(h_act, non_blocking=True)
+            o, r, t, _ = env.rollout(d_act, reset_first=True)
+            h_obs.copy_(o, non_blocking=True); h_rew.copy_(r, non_blocking=True); h_term.copy_(t, non_blocking=True)
+        torch.cuda.synchronize(dev)
+
+    run(3)
+    w0 = time.perf_counter()
+    run(hands)
+    ms = (time.perf_counter() - w0) * 1e3
+    return dict(value=n * 8 * hands / (ms * 1e-3), ms=ms, steps=8 * hands, chunks=1, h2d_bytes_per_step=n,
+                d2h_bytes_per_step=n * (12 + 4 + 1))
+
+
 def cpu_baseline(name, min_seconds=10.0):
     """The oracle port of the reference step (oracle/*.c, OpenMP over envs) on this box's host cores, on a
     bounded sample of the same workload.  Chance words / pieces are pre-generated outside the timed region."""
@@ -266,7 +369,7 @@ def cpu_baseline(name, min_seconds=10.0):
     cores = int(pyoracle.lib().oracle_set_threads(avail))   # torchrun exports OMP_NUM_THREADS=1: set it explicitly
     rng = np.random.default_rng(SEED)
     spent, steps = 0.0, 0
-    if name == "tfe_4x4":
+    if name in ("tfe_4x4", "tfe_4x4_rollout"):
         n = 1 << 20
         orc = pyoracle.OracleTFE(n, 4)
         orc.reset(rng.integers(0, 2**32, (n, 4), dtype=np.uint64).astype(np.uint32))
@@ -308,7 +411,7 @@ def cpu_baseline(name, min_seconds=10.0):
             spent += time.perf_counter() - t0
             steps += n; k += 1
         sample = f"{n} envs x {k} steps, oracle/oracle_core.c::oracle_particle2d_step"
-    elif name == "poker_hu_scripted":
+    elif name in ("poker_hu_scripted", "poker_hu_autoreset"):
         from pulselib_b200 import handranks
 
         n = 1 << 20
@@ -357,7 +460,7 @@ def cpu_baseline(name, min_seconds=10.0):
             steps += 16 * n; k += 16; hands += 1
         sample = (f"{n} tables x {hands} hands x 16 steps: oracle policy + step (OpenMP) + numpy hand statistics and ring "
                   f"append (the reference does these with torch masks), whole-batch hands")
-    elif name == "blackjack":
+    elif name in ("blackjack", "blackjack_per_step"):
         n = 4096
         orc = pyoracle.OracleBlackjack(n)
         acts = rng.integers(0, 2, (8, n)).astype(np.int64)

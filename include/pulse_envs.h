@@ -80,6 +80,15 @@ int pulse_tfe_step(uint64_t* boards, const void* actions, int action_bytes, cons
                    const uint32_t* reset_chance4_or_null, uint64_t seed, uint64_t env_base, uint32_t counter,
                    uint32_t* counter_dev_or_null, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
                    uint8_t* done_inout, int64_t* score_inout, int n_envs, int side, pulse_stream_t stream);
+/* K steps per launch (SURVEY.md 8(b) "K steps per launch"), for open-loop action tapes: actions uint8 / int64 [K, N];
+ * outputs step-major: obs_out int32 [K, N, side, side] (or NULL), reward_out int32 [K, N], done_out uint8 [K, N] --
+ * what K calls of pulse_tfe_step with tape counters counter .. counter + K - 1 would have written one after another
+ * (chance from the tape only).  The row table is staged once per K steps and a board stays in registers between its
+ * steps.  done_inout uint8 [N]: the per-board done flag as pulse_tfe_step keeps it. */
+int pulse_tfe_rollout(uint64_t* boards, const void* actions, int action_bytes, int n_steps, uint64_t seed,
+                      uint64_t env_base, uint32_t counter, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
+                      uint8_t* done_out, uint8_t* done_inout, int64_t* score_inout, int n_envs, int side,
+                      pulse_stream_t stream);
 int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, int side, pulse_stream_t stream);
 /* Domain audit of the packed boards (tile exponents up to 15 = 32768; two 32768 tiles meeting stay unmerged where the
  * reference would make 65536).  counts2 int [2] on the device, accumulated: [0] += boards holding a 32768 tile,
@@ -120,6 +129,16 @@ int pulse_blackjack_reset(uint32_t* st, uint8_t* deck, const uint8_t* injected_d
                           uint8_t* terminated_out, int n_envs, pulse_stream_t stream);
 int pulse_blackjack_step(uint32_t* st, const uint8_t* deck, const int64_t* actions, int32_t* obs_out,
                          int32_t* rewards_out, uint8_t* terminated_out, int n_envs, pulse_stream_t stream);
+/* K steps per launch: at the reference's own batch size (4096 envs) one step is launch-bound, so the
+ * loop over steps runs inside the kernel with the env's state word in registers.  actions: uint8 or int64 [K, N]
+ * (action_bytes 1 / 8); outputs step-major: obs_out int32 [K, N, 3], rewards_out int32 [K, N], terminated_out uint8
+ * [K, N] -- exactly what K calls of pulse_blackjack_step would have written.  reset_first != 0: deal a fresh hand from
+ * the tape (seed, env_base + i, episode) before the first step (= pulse_blackjack_reset; its observation goes to
+ * reset_obs_out_or_null int32 [N, 3]). */
+int pulse_blackjack_rollout(uint32_t* st, uint8_t* deck, const void* actions, int action_bytes, int n_steps,
+                            int reset_first, uint64_t seed, uint64_t env_base, uint32_t episode,
+                            int32_t* reset_obs_out_or_null, int32_t* obs_out, int32_t* rewards_out,
+                            uint8_t* terminated_out, int n_envs, pulse_stream_t stream);
 /* engine state -> the reference's tensor attributes (blackjack.py:24-44), for inspection / parity */
 typedef struct PulseBlackjackCompat {
   int64_t* decks;             /* [N,52] */
@@ -293,14 +312,14 @@ int pulse_poker_unpack_full(const PulsePokerPacked* st, const PulsePokerState* c
  * The reference's step contract (PokerGPU.py:527-633: int64 actions in; float32 [N, 13 + 3 (M - 1)] observations,
  * float32 rewards, bool dones out) for callers whose arrays live in host memory.  Per table-step 1 B goes to the
  * device (the action id) and, only for tables that were live when the step began, one packed record comes back
- * (csrc/poker_wire.cuh: 24 / 40 / 56 B for 2 / 6 / 10 seats, compacted in table order); a pool of host threads
+ * (csrc/poker_wire.cuh: 28 / 52 / 76 B for 2 / 6 / 10 seats, compacted in table order); a pool of host threads
  * expands the records into the caller's arrays.  A table that was already finished keeps its row in obs_host (the
  * reference returns the same row for it), reward 0, done 1 -- so the SAME obs / reward / done arrays must be passed to
  * every call of one env (the reference's `self.obs` is one buffer too, :176-179).  The arrays may be pageable.
  * The handle owns device state, pinned staging buffers, streams (one per chunk: copies and kernels of chunk c+1 overlap
  * the expansion of chunk c) and threads.  Unlike the rest of this header these calls allocate (create), block until
  * the outputs are complete (reset / step) and use their own streams.  Whole-batch hands only (no auto_reset).
- * Requires n_players * max_bbs < 16384 (every chip count must fit the record) and (n_players, max_players) in
+ * Requires n_players * max_bbs < 65536 (every chip count must fit the record's 16-bit fields) and (n_players, max_players) in
  * {(2,2), (3..4,4), (5..6,6), (7..10,10)}; other shapes use the device-buffer API above.
  * host_hand_ranks: the HandRanks table (pulse_handranks_generate), at least its first 36,875 entries.
  * n_chunks / n_threads < 1: 1 chunk / one thread per online CPU. */
@@ -318,9 +337,16 @@ int pulse_poker_host_step(PulsePokerHostEnv* env, const void* actions_host, int 
 /* record size, observation width, chunk / thread counts, and the bytes the last call moved over PCIe */
 int pulse_poker_host_info(const PulsePokerHostEnv* env, int* row_bytes, int* obs_width, int* chunks, int* threads,
                           long long* last_h2d_bytes, long long* last_d2h_bytes);
-/* pure host function: n_rows packed records -> float32 rows [n_rows, 13 + 3 (M - 1)], rewards, dones */
-int pulse_poker_wire_expand_host(const uint64_t* rows, long long n_rows, int active_players, int max_players,
+/* where the time of pulse_poker_host_step goes, accumulated in seconds: out6 = {calls, staging the actions, submitting
+ * GPU work, expansion phase (wall clock), worker seconds waiting for records, worker seconds expanding}; reset != 0
+ * clears the counters */
+int pulse_poker_host_timing(PulsePokerHostEnv* env, double* out6, int reset);
+/* pure host function: n_rows packed records (pkw_row_words(M) 32-bit words each) -> float32 rows [n_rows, 13 + 3 (M - 1)],
+ * rewards, dones.  vectorised != 0: through the host env's own expander (AVX2 when the CPU has it, see
+ * pulse_poker_host_expand_isa), else the portable definition -- the two must agree bit for bit. */
+int pulse_poker_wire_expand_host(const uint32_t* rows, long long n_rows, int max_players, int vectorised,
                                  float* obs_out, float* reward_out, uint8_t* done_out);
+const char* pulse_poker_host_expand_isa(void);
 
 /* ---- run statistics (the vector that is all-reduced across GPUs) -------------------
  * stats4 double [4] on the device: += {n, number of done flags set, sum(reward), sum(reward^2)}.

@@ -77,26 +77,26 @@ PULSE_HD BjState bj_deal(int c0, int c1, int c2, int c3) {
 }
 
 // reset of one env: decks come from `injected` (int32/int64-free: uint8 [N,52] row-major) or the tape
-PULSE_HD void bj_reset_one(uint32_t* __restrict__ st, uint8_t* __restrict__ deck, const uint8_t* __restrict__ injected,
-                           uint64_t seed, uint64_t env_base, uint32_t episode, int32_t* __restrict__ obs,
-                           int32_t* __restrict__ rewards, uint8_t* __restrict__ terminated, long long g, long long n) {
+PULSE_HD BjState bj_reset_state(uint32_t* __restrict__ st, uint8_t* __restrict__ deck, const uint8_t* __restrict__ injected,
+                                uint64_t seed, uint64_t env_base, uint32_t episode, long long g, long long n) {
   uint8_t d[52];
   if (injected) { for (int i = 0; i < 52; ++i) d[i] = injected[g * 52 + i]; }
   else bj_tape_deck(d, seed, env_base + (uint64_t)g, episode);
   for (int i = 0; i < 52; ++i) deck[(long long)i * n + g] = d[i];
   const BjState s = bj_deal(d[0], d[1], d[2], d[3]);
   st[g] = bj_pack(s);
+  return s;
+}
+PULSE_HD void bj_reset_one(uint32_t* __restrict__ st, uint8_t* __restrict__ deck, const uint8_t* __restrict__ injected,
+                           uint64_t seed, uint64_t env_base, uint32_t episode, int32_t* __restrict__ obs,
+                           int32_t* __restrict__ rewards, uint8_t* __restrict__ terminated, long long g, long long n) {
+  const BjState s = bj_reset_state(st, deck, injected, seed, env_base, episode, g, n);
   obs[3 * g] = s.psum; obs[3 * g + 1] = s.ace; obs[3 * g + 2] = s.upcard;
   rewards[g] = 0; terminated[g] = 0;
 }
 
-// step of one env (:179-186)
-PULSE_HD void bj_step_one(uint32_t* __restrict__ st, const uint8_t* __restrict__ deck, const int64_t* __restrict__ actions,
-                          int32_t* __restrict__ obs, int32_t* __restrict__ rewards, uint8_t* __restrict__ terminated,
-                          long long g, long long n) {
-  const uint32_t w0 = st[g];
-  BjState s = bj_unpack_word(w0);
-  const long long a = actions[g];
+// one step on a state held in registers (:179-186); returns the reward
+PULSE_HD int bj_step_state(BjState& s, long long a, const uint8_t* __restrict__ deck, long long g, long long n) {
   int reward = 0;                                      // :183 rewards.zero_()
   if (!s.term) {
     if (a == 0) {                                      // hit :117-135
@@ -112,6 +112,16 @@ PULSE_HD void bj_step_one(uint32_t* __restrict__ st, const uint8_t* __restrict__
       s.term = true;                                   // :177
     }
   }
+  return reward;
+}
+
+// step of one env (:179-186)
+PULSE_HD void bj_step_one(uint32_t* __restrict__ st, const uint8_t* __restrict__ deck, const int64_t* __restrict__ actions,
+                          int32_t* __restrict__ obs, int32_t* __restrict__ rewards, uint8_t* __restrict__ terminated,
+                          long long g, long long n) {
+  const uint32_t w0 = st[g];
+  BjState s = bj_unpack_word(w0);
+  const int reward = bj_step_state(s, actions[g], deck, g, n);
   const uint32_t w1 = bj_pack(s);
   if (w1 != w0) st[g] = w1;
   obs[3 * g] = s.psum; obs[3 * g + 1] = s.ace; obs[3 * g + 2] = s.upcard;  // :103-108

@@ -4,7 +4,7 @@
 // bool done flags out (/root/reference/environments/Poker/PokerGPU.py:527-633) -- for callers whose arrays live in host
 // memory.  What crosses PCIe is not that contract (8 B in, 69 B out per table-step heads-up) but:
 //   in   1 B per table (the action id, 0..12) + 4 B per 32 tables (where the warp's records go)
-//   out  one packed record (poker_wire.cuh: 24 B heads-up) per table that was LIVE when the step began, compacted
+//   out  one packed record (poker_wire.cuh: 28 B heads-up) per table that was LIVE when the step began, compacted
 // and a pool of host threads expands the records into the caller's arrays with streaming stores.  A table that was
 // already finished repeats its row (the caller's buffer keeps it), reward 0, done 1 -- exactly what the reference
 // returns for it.  The batch is cut into chunks, each on its own stream: chunk c+1's copies and step kernel run while
@@ -13,10 +13,12 @@
 // The handle owns its device state (the packed layout of poker_packed_body.cuh), pinned staging buffers, streams and
 // threads; the caller's arrays may be pageable.  One handle = one env on one GPU; calls on one handle are serial.
 #include "poker_packed_body.cuh"
+#include "host_expand.h"
 
 #include <emmintrin.h>
 
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -36,16 +38,16 @@ constexpr int kBlock = 128;
 template <int MAXP, int MT, int MINB>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_host_step_kernel(PulsePokerPacked S, PokerParams pr, const uint8_t* __restrict__ actions,
-                       const uint32_t* __restrict__ warp_off, uint64_t* __restrict__ wire, int starting_bbs,
+                       const uint32_t* __restrict__ warp_off, uint32_t* __restrict__ wire, int starting_bbs,
                        int max_bbs, long long first, long long last, long long n) {
   // one chunk of the batch: tables first .. last-1 (first a multiple of 1024); the seat-major arrays keep the whole
   // batch's stride n; warp_off and wire are the chunk's own
-  constexpr int R = (18 + 4 * (MT - 1) + 7) / 8;
+  constexpr int R = pkw_row_words(MT);
   pr.M = MT;
   const unsigned lane = threadIdx.x & 31u;
   for (long long base = first + (long long)blockIdx.x * kBlock; base < last; base += (long long)gridDim.x * kBlock) {
     const long long g = base + threadIdx.x;
-    uint64_t w[R];
+    uint32_t w[R];
     bool live = false;
     uint32_t off = 0;
     if (g < last) {
@@ -58,7 +60,7 @@ poker_host_step_kernel(PulsePokerPacked S, PokerParams pr, const uint8_t* __rest
     }
     const unsigned bal = __ballot_sync(0xFFFFFFFFu, live);
     if (live) {
-      uint64_t* dst = wire + ((size_t)off + __popc(bal & ((1u << lane) - 1u))) * R;
+      uint32_t* dst = wire + ((size_t)off + __popc(bal & ((1u << lane) - 1u))) * R;
 #pragma unroll
       for (int i = 0; i < R; ++i) dst[i] = w[i];
     }
@@ -68,14 +70,14 @@ poker_host_step_kernel(PulsePokerPacked S, PokerParams pr, const uint8_t* __rest
 // After a whole-batch deal: every table's record, uncompacted (slot = table), reward 0.
 template <int MAXP, int MT>
 __global__ void __launch_bounds__(kBlock)
-poker_host_rows_kernel(PulsePokerPacked S, PokerParams pr, uint64_t* __restrict__ wire, long long n) {
-  constexpr int R = (18 + 4 * (MT - 1) + 7) / 8;
+poker_host_rows_kernel(PulsePokerPacked S, PokerParams pr, uint32_t* __restrict__ wire, long long n) {
+  constexpr int R = pkw_row_words(MT);
   pr.M = MT;
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
     PokerTable<MAXP> t;
     uint32_t fb;
     packed_load(t, fb, S, g, n, pr.AP);
-    uint64_t w[R];
+    uint32_t w[R];
     pkw_pack_row<MAXP, MT>(t, pr, 0.0f, w);
 #pragma unroll
     for (int i = 0; i < R; ++i) wire[(size_t)g * R + i] = w[i];
@@ -130,27 +132,6 @@ class Pool {
   bool stop_ = false;
 };
 
-inline void store16(float* p, __m128 v, bool nt) {
-  if (nt) _mm_stream_ps(p, v); else _mm_storeu_ps(p, v);
-}
-
-// heads-up record (3 words) -> 16 floats; 64 B rows go out as four 16 B (streaming) stores
-inline void expand_hu(const uint64_t* w, float* o, float* reward, uint8_t* done, bool nt) {
-  const uint64_t h = w[0], a = w[1], b = w[2];
-  auto card = [](uint64_t x) { int c = (int)(x & 63u); return c ? c : -1; };
-  const __m128i v0 = _mm_set_epi32(card(h >> 18), card(h >> 12), card(h >> 6), card(h));
-  const __m128i v1 = _mm_set_epi32((int)((h >> 42) & 7u), card(h >> 36), card(h >> 30), card(h >> 24));
-  const __m128i v2 = _mm_set_epi32((int)((a >> 32) & 0xFFFFu), (int)((a >> 16) & 0xFFFFu), (int)(a & 0xFFFFu), (int)((h >> 45) & 15u));
-  const uint32_t s = (uint32_t)(a >> 48);
-  const __m128i v3 = _mm_set_epi32((int)(b & 0xFFFFu), (int)(s >> 14), (int)(s & 0x3FFFu), (int)((h >> 49) & 3u));
-  store16(o, _mm_cvtepi32_ps(v0), nt); store16(o + 4, _mm_cvtepi32_ps(v1), nt);
-  store16(o + 8, _mm_cvtepi32_ps(v2), nt); store16(o + 12, _mm_cvtepi32_ps(v3), nt);
-  union { float f; uint32_t x; } rb;
-  rb.x = (uint32_t)(b >> 32);
-  *reward = rb.f;
-  *done = (uint8_t)((h >> 51) & 1u);
-}
-
 }  // namespace
 
 struct PulsePokerHostEnv {
@@ -162,16 +143,24 @@ struct PulsePokerHostEnv {
   long long N = 0, Nc = 0;                 // tables, tables per chunk (a multiple of 1024; the last chunk may be short)
   PulsePokerPacked st{};
   std::vector<void*> dev_allocs, pin_allocs;
-  uint8_t* d_act = nullptr; uint32_t* d_off = nullptr; uint64_t* d_wire = nullptr;
-  uint8_t* h_act = nullptr; uint32_t* h_off = nullptr; uint64_t* h_wire = nullptr;
+  uint8_t* d_act = nullptr; uint32_t* d_off = nullptr; uint32_t* d_wire = nullptr;
+  uint8_t* h_act = nullptr; uint32_t* h_off = nullptr; uint32_t* h_wire = nullptr;
   std::vector<uint32_t> live;              // bit b of live[w]: table 32 w + b was not done after the last call
   std::vector<long long> chunk_rows;       // live tables per chunk at the start of the next step
   std::vector<cudaStream_t> streams;
   std::vector<cudaEvent_t> events;
+  std::atomic<int>* ready = nullptr;       // per chunk: its records have landed in h_wire (set by a stream host callback)
+  std::atomic<int>* remaining = nullptr;   // per chunk: workers still expanding it (the last one rebuilds its offsets)
   Pool* pool = nullptr;
   long long last_h2d = 0, last_d2h = 0;
+  // seconds, accumulated over calls: staging the actions, submitting GPU work, the expansion phase (wall), and summed
+  // over workers: time spent waiting for records / time spent expanding
+  double t_stage = 0, t_submit = 0, t_expand = 0, t_wait_sum = 0, t_work_sum = 0;
+  long long calls = 0;
   ~PulsePokerHostEnv() {
     delete pool;
+    delete[] ready;
+    delete[] remaining;
     cudaSetDevice(device);
     for (auto s : streams) cudaStreamDestroy(s);
     for (auto e : events) cudaEventDestroy(e);
@@ -220,83 +209,79 @@ PokerParams params_of(const PulsePokerConfig& c) {
     else { pulse_set_error("host env: unsupported (n_players, max_players)"); return PULSE_EUNSUPPORTED; } \
   } while (0)
 
-// Expands the records of tables [g0, g1) (g0 a multiple of 32) of one chunk.  rows: the chunk's records; off: the
-// chunk's per-warp offsets (nullptr: uncompacted, slot = table - chunk start).  Rewrites the live mask.
-void expand_range(PulsePokerHostEnv* e, long long chunk_first, long long g0, long long g1, const uint64_t* rows,
-                  const uint32_t* off, float* obs, float* reward, uint8_t* done, bool fresh) {
-  const int R = e->R, W = e->W, AP = e->cfg.active_players, M = e->cfg.max_players;
-  const bool hu = (R == 3 && W == 16 && AP == 2);
-  const bool nt = hu && ((reinterpret_cast<uintptr_t>(obs) & 15u) == 0);
-  for (long long wg = g0 >> 5; wg < ((g1 + 31) >> 5); ++wg) {
-    const long long gb = wg << 5;
-    const int cnt = (int)((g1 - gb) < 32 ? (g1 - gb) : 32);
-    const uint32_t mask = fresh ? 0xFFFFFFFFu : e->live[wg];
-    uint32_t next = 0;
-    size_t slot = off ? off[wg - (chunk_first >> 5)] : (size_t)(gb - chunk_first);
-    for (int b = 0; b < cnt; ++b) {
-      const long long g = gb + b;
-      if ((mask >> b) & 1u) {
-        const uint64_t* w = rows + slot * R;
-        ++slot;
-        uint8_t d;
-        if (hu) expand_hu(w, obs + g * 16, reward + g, &d, nt);
-        else pkw_expand_row(w, AP, M, obs + g * W, reward + g, &d);
-        done[g] = d;
-        next |= (uint32_t)(d ? 0u : 1u) << b;
-      } else {
-        reward[g] = 0.0f;                                  // PokerGPU.py:632; done stays 1, the row stays as it is
-      }
-    }
-    e->live[wg] = next;
+// per-warp offsets of one chunk for the NEXT step, and the chunk's record count
+void rebuild_offsets(PulsePokerHostEnv* e, int c) {
+  const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
+  uint32_t* off = e->h_off + (first >> 5) + c;           // each chunk has (Nc / 32 + 1) entries
+  uint32_t acc = 0;
+  for (long long wg = first >> 5; wg < ((last + 31) >> 5); ++wg) {
+    off[wg - (first >> 5)] = acc;
+    acc += (uint32_t)__builtin_popcount(e->live[wg]);
   }
-  if (nt) _mm_sfence();
+  off[((last + 31) >> 5) - (first >> 5)] = acc;
+  e->chunk_rows[c] = acc;
 }
 
-// per-warp offsets of every chunk for the NEXT step, and the chunks' record counts
-void rebuild_offsets(PulsePokerHostEnv* e) {
-  e->pool->run([e](int wk) {
-    for (int c = wk; c < e->chunks; c += e->pool->size()) {
-      const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
-      uint32_t* off = e->h_off + (first >> 5) + c;           // each chunk has (Nc / 32 + 1) entries
-      uint32_t acc = 0;
-      for (long long wg = first >> 5; wg < ((last + 31) >> 5); ++wg) {
-        off[wg - (first >> 5)] = acc;
-        acc += (uint32_t)__builtin_popcount(e->live[wg]);
-      }
-      off[((last + 31) >> 5) - (first >> 5)] = acc;
-      e->chunk_rows[c] = acc;
-    }
-  });
-}
+void CUDART_CB mark_ready(void* p) { static_cast<std::atomic<int>*>(p)->store(1, std::memory_order_release); }
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 template <int MP, int MT>
 void launch_step_t(PulsePokerHostEnv* e, const PokerParams& pr, long long first, long long cnt, const uint32_t* d_off,
-                   uint64_t* d_rows, cudaStream_t s) {
+                   uint32_t* d_rows, cudaStream_t s) {
   constexpr int MINB = MP <= 2 ? 8 : MP <= 6 ? 6 : 4;   // resident CTAs per SM, as for the float32-row step
   poker_host_step_kernel<MP, MT, MINB><<<pulse_grid_for(cnt, kBlock), kBlock, 0, s>>>(
       e->st, pr, e->d_act, d_off, d_rows, e->cfg.starting_bbs, e->cfg.max_bbs, first, first + cnt, e->N);
 }
 
 int launch_step(PulsePokerHostEnv* e, const PokerParams& pr, long long first, long long cnt, const uint32_t* d_off,
-                uint64_t* d_rows, cudaStream_t s) {
+                uint32_t* d_rows, cudaStream_t s) {
   HE_DISPATCH(pr.P, pr.M, (launch_step_t<MP, MT>(e, pr, first, cnt, d_off, d_rows, s)));
   return pulse_check_launch("pulse_poker_host_step");
 }
 
+// Every worker walks the chunks in order: waits until the chunk's records have landed (a host callback on the chunk's
+// stream raises its flag), expands its own slice, and the last worker out of a chunk rebuilds that chunk's offsets for
+// the next step.  No barrier between chunks: chunk c+1's copy overlaps chunk c's expansion.
 int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* reward, uint8_t* done, bool fresh) {
-  for (int c = 0; c < e->chunks; ++c) {
-    HE_CUDA(cudaEventSynchronize(e->events[c]));
-    const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
-    const uint64_t* rows = e->h_wire + (size_t)first * e->R;
-    const uint32_t* off = compacted ? e->h_off + (first >> 5) + c : nullptr;
-    e->pool->run([=](int wk) {
-      const int T = e->pool->size();
+  const int T = e->pool->size();
+  for (int c = 0; c < e->chunks; ++c) e->remaining[c].store(T, std::memory_order_relaxed);
+  std::atomic<int> failed{0};
+  std::vector<double> waits((size_t)T, 0.0), works((size_t)T, 0.0);
+  const double t0 = now_s();
+  e->pool->run([&, e, compacted, obs, reward, done, fresh, T](int wk) {
+    for (int c = 0; c < e->chunks; ++c) {
+      const double w0 = now_s();
+      long long spins = 0;
+      // spin briefly, then yield: with every CPU spinning, the driver thread that runs the stream callbacks (and so
+      // raises these flags) gets no core -- measured: 16 spinning workers on 16 CPUs waited 4.5 ms per step
+      while (!e->ready[c].load(std::memory_order_acquire)) {
+        if (++spins < 512) _mm_pause();
+        else std::this_thread::yield();
+        if ((spins & 0xFFFF) == 0 && now_s() - w0 > 60.0) { failed.store(1); return; }   // a dead GPU must not hang the caller
+      }
+      const double w1 = now_s();
+      const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
       const long long per = (((last - first) + T - 1) / T + 31) & ~31LL;
       const long long g0 = first + wk * per, g1 = (g0 + per < last) ? g0 + per : last;
-      if (g0 < g1) expand_range(e, first, g0, g1, rows, off, obs, reward, done, fresh);
-    });
-  }
-  rebuild_offsets(e);
+      if (g0 < g1) {
+        PulseExpandArgs a;
+        a.rows = e->h_wire + (size_t)first * e->R;
+        a.off = compacted ? e->h_off + (first >> 5) + c : nullptr;
+        a.live = e->live.data(); a.chunk_first = first; a.g0 = g0; a.g1 = g1;
+        a.row_words = e->R; a.obs_width = e->W; a.max_players = e->cfg.max_players;
+        a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh;
+        pulse_expand_range(a);
+      }
+      if (e->remaining[c].fetch_sub(1, std::memory_order_acq_rel) == 1) rebuild_offsets(e, c);
+      const double w2 = now_s();
+      waits[wk] += w1 - w0; works[wk] += w2 - w1;
+    }
+  });
+  e->t_expand += now_s() - t0;
+  for (int i = 0; i < T; ++i) { e->t_wait_sum += waits[i]; e->t_work_sum += works[i]; }
+  for (int c = 0; c < e->chunks; ++c) e->ready[c].store(0, std::memory_order_relaxed);
+  if (failed.load()) { pulse_set_error("host env: timed out waiting for the device"); return PULSE_ENOTREADY; }
   return 0;
 }
 
@@ -312,8 +297,8 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
   PULSE_REQUIRE(cfg->n_players >= 2 && cfg->n_players <= 10, "n_players must be in 2..10");
   PULSE_REQUIRE(cfg->active_players >= 2 && cfg->active_players <= cfg->n_players, "active_players must be in 2..n_players");
   PULSE_REQUIRE(cfg->n_games > 0, "n_games must be positive");
-  PULSE_REQUIRE((long long)cfg->n_players * cfg->max_bbs < 16384 && cfg->starting_bbs <= cfg->max_bbs,
-                "n_players * max_bbs must be below 16384 for the packed records (use the device-buffer API otherwise)");
+  PULSE_REQUIRE((long long)cfg->n_players * cfg->max_bbs < 65536 && cfg->starting_bbs <= cfg->max_bbs,
+                "n_players * max_bbs must be below 65536 for the packed records (use the device-buffer API otherwise)");
   PULSE_REQUIRE(host_hand_ranks && n_hand_ranks >= 36875, "the HandRanks table (at least its first 36,875 entries) is required");
   const int P = cfg->n_players, M = cfg->max_players;
   if (!((P <= 2 && M == 2) || (P > 2 && P <= 4 && M == 4) || (P > 4 && P <= 6 && M == 6) || (P > 6 && M == 10))) {
@@ -355,6 +340,9 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
     e->streams.push_back(s); e->events.push_back(ev);
   }
   e->pool = new Pool(n_threads);
+  e->ready = new std::atomic<int>[e->chunks];
+  e->remaining = new std::atomic<int>[e->chunks];
+  for (int c = 0; c < e->chunks; ++c) { e->ready[c].store(0); e->remaining[c].store(0); }
   *out = e;
   return PULSE_OK;
 }
@@ -382,12 +370,11 @@ int pulse_poker_host_reset(PulsePokerHostEnv* e, int active_players, int rotatio
   for (int c = 0; c < e->chunks; ++c) {
     const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
     if (c > 0) HE_CUDA(cudaStreamWaitEvent(e->streams[c], e->events[0], 0));
-    HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, e->d_wire + (size_t)first * e->R, (size_t)cnt * e->R * 8,
+    HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, e->d_wire + (size_t)first * e->R, (size_t)cnt * e->R * 4,
                             cudaMemcpyDeviceToHost, e->streams[c]));
   }
-  // events[0] must complete after chunk 0's copy: re-record in order
-  for (int c = 0; c < e->chunks; ++c) HE_CUDA(cudaEventRecord(e->events[c], e->streams[c]));
-  e->last_h2d = 0; e->last_d2h = (long long)e->N * e->R * 8;
+  for (int c = 0; c < e->chunks; ++c) HE_CUDA(cudaLaunchHostFunc(e->streams[c], mark_ready, &e->ready[c]));
+  e->last_h2d = 0; e->last_d2h = (long long)e->N * e->R * 4;
   // reward / done scratch when the caller does not want them
   std::vector<float> rtmp; std::vector<uint8_t> dtmp;
   float* rw = reward_host_or_null; uint8_t* dn = done_host_or_null;
@@ -404,6 +391,7 @@ int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int ac
   HE_CUDA(cudaSetDevice(e->device));
   const PokerParams pr = params_of(e->cfg);
   // stage the actions in pinned memory as bytes
+  const double t_stage0 = now_s();
   e->pool->run([=](int wk) {
     const int T = e->pool->size();
     const long long per = ((e->N + T - 1) / T + 63) & ~63LL;
@@ -416,6 +404,8 @@ int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int ac
       for (long long i = a; i < b; ++i) { const int64_t v = src[i]; e->h_act[i] = v < 0 ? (uint8_t)255 : v > 12 ? (uint8_t)13 : (uint8_t)v; }
     }
   });
+  const double t_sub0 = now_s();
+  e->t_stage += t_sub0 - t_stage0;
   long long h2d = 0, d2h = 0;
   for (int c = 0; c < e->chunks; ++c) {
     const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
@@ -425,22 +415,23 @@ int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int ac
     HE_CUDA(cudaMemcpyAsync(e->d_act + first, e->h_act + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
     HE_CUDA(cudaMemcpyAsync(d_off, e->h_off + (first >> 5) + c, (size_t)n_off * 4, cudaMemcpyHostToDevice, s));
     h2d += cnt + n_off * 4;
-    uint64_t* d_rows = e->d_wire + (size_t)first * e->R;
+    uint32_t* d_rows = e->d_wire + (size_t)first * e->R;
     int rc = launch_step(e, pr, first, cnt, d_off, d_rows, s);
     if (rc) return rc;
-    const size_t bytes = (size_t)e->chunk_rows[c] * e->R * 8;
+    const size_t bytes = (size_t)e->chunk_rows[c] * e->R * 4;
     if (bytes) HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, d_rows, bytes, cudaMemcpyDeviceToHost, s));
     d2h += (long long)bytes;
-    HE_CUDA(cudaEventRecord(e->events[c], s));
+    HE_CUDA(cudaLaunchHostFunc(s, mark_ready, &e->ready[c]));
   }
   e->last_h2d = h2d; e->last_d2h = d2h;
+  e->t_submit += now_s() - t_sub0; e->calls += 1;
   return expand_chunks(e, true, obs_host, reward_host, done_host, false);
 }
 
 int pulse_poker_host_info(const PulsePokerHostEnv* e, int* row_bytes, int* obs_width, int* chunks, int* threads,
                           long long* last_h2d_bytes, long long* last_d2h_bytes) {
   PULSE_REQUIRE(e != nullptr, "null env");
-  if (row_bytes) *row_bytes = e->R * 8;
+  if (row_bytes) *row_bytes = e->R * 4;
   if (obs_width) *obs_width = e->W;
   if (chunks) *chunks = e->chunks;
   if (threads) *threads = e->pool->size();
@@ -449,15 +440,38 @@ int pulse_poker_host_info(const PulsePokerHostEnv* e, int* row_bytes, int* obs_w
   return PULSE_OK;
 }
 
-// pure host function (no GPU): one record -> the reference's float32 row; exported for tests and for callers that
-// keep the compact records and expand rows on demand
-int pulse_poker_wire_expand_host(const uint64_t* rows, long long n_rows, int active_players, int max_players,
-                                 float* obs_out, float* reward_out, uint8_t* done_out) {
-  PULSE_REQUIRE(rows && obs_out && reward_out && done_out, "null argument");
-  PULSE_REQUIRE(max_players >= 2 && max_players <= 16 && active_players >= 2 && active_players <= max_players, "bad table size");
-  const int R = pkw_row_words(max_players), W = 13 + 3 * (max_players - 1);
-  for (long long i = 0; i < n_rows; ++i)
-    pkw_expand_row(rows + (size_t)i * R, active_players, max_players, obs_out + (size_t)i * W, reward_out + i, done_out + i);
+// seconds accumulated since creation (or the last call with reset != 0): out6 = {calls, staging the actions, submitting
+// GPU work, the expansion phase (wall clock), worker time waiting for records (summed over workers), worker time
+// expanding (summed over workers)}
+int pulse_poker_host_timing(PulsePokerHostEnv* e, double* out6, int reset) {
+  PULSE_REQUIRE(e && out6, "null argument");
+  out6[0] = (double)e->calls; out6[1] = e->t_stage; out6[2] = e->t_submit; out6[3] = e->t_expand;
+  out6[4] = e->t_wait_sum; out6[5] = e->t_work_sum;
+  if (reset) { e->calls = 0; e->t_stage = e->t_submit = e->t_expand = e->t_wait_sum = e->t_work_sum = 0; }
   return PULSE_OK;
 }
+
+// pure host function (no GPU): one record -> the reference's float32 row; exported for tests and for callers that
+// keep the compact records and expand rows on demand
+int pulse_poker_wire_expand_host(const uint32_t* rows, long long n_rows, int max_players, int vectorised,
+                                 float* obs_out, float* reward_out, uint8_t* done_out) {
+  PULSE_REQUIRE(rows && obs_out && reward_out && done_out, "null argument");
+  PULSE_REQUIRE(max_players >= 2 && max_players <= 16, "bad table size");
+  const int R = pkw_row_words(max_players), W = 13 + 3 * (max_players - 1);
+  if (!vectorised) {   // the portable definition (poker_wire.cuh)
+    for (long long i = 0; i < n_rows; ++i)
+      pkw_expand_row(rows + (size_t)i * R, max_players, obs_out + (size_t)i * W, reward_out + i, done_out + i);
+    return PULSE_OK;
+  }
+  // the host env's own expander (AVX2 when the CPU has it), driven as one chunk in which every table has a record
+  std::vector<uint32_t> live((size_t)(n_rows + 31) / 32 + 1, 0u);
+  PulseExpandArgs a;
+  a.rows = rows; a.off = nullptr; a.live = live.data(); a.chunk_first = 0; a.g0 = 0; a.g1 = n_rows;
+  a.row_words = R; a.obs_width = W; a.max_players = max_players;
+  a.obs = obs_out; a.reward = reward_out; a.done = done_out; a.fresh = true;
+  pulse_expand_range(a);
+  return PULSE_OK;
+}
+
+const char* pulse_poker_host_expand_isa(void) { return pulse_expand_isa(); }
 }

@@ -1,0 +1,92 @@
+// Host expander of the PokerGPU host-buffer path (csrc/host_env.cu): packed step records -> the reference's float32
+// observation rows, rewards and done flags in the caller's arrays.  The record (poker_wire.cuh) is laid out so that
+// this is "widen and convert": eight int8 columns, then uint16 columns in observation order.  Heads-up rows are 64 B =
+// one cache line and go out as two 32-byte streaming stores (no read-for-ownership of a line that is fully rewritten).
+// Plain host C++ (no CUDA): compiled for the baseline x86-64 ISA, with an AVX2 body selected at run time.
+#include "host_expand.h"
+
+#include <immintrin.h>
+#include <string.h>
+
+namespace {
+
+inline void expand_row_portable(const uint32_t* w, int W, int R, float* o, float* reward, uint8_t* done) {
+  const int8_t* b = reinterpret_cast<const int8_t*>(w);
+  for (int i = 0; i < 8; ++i) o[i] = (float)b[i];
+  const uint16_t* u = reinterpret_cast<const uint16_t*>(w + 2);
+  for (int p = 0; p < W - 8; ++p) o[8 + p] = (float)u[p];
+  o[12] = (float)(u[4] & 0x7FFFu);
+  *done = (uint8_t)(u[4] >> 15);
+  memcpy(reward, w + R - 1, 4);
+}
+
+__attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, int W, int R, float* o, float* reward,
+                                                            uint8_t* done, bool line_rows) {
+  const __m256i keep = _mm256_setr_epi32(0xFFFF, 0xFFFF, 0xFFFF, 0xFFFF, 0x7FFF, 0xFFFF, 0xFFFF, 0xFFFF);  // column 12: status without the done bit
+  const __m256 f0 = _mm256_cvtepi32_ps(_mm256_cvtepi8_epi32(_mm_loadl_epi64(reinterpret_cast<const __m128i*>(w))));
+  const __m256 f1 = _mm256_cvtepi32_ps(_mm256_and_si256(
+      _mm256_cvtepu16_epi32(_mm_loadu_si128(reinterpret_cast<const __m128i*>(w + 2))), keep));
+  if (line_rows) {           // heads-up, 32-byte aligned rows: the whole cache line, streamed
+    _mm256_stream_ps(o, f0);
+    _mm256_stream_ps(o + 8, f1);
+  } else {
+    _mm256_storeu_ps(o, f0);
+    _mm256_storeu_ps(o + 8, f1);
+    const uint16_t* u = reinterpret_cast<const uint16_t*>(w + 2);
+    int p = 8;
+    for (; p + 8 <= W - 8; p += 8)
+      _mm256_storeu_ps(o + 8 + p, _mm256_cvtepi32_ps(_mm256_cvtepu16_epi32(_mm_loadu_si128(reinterpret_cast<const __m128i*>(u + p)))));
+    for (; p < W - 8; ++p) o[8 + p] = (float)u[p];
+  }
+  *done = (uint8_t)((w[4] >> 15) & 1u);
+  memcpy(reward, w + R - 1, 4);
+}
+
+#define EXPAND_BODY(ROW_CALL)                                                                                   \
+  const int R = a.row_words, W = a.obs_width;                                                                   \
+  for (long long wg = a.g0 >> 5; wg < ((a.g1 + 31) >> 5); ++wg) {                                               \
+    const long long gb = wg << 5;                                                                               \
+    const int cnt = (int)((a.g1 - gb) < 32 ? (a.g1 - gb) : 32);                                                 \
+    const uint32_t mask = a.fresh ? 0xFFFFFFFFu : a.live[wg];                                                   \
+    uint32_t next = 0;                                                                                          \
+    size_t slot = a.off ? a.off[wg - (a.chunk_first >> 5)] : (size_t)(gb - a.chunk_first);                      \
+    /* tables that were already finished: reward 0 (PokerGPU.py:632), done stays 1, the row stays as it is */   \
+    if (mask != 0xFFFFFFFFu || cnt != 32) memset(a.reward + gb, 0, sizeof(float) * (size_t)cnt);               \
+    uint32_t m = cnt == 32 ? mask : (mask & ((1u << cnt) - 1u));                                                \
+    while (m) {                                                                                                 \
+      const int b = __builtin_ctz(m);                                                                           \
+      m &= m - 1;                                                                                               \
+      const long long g = gb + b;                                                                               \
+      const uint32_t* w = a.rows + slot * R;                                                                    \
+      ++slot;                                                                                                   \
+      uint8_t d;                                                                                                \
+      ROW_CALL;                                                                                                 \
+      a.done[g] = d;                                                                                            \
+      next |= (uint32_t)(d ? 0u : 1u) << b;                                                                     \
+    }                                                                                                           \
+    a.live[wg] = next;                                                                                          \
+  }
+
+void expand_range_portable(const PulseExpandArgs& a) {
+  EXPAND_BODY(expand_row_portable(w, W, R, a.obs + g * W, a.reward + g, &d))
+}
+
+__attribute__((target("avx2"))) void expand_range_avx2(const PulseExpandArgs& a) {
+  const bool line_rows = a.obs_width == 16 && (reinterpret_cast<uintptr_t>(a.obs) & 31u) == 0;
+  EXPAND_BODY(expand_row_avx2(w, W, R, a.obs + g * W, a.reward + g, &d, line_rows))
+  if (line_rows) _mm_sfence();
+}
+
+bool have_avx2() {
+  static const bool v = __builtin_cpu_supports("avx2");
+  return v;
+}
+
+}  // namespace
+
+void pulse_expand_range(const PulseExpandArgs& a) {
+  if (have_avx2()) expand_range_avx2(a);
+  else expand_range_portable(a);
+}
+
+const char* pulse_expand_isa(void) { return have_avx2() ? "avx2" : "portable"; }

@@ -126,47 +126,40 @@ PULSE_HD float pk_equity(int stage, int h0, int h1, const int32_t (&board)[5],
   return fminf(fmaxf(e, 0.0f), 1.0f);
 }
 
-// execute_actions for the seat to act (:230-303)
+// execute_actions for the seat to act (:230-303).  Written without branches on the action kind: fold, call and the
+// raises of one warp's tables otherwise run as three instruction streams one after another (13-17 of 32 lanes per
+// instruction in the r2b profile); every table computes the raise amount and the bet, selects decide what is kept.
 template <int MAXP>
 PULSE_HD void pk_execute(PokerTable<MAXP>& t, long long a) {
   const int idx = t.idx;
-  int stat = pk_status(t.st, idx);
-  if (stat != PK_ACTIVE || t.done) return;  // :233
-  if (a < 0) return;                        // matches no mask in the reference
+  // acts only if ACTIVE and the table is not done (:233); negative ids match no mask in the reference
+  const bool act = pk_status(t.st, idx) == PK_ACTIVE && !t.done && a >= 0;
+  if (!act) return;
   int stack = pk_sel(t.stack, idx), crb = pk_sel(t.crb, idx), inv = pk_sel(t.inv, idx);
-  int call_cost = t.highest - crb;  // :232
-  if (a == 0) {                     // :236-238
-    t.st = pk_set_status(t.st, idx, PK_FOLDED);
-    t.acted += 1;
-    return;
-  }
-  int bet;
-  bool is_raise = false;
-  if (a == 1) {  // :241-252
-    bet = call_cost < stack ? call_cost : stack;
-  } else {       // :255-303
-    int raise_amt = 0;
-    if (a == 2) raise_amt = t.last_raise;  // :259
-    else if (a == 12) raise_amt = stack;   // :264
-    else if (a <= 11) {
-      const float fr[9] = {0.25f, 0.33f, 0.50f, 0.75f, 1.00f, 1.50f, 2.00f, 3.00f, 4.00f};  // :39
-      float f = fr[0];
-#pragma unroll
-      for (int k = 1; k < 9; ++k) if (a - 3 == k) f = fr[k];
-      raise_amt = PULSE_F2I_RZ(PULSE_FMUL((float)t.pot, f));  // :270 one fp32 multiply, truncation
-    }
-    bet = (call_cost + raise_amt) < stack ? (call_cost + raise_amt) : stack;  // :272-273
-    is_raise = bet > call_cost;               // :274-275
-  }
+  const int call_cost = t.highest - crb;    // :232
+  const bool fold = a == 0;                 // :236-238
+  const bool raise = a >= 2;                // :255-303 (ids above 12 raise by nothing)
+  float f = 0.25f;                          // raise_fractions (:39), ids 3..11
+  f = a == 4 ? 0.33f : f; f = a == 5 ? 0.50f : f; f = a == 6 ? 0.75f : f; f = a == 7 ? 1.00f : f;
+  f = a == 8 ? 1.50f : f; f = a == 9 ? 2.00f : f; f = a == 10 ? 3.00f : f; f = a == 11 ? 4.00f : f;
+  int raise_amt = PULSE_F2I_RZ(PULSE_FMUL((float)t.pot, f));   // :270 one fp32 multiply, truncation
+  raise_amt = a == 2 ? t.last_raise : raise_amt;                // :259
+  raise_amt = a == 12 ? stack : raise_amt;                      // :264
+  raise_amt = (a < 2 || a > 12) ? 0 : raise_amt;
+  const int want = call_cost + raise_amt;                        // a == 1: call_cost (:241-252); :272-273
+  int bet = want < stack ? want : stack;
+  bet = fold ? 0 : bet;
+  const bool is_raise = raise && bet > call_cost;                // :274-275
   stack -= bet; crb += bet; inv += bet; t.pot += bet;
-  if (stack == 0) t.st = pk_set_status(t.st, idx, PK_ALLIN);
+  if (fold) t.st = pk_set_status(t.st, idx, PK_FOLDED);
+  else if (stack == 0) t.st = pk_set_status(t.st, idx, PK_ALLIN);
   pk_put(t.stack, idx, stack); pk_put(t.crb, idx, crb); pk_put(t.inv, idx, inv);
   if (is_raise) {  // :288-301
-    int size = crb - t.highest;
+    const int size = crb - t.highest;
     t.highest = crb;
     if (size >= t.last_raise) { t.agg = idx; t.acted = 0; t.last_raise = size; }
   }
-  t.acted += 1;  // :252, :303
+  t.acted += 1;  // :238, :252, :303
 }
 
 // next actor, round close, street transition (:547-616).  Deck::card(pos) returns the card at a
@@ -262,6 +255,22 @@ PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck
   }
   if (t.stage <= 1) { t.deck_pos += 1; t.board[3] = deck.card(t.deck_pos); t.deck_pos += 1; }  // :407-411
   if (t.stage <= 2) { t.deck_pos += 1; t.board[4] = deck.card(t.deck_pos); t.deck_pos += 1; }  // :416-419
+  if (MAXP == 2) {
+    // Two seats, both live: the side-pot layers of :346-378 in closed form.  Layer 1 (up to the smaller investment,
+    // two contributors) goes to the better hand, split evenly on a tie (2 lo is even: no remainder); layer 2 (the
+    // excess of the bigger investment, one contributor, who is live) goes back to that seat.
+    const int32_t r0 = ranker.rank(t, 0), r1 = ranker.rank(t, 1);
+    const int32_t i0 = t.inv[0], i1 = t.inv[1];
+    const int32_t lo = i0 < i1 ? i0 : i1, hi = i0 < i1 ? i1 : i0;
+    if (lo > 0) {
+      t.stack[0] += r0 > r1 ? 2 * lo : r0 == r1 ? lo : 0;
+      t.stack[1] += r1 > r0 ? 2 * lo : r0 == r1 ? lo : 0;
+    }
+    if (i0 > i1) t.stack[0] += hi - lo;
+    if (i1 > i0) t.stack[1] += hi - lo;
+    t.pot = 0; t.stage = 5;                                 // :452-453
+    return;
+  }
   int32_t rank[MAXP];
 #pragma unroll
   for (int s = 0; s < MAXP; ++s) {                          // :427-450
@@ -307,12 +316,15 @@ PULSE_HD void pk_showdown(PokerTable<MAXP>& t, const PokerParams& pr, const Deck
 template <int MAXP>
 PULSE_HD float pk_reward(const PokerTable<MAXP>& t, const PokerParams& pr, long long a,
                                            float e, int prev_inv) {
-  float cnt = (float)PULSE_POPC(pk_live_mask(t.st, pr.P));       // :309
-  float fair = PULSE_FDIV(1.0f, fmaxf(cnt, 1.0f));            // :310
+  const int cnt = PULSE_POPC(pk_live_mask(t.st, pr.P));           // :309
+  // :310 fair = 1 / max(cnt, 1): for one or two live seats the quotient is exact, no division needed
+  const float fair = cnt <= 1 ? 1.0f : cnt == 2 ? 0.5f : PULSE_FDIV(1.0f, (float)cnt);
   int cc = t.highest - prev_inv; if (cc < 0) cc = 0;                     // :311
   float pot = (float)t.pot;
   float m = PULSE_FMUL(e, pot);                               // :315
-  float o = PULSE_FDIV((float)cc, PULSE_FADD((float)(t.pot + cc), 1e-6f));  // :316
+  // :316; nothing to call is the common case and 0 / x is exactly 0 -- and a zero numerator sends the IEEE division
+  // down its slow-path subroutine (5% of the step's instructions in the r2b profile)
+  float o = cc == 0 ? 0.0f : PULSE_FDIV((float)cc, PULSE_FADD((float)(t.pot + cc), 1e-6f));
   float s = 0.0f;
   if (a == 1) s = PULSE_FMUL(PULSE_FSUB(e, o), pot);           // :326
   else if (a == 0) s = PULSE_FMUL(PULSE_FSUB(o, e), pot);      // :327

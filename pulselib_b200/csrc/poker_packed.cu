@@ -94,7 +94,18 @@ __device__ __forceinline__ void packed_prefetch_tile(const PulsePokerPacked& S, 
   }
 }
 
-template <int MAXP, int MT, int MINB, bool POLICY = false, int AUTO = 0>
+// Heads-up rows are 16 floats = 64 B = two 32-byte sectors: each thread writes its own row with two 256-bit stores
+// (sm_100: st.global.v8.f32 -> STG.E.256).  Every store fills a whole sector, so nothing is gained by staging the
+// rows through shared memory first -- and the staging (4 STS.128, two block barriers, 4 LDS.128, index arithmetic) was
+// 18% of the instructions of an issue-bound kernel (profiles/r2b_autoreset_step_raw.csv).  dst must be 32-byte aligned.
+__device__ __forceinline__ void store_row16(float* dst, const float (&r)[16]) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "f"(r[0]), "f"(r[1]), "f"(r[2]),
+               "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7]) : "memory");
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 8), "f"(r[8]), "f"(r[9]), "f"(r[10]),
+               "f"(r[11]), "f"(r[12]), "f"(r[13]), "f"(r[14]), "f"(r[15]) : "memory");
+}
+
+template <int MAXP, int MT, int MINB, bool POLICY = false, int AUTO = 0, bool DIRECT = false>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
                          float* __restrict__ obs_out, float* __restrict__ reward_out,
@@ -114,7 +125,11 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
     if (g < n)
       packed_step_one<MAXP, POLICY, AUTO>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base,
                                           starting_bbs, max_bbs, g, n, &pol);
-    stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
+    if (DIRECT && MT == 2) {
+      if (g < n) store_row16(obs_out + g * 16, reinterpret_cast<const float(&)[16]>(row));
+    } else {
+      stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
+    }
   }
 }
 
@@ -315,10 +330,20 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  // heads-up rows: direct 256-bit stores (PULSE_POKER_OBS_DIRECT=0 keeps the staged write-out, for A/B runs)
+  static const bool direct_env = !(getenv("PULSE_POKER_OBS_DIRECT") && atoi(getenv("PULSE_POKER_OBS_DIRECT")) == 0);
+  const bool direct = direct_env && (reinterpret_cast<uintptr_t>(obs_out) & 31u) == 0;
 #define PKP_STEP_A(MP, MT, MINB, AUTO, SMEM)                                                              \
-  poker_packed_step_kernel<MP, MT, MINB, false, AUTO><<<grid, kBlock, SMEM, stream>>>(                     \
-      *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
-      (long long)cfg->n_games, l2_ahead_for(MINB, MP))
+  do {                                                                                                    \
+    if ((MT) == 2 && direct)                                                                              \
+      poker_packed_step_kernel<MP, MT, MINB, false, AUTO, true><<<grid, kBlock, 0, stream>>>(              \
+          *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
+          (long long)cfg->n_games, l2_ahead_for(MINB, MP));                                               \
+    else                                                                                                  \
+      poker_packed_step_kernel<MP, MT, MINB, false, AUTO><<<grid, kBlock, SMEM, stream>>>(                 \
+          *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
+          (long long)cfg->n_games, l2_ahead_for(MINB, MP));                                               \
+  } while (0)
 #define PKP_STEP_B(MP, MT, MINB, SMEM)                       \
   do {                                                       \
     if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);       \
@@ -330,7 +355,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   static const int minb_env = getenv("PULSE_POKER_MINB") ? atoi(getenv("PULSE_POKER_MINB")) : 0;
 #define PKP_STEP(MP, MT, SMEM)                                    \
   do {                                                            \
-    const int minb = minb_env > 0 ? minb_env : ((MP) <= 2 ? 10 : 8); \
+    const int minb = minb_env > 0 ? minb_env : ((MP) <= 2 && !direct ? 10 : 8); \
     if (minb >= 12) PKP_STEP_B(MP, MT, 12, SMEM);                 \
     else if (minb >= 10) PKP_STEP_B(MP, MT, 10, SMEM);            \
     else PKP_STEP_B(MP, MT, 8, SMEM);                             \
@@ -392,10 +417,19 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   PokerParams pr = make_params(cfg);
   const int W = 13 + 3 * (pr.M - 1);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  static const bool direct_env = !(getenv("PULSE_POKER_OBS_DIRECT") && atoi(getenv("PULSE_POKER_OBS_DIRECT")) == 0);
+  const bool direct = direct_env && (reinterpret_cast<uintptr_t>(obs_out) & 31u) == 0;
 #define PKP_POL_A(MP, MT, MINB, AUTO, SMEM)                                                                \
-  poker_packed_step_kernel<MP, MT, MINB, true, AUTO><<<grid, kBlock, SMEM, stream>>>(                       \
-      *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,      \
-      cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB, MP), pol)
+  do {                                                                                                     \
+    if ((MT) == 2 && direct)                                                                               \
+      poker_packed_step_kernel<MP, MT, MINB, true, AUTO, true><<<grid, kBlock, 0, stream>>>(                \
+          *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,  \
+          cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB, MP), pol);                             \
+    else                                                                                                   \
+      poker_packed_step_kernel<MP, MT, MINB, true, AUTO><<<grid, kBlock, SMEM, stream>>>(                   \
+          *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,  \
+          cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB, MP), pol);                             \
+  } while (0)
 #define PKP_POL(MP, MT, MINB, SMEM)                          \
   do {                                                       \
     if (auto_reset) PKP_POL_A(MP, MT, MINB, 2, SMEM);        \

@@ -188,6 +188,76 @@ tfe_step_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions,
   pulse_counter_advance(counter_dev, dev_ctr);
 }
 
+// ---- K steps per launch ("rollout") -------------------------------------------------------------------
+// For open-loop action tapes (random-policy rollouts, BASELINE config 2) the K actions of a board are known up front:
+// the table is staged ONCE per K steps instead of once per step (~3 us of a 22 us step launch), and a board and its
+// score stay in registers between its steps (no 32 B of state traffic per step).  A thread plays all K steps of one
+// board, then takes its next board; actions are [K, N], outputs step-major [K, N, ...], so the stores of a warp are
+// contiguous for every k.  Chance comes from the tape at counter + k, exactly as K single-step launches would draw it.
+template <int SIDE, typename ActT>
+__global__ void __launch_bounds__(kStepBlock, 1)
+tfe_rollout_kernel(uint64_t* __restrict__ boards, const ActT* __restrict__ actions, int K, const uint4* __restrict__ table,
+                   uint64_t seed, uint64_t env_base, uint32_t counter, int auto_reset, int32_t* __restrict__ obs_out,
+                   int32_t* __restrict__ reward_out, uint8_t* __restrict__ done_out, uint8_t* __restrict__ done_state,
+                   int64_t* __restrict__ score, uint32_t n) {
+  extern __shared__ uint4 smem_raw[];
+  __shared__ uint64_t table_bar;
+  if (threadIdx.x == 0) pulse_mbar_init(&table_bar, 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pulse_mbar_expect_tx(&table_bar, kTableBytes);
+    constexpr int kChunk = 16384;
+#pragma unroll 1
+    for (int off = 0; off < kTableBytes; off += kChunk)
+      pulse_bulk_g2s(reinterpret_cast<uint8_t*>(smem_raw) + off, reinterpret_cast<const uint8_t*>(table) + off, kChunk,
+                     &table_bar);
+  }
+  uint64_t* wboards = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes) + (threadIdx.x & ~31);
+  uint2* lut = reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8);
+  uint32_t* score_lut = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(smem_raw) + kTableBytes + kStepBlock * 8 + kLutBytes);
+  if (threadIdx.x < 256) {
+    lut[tfe_lut_slot(threadIdx.x)] = make_uint2((1u << (threadIdx.x & 15u)) & ~1u, (1u << (threadIdx.x >> 4)) & ~1u);
+    score_lut[threadIdx.x] = tfe_code_score(threadIdx.x);
+  }
+  TfeTableRows rows;
+  rows.result = reinterpret_cast<const uint16_t*>(smem_raw);
+  rows.code = reinterpret_cast<const uint8_t*>(smem_raw) + 65536 * 2;
+  rows.score_of_code = score_lut;
+  __syncthreads();
+  pulse_mbar_wait(&table_bar, 0);
+  const uint32_t stride = gridDim.x * kStepBlock;
+  const uint32_t lane = threadIdx.x & 31;
+  const size_t W = (size_t)SIDE * SIDE;
+  for (uint32_t g = blockIdx.x * kStepBlock + threadIdx.x; g - lane < n; g += stride) {   // warp-uniform trip count
+    const bool valid = g < n;
+    uint64_t b = 0; int64_t total = 0; bool was_done = false; int a = 0;
+    if (valid) { b = boards[g]; total = score[g]; was_done = done_state[g] != 0; a = (int)actions[g]; }
+    for (int k = 0; k < K; ++k) {
+      int na = 0;
+      if (valid && k + 1 < K) na = (int)actions[(size_t)(k + 1) * n + g];                  // one step ahead
+      int32_t reward = 0; bool done = false;
+      if (valid) {
+        const bool reset_now = auto_reset && was_done;
+        const PulseU4 c = pulse_tape(seed, env_base + (uint64_t)g, reset_now ? PULSE_STREAM_TFE_RESET : PULSE_STREAM_TFE_SPAWN,
+                                     counter + (uint32_t)k);
+        b = tfe_step_fused<SIDE>(b, a, reset_now, c, total, reward, done, rows);
+        const size_t o = (size_t)k * n + g;
+        reward_out[o] = reward;
+        done_out[o] = done;
+        was_done = done;
+      }
+      if (obs_out) {
+        wboards[lane] = SIDE == 4 ? tfe_lut_swizzle_board(b) : b;
+        __syncwarp();
+        tfe_warp_write_obs<SIDE>(wboards, lut, g - lane, n, obs_out + (size_t)k * n * W);
+        __syncwarp();
+      }
+      a = na;
+    }
+    if (valid) { boards[g] = b; score[g] = total; done_state[g] = was_done; }
+  }
+}
+
 // builds the row-move table: result[row] (uint16) then code[row] (uint8), 196,608 bytes
 __global__ void tfe_build_table_kernel(uint16_t* __restrict__ result, uint8_t* __restrict__ code) {
   const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
@@ -273,6 +343,7 @@ std::atomic<uint4*> g_table[64];   // published with release / read with acquire
 
 template <int SIDE, typename ActT>
 cudaError_t allow_smem() {
+  cudaFuncSetAttribute(tfe_rollout_kernel<SIDE, ActT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
   return cudaFuncSetAttribute(tfe_step_kernel<SIDE, ActT>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStepSmem);
 }
 
@@ -376,6 +447,30 @@ int pulse_tfe_unpack(const uint64_t* boards, int32_t* values_out, int n_envs, in
   TFE_SIDE_DISPATCH(side, (tfe_unpack_kernel<SD><<<pulse_grid_for(n_envs, kBlock), kBlock, 0, stream>>>(
                               boards, values_out, (long long)n_envs)));
   return pulse_check_launch("pulse_tfe_unpack");
+}
+
+int pulse_tfe_rollout(uint64_t* boards, const void* actions, int action_bytes, int n_steps, uint64_t seed,
+                      uint64_t env_base, uint32_t counter, int auto_reset, int32_t* obs_out_or_null, int32_t* reward_out,
+                      uint8_t* done_out, uint8_t* done_inout, int64_t* score_inout, int n_envs, int side,
+                      cudaStream_t stream) {
+  PULSE_REQUIRE(n_envs >= 0 && n_steps >= 0, "n_envs / n_steps < 0");
+  PULSE_REQUIRE(side >= 2 && side <= 4, "side must be 2, 3 or 4");
+  PULSE_REQUIRE(action_bytes == 1 || action_bytes == 8, "actions must be uint8 or int64");
+  if (n_envs == 0 || n_steps == 0) return PULSE_OK;
+  PULSE_REQUIRE(boards && actions && reward_out && done_out && done_inout && score_inout, "null buffer");
+  PULSE_REQUIRE(!obs_out_or_null || (reinterpret_cast<uintptr_t>(obs_out_or_null) & 15u) == 0, "obs must be 16-byte aligned");
+  const uint4* table = nullptr;
+  int rc = tfe_ensure_table(stream, &table);
+  if (rc) return rc;
+  const long long need = ((long long)n_envs + kStepBlock - 1) / kStepBlock;
+  const int grid = (int)(need < pulse_sm_count() ? need : pulse_sm_count());
+#define TFE_ROLL(ACT)                                                                                                  \
+  TFE_SIDE_DISPATCH(side, (tfe_rollout_kernel<SD, ACT><<<grid, kStepBlock, kStepSmem, stream>>>(                        \
+                              boards, (const ACT*)actions, n_steps, table, seed, env_base, counter, auto_reset,         \
+                              obs_out_or_null, reward_out, done_out, done_inout, score_inout, (uint32_t)n_envs)))
+  if (action_bytes == 1) TFE_ROLL(uint8_t); else TFE_ROLL(int64_t);
+#undef TFE_ROLL
+  return pulse_check_launch("pulse_tfe_rollout");
 }
 
 int pulse_tfe_domain_check(const uint64_t* boards, int* counts2, int n_envs, cudaStream_t stream) {

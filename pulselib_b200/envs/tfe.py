@@ -102,6 +102,36 @@ class TFEBatched(gym.Env):
             self._t += 1
         return self.get_obs(), self.rewards, self.done, False, self.get_info()
 
+    def rollout(self, actions, return_obs=None):
+        """K steps in ONE launch (pulse_tfe_rollout) for an open-loop action tape: actions uint8 / int64 [K, N] ->
+        (obs int32 [K, N, side, side] or None, reward int32 [K, N], done bool [K, N]) -- exactly what K step() calls
+        would return one after another (chance from the tape at the same counters)."""
+        if not self._started:
+            raise _lib.PulseError("TFEBatched.rollout called before reset")
+        if self._ctr is not None:
+            raise _lib.PulseError("rollout keeps the tape counter on the host: construct the env without device_counter")
+        actions = torch.as_tensor(actions, device=self.device)
+        if actions.dim() != 2 or actions.shape[1] != self.n_envs:
+            raise ValueError(f"actions must have shape (K, {self.n_envs}), got {tuple(actions.shape)}")
+        if actions.dtype not in (torch.uint8, torch.int64) or not actions.is_contiguous():
+            actions = actions.to(torch.int64).contiguous()
+        K, n, dev = int(actions.shape[0]), self.n_envs, self.device
+        want_obs = self.return_obs if return_obs is None else bool(return_obs)
+        obs = torch.empty((K, n, self.side, self.side), dtype=torch.int32, device=dev) if want_obs else None
+        rew = torch.empty((K, n), dtype=torch.int32, device=dev)
+        done = torch.empty((K, n), dtype=torch.bool, device=dev)
+        with _lib.device_guard(dev):
+            _lib.check(self._lib.pulse_tfe_rollout(
+                ptr(self.boards), ptr(actions), c_i(actions.element_size()), c_i(K), c_u64(self.seed_value),
+                c_u64(self.env_base), c_u32(self._t), c_i(self.auto_reset), ptr(obs), ptr(rew), ptr(done), ptr(self.done),
+                ptr(self.total_score), c_i(n), c_i(self.side), _lib.cuda_stream(dev)), "pulse_tfe_rollout")
+        self._t += K
+        if K:
+            self.rewards = rew[-1]
+            if want_obs and self.obs is not None:
+                self.obs = obs[-1]
+        return obs, rew, done
+
     def get_obs(self):
         return self.obs if self.return_obs else self.boards
 

@@ -3,7 +3,7 @@
 `PokerHostEnv` keeps the reference's step contract -- actions in, float32 observations [N, 13 + 3 (M - 1)], float32
 rewards and bool dones out (/root/reference/environments/Poker/PokerGPU.py:527-633) -- with every array in HOST
 memory.  It binds `pulse_poker_host_*` (include/pulse_envs.h, csrc/host_env.cu): 1 B per table goes to the GPU, one
-packed 24 B record per LIVE table comes back, and a pool of native threads expands the records into `self.obs`,
+packed 28 B record per LIVE table comes back, and a pool of native threads expands the records into `self.obs`,
 `self.rewards`, `self.dones` -- the same three arrays on every call, as the reference reuses `self.obs`.
 bench.py's `e2e` number is this class."""
 from __future__ import annotations
@@ -67,6 +67,12 @@ class PokerHostEnv:
         return dict(row_bytes=v[0].value, obs_width=v[1].value, chunks=v[2].value, threads=v[3].value,
                     last_h2d_bytes=v[4].value, last_d2h_bytes=v[5].value)
 
+    def timing(self, reset=False) -> dict:
+        out = (C.c_double * 6)()
+        _lib.check(self._lib.pulse_poker_host_timing(self._h, out, C.c_int(1 if reset else 0)), "pulse_poker_host_timing")
+        keys = ("calls", "stage_s", "submit_s", "expand_wall_s", "worker_wait_s", "worker_expand_s")
+        return dict(zip(keys, (float(v) for v in out)))
+
     def close(self):
         if getattr(self, "_h", None):
             self._lib.pulse_poker_host_destroy(self._h)
@@ -90,12 +96,19 @@ def _aligned(shape, dtype, align=64):
     return raw[off:off + n].view(dtype).reshape(shape)
 
 
-def expand_rows(rows: np.ndarray, active_players: int, max_players: int):
-    """Packed step records (uint64 [n, words]) -> (obs float32 [n, W], reward float32 [n], done uint8 [n]); host only."""
+def expand_rows(rows: np.ndarray, max_players: int, vectorised: bool = True):
+    """Packed step records (uint32 [n, words]) -> (obs float32 [n, W], reward float32 [n], done uint8 [n]); host only.
+    vectorised: through the host env's own expander (AVX2 when available), else the portable definition."""
     lib = _lib.load()
-    rows = np.ascontiguousarray(rows, dtype=np.uint64)
+    rows = np.ascontiguousarray(rows, dtype=np.uint32)
     n, W = rows.shape[0], 13 + 3 * (max_players - 1)
-    obs, rew, done = np.zeros((n, W), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8)
-    _lib.check(lib.pulse_poker_wire_expand_host(_p(rows), C.c_longlong(n), C.c_int(active_players), C.c_int(max_players),
+    obs, rew, done = _aligned((n, W), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint8)
+    _lib.check(lib.pulse_poker_wire_expand_host(_p(rows), C.c_longlong(n), C.c_int(max_players), C.c_int(1 if vectorised else 0),
                                                 _p(obs), _p(rew), _p(done)), "pulse_poker_wire_expand_host")
     return obs, rew, done
+
+
+def expand_isa() -> str:
+    lib = _lib.load()
+    lib.pulse_poker_host_expand_isa.restype = C.c_char_p
+    return lib.pulse_poker_host_expand_isa().decode()

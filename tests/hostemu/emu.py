@@ -162,8 +162,8 @@ class EmuPokerPacked(EmuPoker):
 
     def wire_rows(self):
         """the compact step record (csrc/poker_wire.cuh) of every table, reward = self.rewards"""
-        words = (18 + 4 * (self.max_players - 1) + 7) // 8
-        rows = np.zeros((self.n_games, words), np.uint64)
+        words = 3 + (13 + 3 * (self.max_players - 1) - 8 + 1) // 2
+        rows = np.zeros((self.n_games, words), np.uint32)
         s = self._packed()
         rc = lib().emu_poker_wire_rows(C.byref(s), C.byref(self.cfg), p(self.rewards), p(rows))
         assert rc == 0

@@ -96,16 +96,16 @@ int emu_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerCon
   return 0;
 }
 // the compact step record (poker_wire.cuh) of every table of a packed batch, reward taken from `rewards`
-int emu_poker_wire_rows(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const float* rewards, uint64_t* rows) {
+int emu_poker_wire_rows(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const float* rewards, uint32_t* rows) {
   PokerParams pr = mk(cfg);
   const long long n = cfg->n_games;
 #define EMU_WIRE(MPV, MTV)                                                         \
   for (long long g = 0; g < n; ++g) {                                              \
     PokerTable<MPV> t; uint32_t fb;                                                \
     packed_load(t, fb, *st, g, n, pr.AP);                                          \
-    uint64_t w[(18 + 4 * (MTV - 1) + 7) / 8];                                      \
+    uint32_t w[pkw_row_words(MTV)];                                                \
     pkw_pack_row<MPV, MTV>(t, pr, rewards[g], w);                                  \
-    for (int i = 0; i < (18 + 4 * (MTV - 1) + 7) / 8; ++i) rows[g * ((18 + 4 * (MTV - 1) + 7) / 8) + i] = w[i]; \
+    for (int i = 0; i < pkw_row_words(MTV); ++i) rows[g * pkw_row_words(MTV) + i] = w[i]; \
   }
   if (pr.P <= 2 && pr.M == 2) { EMU_WIRE(2, 2) }
   else if (pr.P <= 4 && pr.M == 4) { EMU_WIRE(4, 4) }
@@ -140,6 +140,19 @@ int emu_blackjack_reset(uint32_t* st, uint8_t* deck, const uint8_t* injected, ui
 int emu_blackjack_step(uint32_t* st, const uint8_t* deck, const int64_t* actions, int32_t* obs, int32_t* rewards,
                        uint8_t* terminated, int n) {
   for (long long g = 0; g < n; ++g) bj_step_one(st, deck, actions, obs, rewards, terminated, g, n);
+  return 0;
+}
+int emu_blackjack_rollout(uint32_t* st, uint8_t* deck, const int64_t* actions, int K, int32_t* obs, int32_t* rewards,
+                          uint8_t* terminated, int n) {
+  for (long long g = 0; g < n; ++g) {
+    BjState s = bj_unpack_word(st[g]);
+    for (int k = 0; k < K; ++k) {
+      const long long o = (long long)k * n + g;
+      rewards[o] = bj_step_state(s, actions[o], deck, g, n);
+      obs[3 * o] = s.psum; obs[3 * o + 1] = s.ace; obs[3 * o + 2] = s.upcard; terminated[o] = s.term;
+    }
+    st[g] = bj_pack(s);
+  }
   return 0;
 }
 int emu_blackjack_unpack(const uint32_t* st, const uint8_t* deck, const BjCompat* C, int n) {

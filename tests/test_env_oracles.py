@@ -117,3 +117,31 @@ def test_tetris_known_placements():
     assert rew[0] == 1 and orc.rows[0, 0] == 0b1100000000 and orc.rows[0, 1] == 0 and orc.lines[0] == 1
     orc.step(np.array([19]), np.array([0], np.uint8))        # I vertical (rot 1), x=9: rests on the O remnant
     assert [int(r) for r in orc.rows[0, :6]] == [0x300, 0x200, 0x200, 0x200, 0x200, 0]
+
+
+def test_tetris_oracle_agrees_with_independent_python_spec():
+    """Tetris has no reference behaviour (parity UNPINNED): the C oracle and a second implementation written from
+    DESIGN.md section 6 by a different route (tests/tetris_spec_py.py) must agree step for step."""
+    from tests.tetris_spec_py import TetrisSpec
+
+    n, steps = 96, 260
+    rng = np.random.default_rng(44)
+    first = rng.integers(0, 7, n).astype(np.uint8)
+    orc = pyoracle.OracleTetris(n)
+    orc.reset(first)
+    specs = [TetrisSpec(p) for p in first]
+    ended = 0
+    for t in range(steps):
+        a = rng.integers(-2, 43, n)                 # out-of-range actions are clamped
+        if t % 3 == 0:
+            a[: n // 4] = rng.integers(0, 10, n // 4)   # some envs stack one column: lock-outs and line clears both happen
+        nx, rp = rng.integers(0, 7, n).astype(np.uint8), rng.integers(0, 7, n).astype(np.uint8)
+        auto = t % 2 == 0 or t > 100
+        rows, rew, done = orc.step(a, nx, auto_reset=auto, reset_piece=rp)
+        for i, s in enumerate(specs):
+            r = s.step(a[i], nx[i], rp[i], auto)
+            assert r == rew[i], f"step {t} env {i}: reward {rew[i]} vs spec {r}"
+            assert s.done == bool(done[i]) and s.lines == orc.lines[i] and s.piece == orc.piece[i], f"step {t} env {i}"
+            assert s.rows_as_bits() == [int(v) for v in rows[i]], f"step {t} env {i}: board"
+        ended += int(done.sum())
+    assert ended > 0 and int(orc.lines.max()) > 0

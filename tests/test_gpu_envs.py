@@ -319,3 +319,65 @@ def test_tfe_domain_check_flags_32768_tiles(cuda_device):
     assert env.domain_check(raise_on_overflow=False) == (2, 1)
     with pytest.raises(_lib.PulseError):
         env.domain_check()
+
+
+def test_blackjack_rollout_equals_k_steps(cuda_device):
+    """pulse_blackjack_rollout: K steps in one launch == K step() calls, against the oracle too"""
+    import torch
+    from pulselib_b200.envs.blackjack import BlackJack
+
+    n, K = 4096, 9
+    a = BlackJack(device=cuda_device, batch_size=n, seed=3, env_base=10)
+    b = BlackJack(device=cuda_device, batch_size=n, seed=3, env_base=10)
+    orc = pyoracle.OracleBlackjack(n)
+    rng = np.random.default_rng(8)
+    for episode in range(3):
+        acts = rng.integers(0, 3, (K, n)).astype(np.int64)      # 2 = neither hit nor stand: a no-op
+        t_acts = torch.from_numpy(acts).to(cuda_device)
+        if episode == 1:
+            t_acts = t_acts.to(torch.uint8)                      # byte-wide actions
+        obs_k, rew_k, term_k, first = a.rollout(t_acts, reset_first=True)
+        o0, _ = b.reset()
+        orc.tape_decks(3, 10, episode)
+        np.testing.assert_array_equal(first.cpu().numpy(), orc.reset(None))
+        np.testing.assert_array_equal(first.cpu().numpy(), o0.cpu().numpy())
+        for k in range(K):
+            o, r, t, _, _ = b.step(torch.from_numpy(acts[k]).to(cuda_device))
+            o2, r2, t2 = orc.step(acts[k])
+            np.testing.assert_array_equal(obs_k[k].cpu().numpy(), o.cpu().numpy(), err_msg=f"ep {episode} step {k} obs")
+            np.testing.assert_array_equal(rew_k[k].cpu().numpy(), r.cpu().numpy())
+            np.testing.assert_array_equal(term_k[k].cpu().numpy(), t.cpu().numpy())
+            np.testing.assert_array_equal(obs_k[k].cpu().numpy(), o2)
+            np.testing.assert_array_equal(rew_k[k].cpu().numpy(), r2)
+        # a second rollout without reset carries on from the state the first one left
+        more = rng.integers(0, 2, (2, n)).astype(np.int64)
+        ok, rk, tk = a.rollout(torch.from_numpy(more).to(cuda_device))
+        for k in range(2):
+            o, r, t, _, _ = b.step(torch.from_numpy(more[k]).to(cuda_device))
+            np.testing.assert_array_equal(ok[k].cpu().numpy(), o.cpu().numpy())
+            np.testing.assert_array_equal(tk[k].cpu().numpy(), t.cpu().numpy())
+
+
+@pytest.mark.parametrize("side,n", [(4, 4096), (4, 1 << 18), (3, 1000)])
+def test_tfe_rollout_equals_k_steps(side, n, cuda_device):
+    """pulse_tfe_rollout: K steps in one launch == K step() calls (same tape counters), auto-reset included"""
+    import torch
+    from pulselib_b200.envs.tfe import TFEBatched
+
+    K = 24
+    a = TFEBatched(cuda_device, n, side=side, seed=7, env_base=5, auto_reset=True)
+    b = TFEBatched(cuda_device, n, side=side, seed=7, env_base=5, auto_reset=True)
+    a.reset(); b.reset()
+    rng = np.random.default_rng(side)
+    for rnd in range(4 if side == 3 else 2):              # 3x3 boards finish within tens of moves: resets happen
+        acts = torch.from_numpy(rng.integers(0, 4, (K, n)).astype(np.uint8 if rnd % 2 else np.int64)).to(cuda_device)
+        obs_k, rew_k, done_k = a.rollout(acts)
+        for k in range(K):
+            o, r, d, _, info = b.step(acts[k])
+            np.testing.assert_array_equal(obs_k[k].cpu().numpy(), o.cpu().numpy(), err_msg=f"round {rnd} step {k} boards")
+            np.testing.assert_array_equal(rew_k[k].cpu().numpy(), r.cpu().numpy())
+            np.testing.assert_array_equal(done_k[k].cpu().numpy(), d.cpu().numpy())
+        np.testing.assert_array_equal(a.total_score.cpu().numpy(), b.total_score.cpu().numpy())
+        np.testing.assert_array_equal(a.boards.cpu().numpy(), b.boards.cpu().numpy())
+    if side == 3:
+        assert int(done_k.sum()) > 0

@@ -50,7 +50,7 @@ def test_host_env_matches_float32_engine(P, M, ap, N, chunks, threads, cuda_devi
             np.testing.assert_array_equal(r1.view(np.uint32), r2.cpu().numpy().view(np.uint32), err_msg=tag + " reward bits")
             np.testing.assert_array_equal(d1, d2.cpu().numpy(), err_msg=tag + " done")
         inf = henv.info()
-        assert inf["row_bytes"] == 8 * ((18 + 4 * (M - 1) + 7) // 8)
+        assert inf["row_bytes"] == 4 * (3 + (13 + 3 * (M - 1) - 8 + 1) // 2)
         assert inf["last_d2h_bytes"] <= N * inf["row_bytes"] and inf["last_h2d_bytes"] >= N
     henv.close()
 
@@ -80,6 +80,6 @@ def test_host_env_refuses_unrepresentable_configs(cuda_device):
     from pulselib_b200.host_env import PokerHostEnv
 
     with pytest.raises(_lib.PulseError):
-        PokerHostEnv(cuda_device, n_players=10, max_players=10, n_games=64, max_bbs=5000)   # 50,000 chips do not fit 14 bits
+        PokerHostEnv(cuda_device, n_players=10, max_players=10, n_games=64, max_bbs=7000)   # 70,000 chips do not fit 16 bits
     with pytest.raises(_lib.PulseError):
         PokerHostEnv(cuda_device, n_players=3, max_players=10, n_games=64)                  # shape outside the specialised set

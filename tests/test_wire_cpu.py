@@ -20,8 +20,16 @@ def test_wire_rows_round_trip(P, M, ap, hr_table):
         env.reset(None, active_players=ap, rotation=hand % P, hand=hand)
         env.rewards[...] = 0
         for t in range(40):
-            obs, rew, done = host_env.expand_rows(env.wire_rows(), ap, M)
-            np.testing.assert_array_equal(obs, env.obs, err_msg=f"hand {hand} step {t} obs")
-            np.testing.assert_array_equal(rew.view(np.uint32), env.rewards.view(np.uint32))
-            np.testing.assert_array_equal(done, env.is_done)
+            rows = env.wire_rows()
+            for vec in (True, False):      # the host env's vectorised expander and the portable definition
+                obs, rew, done = host_env.expand_rows(rows, M, vectorised=vec)
+                np.testing.assert_array_equal(obs, env.obs, err_msg=f"hand {hand} step {t} obs (vectorised={vec})")
+                np.testing.assert_array_equal(rew.view(np.uint32), env.rewards.view(np.uint32))
+                np.testing.assert_array_equal(done, env.is_done)
             env.step(rng.integers(0, 13, N))
+
+
+def test_expander_isa_is_reported():
+    from pulselib_b200 import host_env
+
+    assert host_env.expand_isa() in ("avx2", "portable")
