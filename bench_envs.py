@@ -22,7 +22,7 @@ SPECS = {
     # board stays in registers between its steps -- action 1 + obs 64 + reward 4 + done 1 = 70 B per board-step plus
     # 32 B of state per 16 steps; reported against the same fixed 106 B
     "tfe_4x4_rollout": dict(n=1 << 20, algo_bytes=106, moved_bytes=72, replicas=4, kernel="tfe_rollout_kernel<4, uint8_t>",
-                            graph=0, actions=16,
+                            graph=0, actions=16, steps_per_call=16,
                             desc="2048 4x4, {n} boards/GPU, uniform random moves (uint8) supplied as a [16, N] tape, 16 steps per "
                                  "launch, spawns from the chance tape, auto-reset on game over, int32 4x4 observations of "
                                  "every step written ([16, N, 4, 4])"),
@@ -57,9 +57,9 @@ SPECS = {
                                 desc="PokerGPU heads-up, {n} tables/GPU, seat 0 = learner (uniform random actions supplied), "
                                      "seat 1 = TightAggressive rule inside the step kernel, per-table auto-reset, hand "
                                      "statistics and the learner's transitions (ring of 8M) gathered on the device every step"),
-    "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_rollout_kernel<long>", graph=0, actions=8,
+    "blackjack": dict(n=4096, algo_bytes=50, kernel="blackjack_rollout_kernel<unsigned char>", graph=0, actions=128, steps_per_call=128,
                       desc="Blackjack, {n} envs/GPU (the reference's CPU-sized config), uniform hit/stand, hands of 8 steps: "
-                           "ONE launch deals the hand and plays its 8 steps (pulse_blackjack_rollout, outputs [8, N, ...]); "
+                           "ONE launch deals and plays 16 hands (pulse_blackjack_rollout, 128 steps, outputs [128, N, ...]); "
                            "working set is L2-resident by construction"),
     # the same config one launch per step (the reference's call pattern, blackjack.py:179-186)
     "blackjack_per_step": dict(n=4096, algo_bytes=50, kernel="blackjack_step_kernel", graph=0, actions=8,
@@ -92,13 +92,9 @@ def _make(name, dev, n, rank, e2e=False):
         acts = torch.randint(0, 4, (L, n), dtype=torch.uint8, device=dev, generator=gen)
         env._bench_k, env._bench_out = 0, None
 
-        def step(e, a):
-            k = e._bench_k % L
-            if k == 0:                                   # one launch plays the next L steps of every board
-                e._bench_out = e.rollout(acts)
-            e._bench_k += 1
-            o, r, d = e._bench_out
-            return o[k], r[k], d[k]
+        def step(e, a):                                  # one launch plays the next L steps of every board
+            o, r, d = e.rollout(acts)
+            return o[-1], r[-1], d[-1]
     elif name == "tetris":
         from pulselib_b200.envs.tetris import TetrisBatched
 
@@ -167,16 +163,12 @@ def _make(name, dev, n, rank, e2e=False):
         from pulselib_b200.envs.blackjack import BlackJack
 
         env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
-        acts = torch.randint(0, 2, (L, n), dtype=torch.int64, device=dev, generator=gen)
+        acts = torch.randint(0, 2, (L, n), dtype=torch.uint8, device=dev, generator=gen)
         env._bench_k, env._bench_out = 0, None
 
-        def step(e, a):
-            k = e._bench_k % 8
-            if k == 0:                                   # one launch: deal + the hand's 8 steps
-                e._bench_out = e.rollout(acts, reset_first=True)
-            e._bench_k += 1
-            o, r, t = e._bench_out[:3]
-            return o[k], r[k], t[k]
+        def step(e, a):                                  # one launch: 16 x (deal + the hand's 8 steps)
+            o, r, t = e.rollout(acts, reset_first=True, n_hands=L // 8)[:3]
+            return o[-1], r[-1], t[-1]
     elif name == "blackjack_per_step":
         from pulselib_b200.envs.blackjack import BlackJack
 
@@ -220,8 +212,10 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
         chunk -= chunk % replicas or 0
         chunk = max(chunk, replicas)
 
+    spc = int(spec.get("steps_per_call", 1))   # rollout workloads: one call (= one launch) plays this many steps
+
     def eager(k, start, pairs=None):
-        for i in range(k):
+        for i in range(0, k, spc):
             j = start + i
             if pairs is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -276,8 +270,8 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
     t1.record(stream)
     barrier()
     total_ms = t0.elapsed_time(t1)
-    kernel_ms = (sum(a.elapsed_time(b) for a, b in pairs) / len(pairs)) if pairs else total_ms / steps
-    launches = steps // 16 + 1 if name == "tfe_4x4_rollout" else steps // 8 + 1 if name == "blackjack" else steps + (steps // 8 + 1 if name == "blackjack_per_step" else 0)
+    kernel_ms = (sum(a.elapsed_time(b) for a, b in pairs) / len(pairs) / spc) if pairs else total_ms / steps
+    launches = steps // 16 + 1 if name == "tfe_4x4_rollout" else steps // 128 + 1 if name == "blackjack" else steps + (steps // 8 + 1 if name == "blackjack_per_step" else 0)
     return dict(n=n, total_ms=total_ms, kernel_ms=kernel_ms, launches=launches, replicas=replicas, live_fraction=live_fraction,
                 mode=f"cuda graph of {chunk} steps" if graph is not None else "eager launches",
                 kernel_time="graph time / steps (includes inter-kernel gaps)" if graph is not None
@@ -294,6 +288,8 @@ def e2e(name, dev, rank, steps, n=None, chunks=4):
     n = int(n or spec["n"])
     if name == "blackjack":
         return _e2e_blackjack_rollout(dev, rank, steps, n)
+    if name == "tfe_4x4_rollout":   # end to end the link carries the same 69 B per board-step either way: measured per step
+        name, spec = "tfe_4x4", SPECS["tfe_4x4"]
     chunks = chunks if n >= 1 << 16 else 1
     nc = n // chunks
     made = [_make(name, dev, nc, rank * 64 + 32 + c, e2e=True) for c in range(chunks)]
@@ -335,17 +331,18 @@ def _e2e_blackjack_rollout(dev, rank, steps, n):
     from pulselib_b200.envs.blackjack import BlackJack
 
     env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
-    hands = max(1, steps // 8)
-    h_act = torch.randint(0, 2, (8, n), dtype=torch.uint8).pin_memory()
-    d_act = torch.empty((8, n), dtype=torch.uint8, device=dev)
-    h_obs = torch.empty((8, n, 3), dtype=torch.int32).pin_memory()
-    h_rew = torch.empty((8, n), dtype=torch.int32).pin_memory()
-    h_term = torch.empty((8, n), dtype=torch.bool).pin_memory()
+    KT = 128                                         # 16 hands of 8 steps per launch
+    hands = max(1, steps // KT)
+    h_act = torch.randint(0, 2, (KT, n), dtype=torch.uint8).pin_memory()
+    d_act = torch.empty((KT, n), dtype=torch.uint8, device=dev)
+    h_obs = torch.empty((KT, n, 3), dtype=torch.int32).pin_memory()
+    h_rew = torch.empty((KT, n), dtype=torch.int32).pin_memory()
+    h_term = torch.empty((KT, n), dtype=torch.bool).pin_memory()
 
     def run(k):
         for _ in range(k):
             d_act.copy_(h_act, non_blocking=True)
-            o, r, t, _ = env.rollout(d_act, reset_first=True)
+            o, r, t, _ = env.rollout(d_act, reset_first=True, n_hands=KT // 8)
             h_obs.copy_(o, non_blocking=True); h_rew.copy_(r, non_blocking=True); h_term.copy_(t, non_blocking=True)
         torch.cuda.synchronize(dev)
 
@@ -353,7 +350,7 @@ def _e2e_blackjack_rollout(dev, rank, steps, n):
     w0 = time.perf_counter()
     run(hands)
     ms = (time.perf_counter() - w0) * 1e3
-    return dict(value=n * 8 * hands / (ms * 1e-3), ms=ms, steps=8 * hands, chunks=1, h2d_bytes_per_step=n,
+    return dict(value=n * KT * hands / (ms * 1e-3), ms=ms, steps=KT * hands, chunks=1, h2d_bytes_per_step=n,
                 d2h_bytes_per_step=n * (12 + 4 + 1))
 
 

@@ -134,8 +134,10 @@ int pulse_blackjack_step(uint32_t* st, const uint8_t* deck, const int64_t* actio
  * (action_bytes 1 / 8); outputs step-major: obs_out int32 [K, N, 3], rewards_out int32 [K, N], terminated_out uint8
  * [K, N] -- exactly what K calls of pulse_blackjack_step would have written.  reset_first != 0: deal a fresh hand from
  * the tape (seed, env_base + i, episode) before the first step (= pulse_blackjack_reset; its observation goes to
- * reset_obs_out_or_null int32 [N, 3]). */
-int pulse_blackjack_rollout(uint32_t* st, uint8_t* deck, const void* actions, int action_bytes, int n_steps,
+ * reset_obs_out_or_null int32 [N, 3]).  n_hands > 1: that many hands of n_steps steps in the one launch, each after the
+ * first (and the first too when reset_first) starting with a fresh deal from consecutive tape episodes; actions and
+ * outputs are then [n_hands * n_steps, N, ...] and reset_obs_out [n_hands, N, 3]. */
+int pulse_blackjack_rollout(uint32_t* st, uint8_t* deck, const void* actions, int action_bytes, int n_steps, int n_hands,
                             int reset_first, uint64_t seed, uint64_t env_base, uint32_t episode,
                             int32_t* reset_obs_out_or_null, int32_t* obs_out, int32_t* rewards_out,
                             uint8_t* terminated_out, int n_envs, pulse_stream_t stream);
@@ -285,6 +287,18 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
                                    int32_t* seat_idx_out_or_null, float* obs_out, float* reward_out, uint8_t* done_out, int auto_reset,
                                    uint64_t seed, uint64_t env_base, pulse_stream_t stream);
 
+/* K steps per launch with every seat played on the device (SURVEY.md 8(b) "pulse_poker_rollout"): for the small batches
+ * the reference benchmarks (N = 256, /root/reference/benchmarking/Poker) a step is launch-bound, so the loop over steps
+ * runs inside one kernel.  seat_kinds: HOST array, one PULSE_AGENT_RANDOM .. PULSE_AGENT_SMALL_BALL per seat (no
+ * EXTERNAL seats); step k draws its chance pair from the tape at counter + k, exactly as n_steps calls of
+ * pulse_poker_packed_step_policy would.  Outputs step-major: reward_out float32 [K, N], done_out uint8 [K, N],
+ * actions_out_or_null int64 [K, N] (the actions played); obs_final_or_null float32 [N, 13 + 3 (M - 1)] = the
+ * observation after the last step. */
+int pulse_poker_packed_rollout(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const uint8_t* seat_kinds,
+                               uint32_t counter, int n_steps, int auto_reset, uint64_t seed, uint64_t env_base,
+                               float* obs_final_or_null, float* reward_out, uint8_t* done_out, int64_t* actions_out_or_null,
+                               pulse_stream_t stream);
+
 /* Enumerated hand strength (no reference behaviour -- the reference's notes call its table-walk
  * proxy a known weakness, rl/depth_notes.txt:302-333).  strength_out float32 [N, active_players]: the expectation over
  * the board cards still to come of the river strength clamp((v7 - 4109) / 32765, 0, 1) (PokerGPU.py:477-481) from each
@@ -346,6 +360,12 @@ int pulse_poker_host_timing(PulsePokerHostEnv* env, double* out6, int reset);
  * pulse_poker_host_expand_isa), else the portable definition -- the two must agree bit for bit. */
 int pulse_poker_wire_expand_host(const uint32_t* rows, long long n_rows, int max_players, int vectorised,
                                  float* obs_out, float* reward_out, uint8_t* done_out);
+/* pure host function: one step of the host env's own bookkeeping without a GPU.  rows: the records of the tables whose
+ * bit is set in live_inout, compacted in table order (of every table when fresh != 0); obs / reward / done: the caller's
+ * persistent arrays; live_inout / prev_live_inout: ceil(n_tables / 32) words, updated as the env updates them. */
+int pulse_poker_wire_expand_step_host(const uint32_t* rows, uint32_t* live_inout, uint32_t* prev_live_inout,
+                                      long long n_tables, int max_players, int fresh, float* obs, float* reward,
+                                      uint8_t* done);
 const char* pulse_poker_host_expand_isa(void);
 
 /* ---- run statistics (the vector that is all-reduced across GPUs) -------------------

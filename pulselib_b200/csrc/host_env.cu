@@ -39,7 +39,9 @@ template <int MAXP, int MT, int MINB>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_host_step_kernel(PulsePokerPacked S, PokerParams pr, const uint8_t* __restrict__ actions,
                        const uint32_t* __restrict__ warp_off, uint32_t* __restrict__ wire, int starting_bbs,
-                       int max_bbs, long long first, long long last, long long n) {
+                       int max_bbs, long long first, long long last, long long n, uint32_t* __restrict__ epoch_word,
+                       uint32_t epoch) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) *epoch_word = epoch;   // copied to the host behind the records: "chunk landed"
   // one chunk of the batch: tables first .. last-1 (first a multiple of 1024); the seat-major arrays keep the whole
   // batch's stride n; warp_off and wire are the chunk's own
   constexpr int R = pkw_row_words(MT);
@@ -70,7 +72,9 @@ poker_host_step_kernel(PulsePokerPacked S, PokerParams pr, const uint8_t* __rest
 // After a whole-batch deal: every table's record, uncompacted (slot = table), reward 0.
 template <int MAXP, int MT>
 __global__ void __launch_bounds__(kBlock)
-poker_host_rows_kernel(PulsePokerPacked S, PokerParams pr, uint32_t* __restrict__ wire, long long n) {
+poker_host_rows_kernel(PulsePokerPacked S, PokerParams pr, uint32_t* __restrict__ wire, long long n,
+                       uint32_t* __restrict__ epoch_words, int n_words, uint32_t epoch) {
+  if (blockIdx.x == 0 && (int)threadIdx.x < n_words) epoch_words[threadIdx.x] = epoch;
   constexpr int R = pkw_row_words(MT);
   pr.M = MT;
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
@@ -149,7 +153,12 @@ struct PulsePokerHostEnv {
   std::vector<long long> chunk_rows;       // live tables per chunk at the start of the next step
   std::vector<cudaStream_t> streams;
   std::vector<cudaEvent_t> events;
-  std::atomic<int>* ready = nullptr;       // per chunk: its records have landed in h_wire (set by a stream host callback)
+  // "chunk c has landed": the kernel writes the call's epoch into d_flag[c], a 4-byte copy queued behind the chunk's
+  // records brings it to h_flag[c] (pinned), the workers poll that word.  No driver thread is involved (stream host
+  // callbacks cost 20-50 us each and are run one at a time by a thread the spinning workers can starve).
+  uint32_t* d_flag = nullptr; volatile uint32_t* h_flag = nullptr;
+  uint32_t epoch = 0;
+  std::vector<uint32_t> prev_live;         // the live mask as it was when the previous call began (reward zeroing)
   std::atomic<int>* remaining = nullptr;   // per chunk: workers still expanding it (the last one rebuilds its offsets)
   Pool* pool = nullptr;
   long long last_h2d = 0, last_d2h = 0;
@@ -159,7 +168,6 @@ struct PulsePokerHostEnv {
   long long calls = 0;
   ~PulsePokerHostEnv() {
     delete pool;
-    delete[] ready;
     delete[] remaining;
     cudaSetDevice(device);
     for (auto s : streams) cudaStreamDestroy(s);
@@ -222,44 +230,52 @@ void rebuild_offsets(PulsePokerHostEnv* e, int c) {
   e->chunk_rows[c] = acc;
 }
 
-void CUDART_CB mark_ready(void* p) { static_cast<std::atomic<int>*>(p)->store(1, std::memory_order_release); }
-
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 template <int MP, int MT>
 void launch_step_t(PulsePokerHostEnv* e, const PokerParams& pr, long long first, long long cnt, const uint32_t* d_off,
-                   uint32_t* d_rows, cudaStream_t s) {
+                   uint32_t* d_rows, uint32_t* d_flag, cudaStream_t s) {
   constexpr int MINB = MP <= 2 ? 8 : MP <= 6 ? 6 : 4;   // resident CTAs per SM, as for the float32-row step
   poker_host_step_kernel<MP, MT, MINB><<<pulse_grid_for(cnt, kBlock), kBlock, 0, s>>>(
-      e->st, pr, e->d_act, d_off, d_rows, e->cfg.starting_bbs, e->cfg.max_bbs, first, first + cnt, e->N);
+      e->st, pr, e->d_act, d_off, d_rows, e->cfg.starting_bbs, e->cfg.max_bbs, first, first + cnt, e->N, d_flag, e->epoch);
 }
 
 int launch_step(PulsePokerHostEnv* e, const PokerParams& pr, long long first, long long cnt, const uint32_t* d_off,
-                uint32_t* d_rows, cudaStream_t s) {
-  HE_DISPATCH(pr.P, pr.M, (launch_step_t<MP, MT>(e, pr, first, cnt, d_off, d_rows, s)));
+                uint32_t* d_rows, uint32_t* d_flag, cudaStream_t s) {
+  HE_DISPATCH(pr.P, pr.M, (launch_step_t<MP, MT>(e, pr, first, cnt, d_off, d_rows, d_flag, s)));
   return pulse_check_launch("pulse_poker_host_step");
 }
 
-// Every worker walks the chunks in order: waits until the chunk's records have landed (a host callback on the chunk's
-// stream raises its flag), expands its own slice, and the last worker out of a chunk rebuilds that chunk's offsets for
-// the next step.  No barrier between chunks: chunk c+1's copy overlaps chunk c's expansion.
-int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* reward, uint8_t* done, bool fresh) {
+// Every worker walks the chunks in order: waits until the chunk's records have landed (its epoch word has arrived in
+// pinned memory), expands its own slice, and the last worker out of a chunk rebuilds that chunk's offsets for the next
+// step.  No barrier between chunks: chunk c+1's copy overlaps chunk c's expansion.  Worker 0 -- the calling thread --
+// first runs `submit`, which queues the GPU work of every chunk: the others are already waiting for chunk 0 by then, so
+// queueing chunks 1.. overlaps chunk 0's transfer instead of preceding the whole phase.
+int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* reward, uint8_t* done, bool fresh,
+                  const std::function<int()>& submit) {
   const int T = e->pool->size();
   for (int c = 0; c < e->chunks; ++c) e->remaining[c].store(T, std::memory_order_relaxed);
   std::atomic<int> failed{0};
   std::vector<double> waits((size_t)T, 0.0), works((size_t)T, 0.0);
+  const uint32_t epoch = e->epoch;
   const double t0 = now_s();
-  e->pool->run([&, e, compacted, obs, reward, done, fresh, T](int wk) {
+  e->pool->run([&, e, compacted, obs, reward, done, fresh, T, epoch](int wk) {
+    if (wk == 0) {
+      const double s0 = now_s();
+      const int rc = submit();
+      e->t_submit += now_s() - s0;
+      if (rc) { failed.store(rc); return; }
+    }
     for (int c = 0; c < e->chunks; ++c) {
       const double w0 = now_s();
       long long spins = 0;
-      // spin briefly, then yield: with every CPU spinning, the driver thread that runs the stream callbacks (and so
-      // raises these flags) gets no core -- measured: 16 spinning workers on 16 CPUs waited 4.5 ms per step
-      while (!e->ready[c].load(std::memory_order_acquire)) {
-        if (++spins < 512) _mm_pause();
+      while (e->h_flag[c] != epoch) {
+        if (failed.load(std::memory_order_relaxed)) return;
+        if (++spins < 2048) _mm_pause();
         else std::this_thread::yield();
-        if ((spins & 0xFFFF) == 0 && now_s() - w0 > 60.0) { failed.store(1); return; }   // a dead GPU must not hang the caller
+        if ((spins & 0xFFFF) == 0 && now_s() - w0 > 60.0) { failed.store(PULSE_ENOTREADY); return; }   // a dead GPU must not hang the caller
       }
+      std::atomic_thread_fence(std::memory_order_acquire);
       const double w1 = now_s();
       const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
       const long long per = (((last - first) + T - 1) / T + 31) & ~31LL;
@@ -268,7 +284,7 @@ int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* rewar
         PulseExpandArgs a;
         a.rows = e->h_wire + (size_t)first * e->R;
         a.off = compacted ? e->h_off + (first >> 5) + c : nullptr;
-        a.live = e->live.data(); a.chunk_first = first; a.g0 = g0; a.g1 = g1;
+        a.live = e->live.data(); a.prev_live = e->prev_live.data(); a.chunk_first = first; a.g0 = g0; a.g1 = g1;
         a.row_words = e->R; a.obs_width = e->W; a.max_players = e->cfg.max_players;
         a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh;
         pulse_expand_range(a);
@@ -280,9 +296,9 @@ int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* rewar
   });
   e->t_expand += now_s() - t0;
   for (int i = 0; i < T; ++i) { e->t_wait_sum += waits[i]; e->t_work_sum += works[i]; }
-  for (int c = 0; c < e->chunks; ++c) e->ready[c].store(0, std::memory_order_relaxed);
-  if (failed.load()) { pulse_set_error("host env: timed out waiting for the device"); return PULSE_ENOTREADY; }
-  return 0;
+  const int f = failed.load();
+  if (f == PULSE_ENOTREADY) pulse_set_error("host env: timed out waiting for the device");
+  return f;
 }
 
 }  // namespace
@@ -340,9 +356,15 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
     e->streams.push_back(s); e->events.push_back(ev);
   }
   e->pool = new Pool(n_threads);
-  e->ready = new std::atomic<int>[e->chunks];
   e->remaining = new std::atomic<int>[e->chunks];
-  for (int c = 0; c < e->chunks; ++c) { e->ready[c].store(0); e->remaining[c].store(0); }
+  for (int c = 0; c < e->chunks; ++c) e->remaining[c].store(0);
+  {
+    uint32_t* hf = nullptr;
+    if ((rc = dev_alloc(e, &e->d_flag, (size_t)e->chunks + 32)) || (rc = pin_alloc(e, &hf, (size_t)e->chunks + 32))) return fail(rc);
+    for (int c = 0; c < e->chunks + 32; ++c) hf[c] = 0;
+    e->h_flag = hf;
+  }
+  e->prev_live.assign(N / 32 + 2, 0u);
   *out = e;
   return PULSE_OK;
 }
@@ -356,31 +378,36 @@ int pulse_poker_host_reset(PulsePokerHostEnv* e, int active_players, int rotatio
   HE_CUDA(cudaSetDevice(e->device));
   e->cfg.active_players = active_players;
   const PokerParams pr = params_of(e->cfg);
-  // the deal (no float32 observation), then every table's record
-  int rc = pulse_poker_packed_reset(&e->st, &e->cfg, nullptr, e->seed, e->env_base, e->hand_counter, e->first ? 0 : rotation,
-                                    (e->first ? 3 : 0) | (e->first ? 4 : 0), nullptr, e->streams[0]);
-  if (rc) return rc;
-  e->first = false;
-  e->hand_counter += 1;
-  const int grid = pulse_grid_for(e->N, kBlock);
-  HE_DISPATCH(pr.P, pr.M, (poker_host_rows_kernel<MP, MT><<<grid, kBlock, 0, e->streams[0]>>>(e->st, pr, e->d_wire, e->N)));
-  rc = pulse_check_launch("pulse_poker_host_reset");
-  if (rc) return rc;
-  HE_CUDA(cudaEventRecord(e->events[0], e->streams[0]));
-  for (int c = 0; c < e->chunks; ++c) {
-    const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
-    if (c > 0) HE_CUDA(cudaStreamWaitEvent(e->streams[c], e->events[0], 0));
-    HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, e->d_wire + (size_t)first * e->R, (size_t)cnt * e->R * 4,
-                            cudaMemcpyDeviceToHost, e->streams[c]));
-  }
-  for (int c = 0; c < e->chunks; ++c) HE_CUDA(cudaLaunchHostFunc(e->streams[c], mark_ready, &e->ready[c]));
-  e->last_h2d = 0; e->last_d2h = (long long)e->N * e->R * 4;
+  e->epoch += 1;
   // reward / done scratch when the caller does not want them
   std::vector<float> rtmp; std::vector<uint8_t> dtmp;
   float* rw = reward_host_or_null; uint8_t* dn = done_host_or_null;
   if (!rw) { rtmp.resize((size_t)e->N); rw = rtmp.data(); }
   if (!dn) { dtmp.resize((size_t)e->N); dn = dtmp.data(); }
-  return expand_chunks(e, false, obs_host, rw, dn, true);
+  // the deal (no float32 observation), then every table's record, copied chunk by chunk
+  auto submit = [e, pr, rotation]() -> int {
+    int rc = pulse_poker_packed_reset(&e->st, &e->cfg, nullptr, e->seed, e->env_base, e->hand_counter, e->first ? 0 : rotation,
+                                      e->first ? 7 : 0, nullptr, e->streams[0]);
+    if (rc) return rc;
+    e->first = false;
+    e->hand_counter += 1;
+    const int grid = pulse_grid_for(e->N, kBlock);
+    HE_DISPATCH(pr.P, pr.M, (poker_host_rows_kernel<MP, MT><<<grid, kBlock, 0, e->streams[0]>>>(e->st, pr, e->d_wire, e->N,
+                                                                                              e->d_flag, e->chunks, e->epoch)));
+    rc = pulse_check_launch("pulse_poker_host_reset");
+    if (rc) return rc;
+    HE_CUDA(cudaEventRecord(e->events[0], e->streams[0]));
+    for (int c = 0; c < e->chunks; ++c) {
+      const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
+      if (c > 0) HE_CUDA(cudaStreamWaitEvent(e->streams[c], e->events[0], 0));
+      HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, e->d_wire + (size_t)first * e->R, (size_t)cnt * e->R * 4,
+                              cudaMemcpyDeviceToHost, e->streams[c]));
+      HE_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(e->h_flag) + c, e->d_flag + c, 4, cudaMemcpyDeviceToHost, e->streams[c]));
+    }
+    return 0;
+  };
+  e->last_h2d = 0; e->last_d2h = (long long)e->N * e->R * 4;
+  return expand_chunks(e, false, obs_host, rw, dn, true, submit);
 }
 
 int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int action_bytes, float* obs_host,
@@ -404,28 +431,33 @@ int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int ac
       for (long long i = a; i < b; ++i) { const int64_t v = src[i]; e->h_act[i] = v < 0 ? (uint8_t)255 : v > 12 ? (uint8_t)13 : (uint8_t)v; }
     }
   });
-  const double t_sub0 = now_s();
-  e->t_stage += t_sub0 - t_stage0;
+  e->t_stage += now_s() - t_stage0;
+  e->epoch += 1;
   long long h2d = 0, d2h = 0;
   for (int c = 0; c < e->chunks; ++c) {
     const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
-    const long long n_off = ((cnt + 31) >> 5) + 1;
-    cudaStream_t s = e->streams[c];
-    uint32_t* d_off = e->d_off + (first >> 5) + c;
-    HE_CUDA(cudaMemcpyAsync(e->d_act + first, e->h_act + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
-    HE_CUDA(cudaMemcpyAsync(d_off, e->h_off + (first >> 5) + c, (size_t)n_off * 4, cudaMemcpyHostToDevice, s));
-    h2d += cnt + n_off * 4;
-    uint32_t* d_rows = e->d_wire + (size_t)first * e->R;
-    int rc = launch_step(e, pr, first, cnt, d_off, d_rows, s);
-    if (rc) return rc;
-    const size_t bytes = (size_t)e->chunk_rows[c] * e->R * 4;
-    if (bytes) HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, d_rows, bytes, cudaMemcpyDeviceToHost, s));
-    d2h += (long long)bytes;
-    HE_CUDA(cudaLaunchHostFunc(s, mark_ready, &e->ready[c]));
+    h2d += cnt + (((cnt + 31) >> 5) + 1) * 4;
+    d2h += e->chunk_rows[c] * e->R * 4 + 4;
   }
-  e->last_h2d = h2d; e->last_d2h = d2h;
-  e->t_submit += now_s() - t_sub0; e->calls += 1;
-  return expand_chunks(e, true, obs_host, reward_host, done_host, false);
+  e->last_h2d = h2d; e->last_d2h = d2h; e->calls += 1;
+  auto submit = [e, pr]() -> int {
+    for (int c = 0; c < e->chunks; ++c) {
+      const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
+      const long long n_off = ((cnt + 31) >> 5) + 1;
+      cudaStream_t s = e->streams[c];
+      uint32_t* d_off = e->d_off + (first >> 5) + c;
+      HE_CUDA(cudaMemcpyAsync(e->d_act + first, e->h_act + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
+      HE_CUDA(cudaMemcpyAsync(d_off, e->h_off + (first >> 5) + c, (size_t)n_off * 4, cudaMemcpyHostToDevice, s));
+      uint32_t* d_rows = e->d_wire + (size_t)first * e->R;
+      int rc = launch_step(e, pr, first, cnt, d_off, d_rows, e->d_flag + c, s);
+      if (rc) return rc;
+      const size_t bytes = (size_t)e->chunk_rows[c] * e->R * 4;
+      if (bytes) HE_CUDA(cudaMemcpyAsync(e->h_wire + (size_t)first * e->R, d_rows, bytes, cudaMemcpyDeviceToHost, s));
+      HE_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(e->h_flag) + c, e->d_flag + c, 4, cudaMemcpyDeviceToHost, s));
+    }
+    return 0;
+  };
+  return expand_chunks(e, true, obs_host, reward_host, done_host, false, submit);
 }
 
 int pulse_poker_host_info(const PulsePokerHostEnv* e, int* row_bytes, int* obs_width, int* chunks, int* threads,
@@ -466,9 +498,32 @@ int pulse_poker_wire_expand_host(const uint32_t* rows, long long n_rows, int max
   // the host env's own expander (AVX2 when the CPU has it), driven as one chunk in which every table has a record
   std::vector<uint32_t> live((size_t)(n_rows + 31) / 32 + 1, 0u);
   PulseExpandArgs a;
-  a.rows = rows; a.off = nullptr; a.live = live.data(); a.chunk_first = 0; a.g0 = 0; a.g1 = n_rows;
+  std::vector<uint32_t> prev(live.size(), 0u);
+  a.rows = rows; a.off = nullptr; a.live = live.data(); a.prev_live = prev.data(); a.chunk_first = 0; a.g0 = 0; a.g1 = n_rows;
   a.row_words = R; a.obs_width = W; a.max_players = max_players;
   a.obs = obs_out; a.reward = reward_out; a.done = done_out; a.fresh = true;
+  pulse_expand_range(a);
+  return PULSE_OK;
+}
+
+// pure host function: one step of the host env's bookkeeping without a GPU -- `rows` holds the records of the tables
+// whose bit is set in live_inout (compacted in table order; every table when fresh != 0); obs / reward / done are the
+// caller's persistent arrays of n_tables entries; live_inout / prev_live_inout (ceil(n / 32) words) are updated exactly as
+// the env updates them.  Exists so the CPU suite can drive the expander through whole hands.
+int pulse_poker_wire_expand_step_host(const uint32_t* rows, uint32_t* live_inout, uint32_t* prev_live_inout,
+                                      long long n_tables, int max_players, int fresh, float* obs, float* reward,
+                                      uint8_t* done) {
+  PULSE_REQUIRE(rows && live_inout && prev_live_inout && obs && reward && done, "null argument");
+  PULSE_REQUIRE(max_players >= 2 && max_players <= 16 && n_tables >= 0, "bad arguments");
+  const long long groups = (n_tables + 31) >> 5;
+  std::vector<uint32_t> off((size_t)groups + 1, 0u);
+  uint32_t acc = 0;
+  for (long long w = 0; w < groups; ++w) { off[w] = acc; acc += (uint32_t)__builtin_popcount(live_inout[w]); }
+  PulseExpandArgs a;
+  a.rows = rows; a.off = fresh ? nullptr : off.data(); a.live = live_inout; a.prev_live = prev_live_inout;
+  a.chunk_first = 0; a.g0 = 0; a.g1 = n_tables;
+  a.row_words = pkw_row_words(max_players); a.obs_width = 13 + 3 * (max_players - 1); a.max_players = max_players;
+  a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh != 0;
   pulse_expand_range(a);
   return PULSE_OK;
 }

@@ -50,9 +50,13 @@ __attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, i
     const uint32_t mask = a.fresh ? 0xFFFFFFFFu : a.live[wg];                                                   \
     uint32_t next = 0;                                                                                          \
     size_t slot = a.off ? a.off[wg - (a.chunk_first >> 5)] : (size_t)(gb - a.chunk_first);                      \
-    /* tables that were already finished: reward 0 (PokerGPU.py:632), done stays 1, the row stays as it is */   \
-    if (mask != 0xFFFFFFFFu || cnt != 32) memset(a.reward + gb, 0, sizeof(float) * (size_t)cnt);               \
-    uint32_t m = cnt == 32 ? mask : (mask & ((1u << cnt) - 1u));                                                \
+    /* a table that finished on the previous step: reward 0 from now on (PokerGPU.py:632); done stays 1 and the   \
+       row stays as it is.  Tables finished earlier were zeroed then. */                                         \
+    const uint32_t in_range = cnt == 32 ? 0xFFFFFFFFu : ((1u << cnt) - 1u);   /* the batch's last group may be short */ \
+    uint32_t z = a.fresh ? 0u : (a.prev_live[wg] & ~mask & in_range);                                            \
+    while (z) { a.reward[gb + __builtin_ctz(z)] = 0.0f; z &= z - 1; }                                            \
+    a.prev_live[wg] = mask;                                                                                      \
+    uint32_t m = mask & in_range;                                                                               \
     while (m) {                                                                                                 \
       const int b = __builtin_ctz(m);                                                                           \
       m &= m - 1;                                                                                               \

@@ -105,6 +105,13 @@ __device__ __forceinline__ void store_row16(float* dst, const float (&r)[16]) {
                "f"(r[11]), "f"(r[12]), "f"(r[13]), "f"(r[14]), "f"(r[15]) : "memory");
 }
 
+// AUTO == 3, tile-local redeal (an experiment kept selectable, NOT the default -- see pulse_poker_packed_step): tables
+// that were already finished when the step began are not stepped; once the tile's
+// 128 tables are done, the CTA's first warp deals them their next hands -- compacted (one lane per finished table, so
+// the ~1,500-instruction deal runs at the density of a separate pass) and in place: the tile's state sectors were just
+// read and written by the step phase and sit in L2, so the deal's scattered 4-byte stores merge there.  The separate
+// redeal pass (AUTO == 2) re-read a counter for every table and paid a DRAM read-modify-write per scattered store --
+// 410 MB of traffic per 4M-table step, most of its 85 us (profiles/r2b_autoreset_redeal_raw.csv).
 template <int MAXP, int MT, int MINB, bool POLICY = false, int AUTO = 0, bool DIRECT = false>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
@@ -113,6 +120,9 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
                          int starting_bbs, int max_bbs, long long n, int l2_ahead,
                          PackedPolicy pol = PackedPolicy()) {
   extern __shared__ float4 smem4[];
+  __shared__ int rd_list[AUTO == 3 ? kBlock : 1];
+  __shared__ int rd_count;
+  __shared__ uint32_t rd_deck[AUTO == 3 ? 13 * 32 : 1];
   if (l2_ahead > 0)  // bit 30 of l2_ahead: include the hand-value words
     packed_prefetch_tile<MAXP>(S, actions, pr.AP, ((long long)blockIdx.x + (l2_ahead & 0xFFFFF)) * kBlock, n,
                                (l2_ahead >> 30) & 1);
@@ -121,14 +131,57 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
   const int W = 13 + 3 * (pr.M - 1);
   for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
     const long long g = base + threadIdx.x;
+    if (AUTO == 3) {
+      if (threadIdx.x == 0) rd_count = 0;
+      __syncthreads();
+    }
     float row[WT];
-    if (g < n)
-      packed_step_one<MAXP, POLICY, AUTO>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base,
-                                          starting_bbs, max_bbs, g, n, &pol);
+    bool marked = false;
+    if (g < n) {
+      PokerTable<MAXP> t;
+      const PackedStepResult r = packed_step_core<MAXP, POLICY, AUTO>(S, pr, actions, auto_reset, seed, env_base,
+                                                                      starting_bbs, max_bbs, g, n, &pol, t);
+      marked = AUTO == 3 && auto_reset && r.was_done;
+      if (!marked) {
+        reward_out[g] = r.reward;
+        done_out[g] = r.done;
+      }
+      if (!(marked && DIRECT)) pk_obs(t, pr, row);
+    }
     if (DIRECT && MT == 2) {
-      if (g < n) store_row16(obs_out + g * 16, reinterpret_cast<const float(&)[16]>(row));
+      if (g < n && !marked) store_row16(obs_out + g * 16, reinterpret_cast<const float(&)[16]>(row));
     } else {
       stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
+    }
+    if (AUTO == 3) {
+      const unsigned lane = threadIdx.x & 31u;
+      const unsigned bal = __ballot_sync(0xFFFFFFFFu, marked);
+      if (bal) {
+        int pos = 0;
+        if (lane == 0) pos = atomicAdd(&rd_count, __popc(bal));
+        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+        if (marked) rd_list[pos + __popc(bal & ((1u << lane) - 1u))] = (int)threadIdx.x;
+      }
+      __syncthreads();
+      if (threadIdx.x < 32) {
+        const int cnt = rd_count;
+        PackedDeckShared dk{reinterpret_cast<uint8_t*>(rd_deck) + 4 * threadIdx.x, 4 * 32};
+        for (int i = threadIdx.x; i < cnt; i += 32) {
+          const long long g2 = base + rd_list[i];
+          float nrow[WT];
+          packed_reset_one<MAXP>(S, pr, nullptr, seed, env_base, S.hand_ctr[g2] + 1u, 0, 4, starting_bbs, max_bbs, nrow, g2, n, dk);
+          reward_out[g2] = 0.0f;
+          done_out[g2] = 0;
+          float* dst = obs_out + g2 * W;
+          if (DIRECT && MT == 2) {
+            store_row16(dst, reinterpret_cast<const float(&)[16]>(nrow));
+          } else if ((W & 3) == 0 && (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0) {
+            for (int c = 0; c < W; c += 4) *reinterpret_cast<float4*>(dst + c) = make_float4(nrow[c], nrow[c + 1], nrow[c + 2], nrow[c + 3]);
+          } else {
+            for (int c = 0; c < W; ++c) dst[c] = nrow[c];
+          }
+        }
+      }
     }
   }
 }
@@ -214,6 +267,35 @@ poker_packed_redeal_kernel(PulsePokerPacked S, PokerParams pr, uint64_t seed, ui
       }
     }
     __syncthreads();
+  }
+}
+
+// K steps per launch with every seat played on the device (SURVEY.md 8(b) pulse_poker_rollout): at the reference's own
+// benchmark size (N = 256, benchmarking/Poker) one step is a few microseconds of work behind a launch, so the loop over
+// steps runs inside the kernel.  A thread owns its table for all K steps; the table's words go through global memory
+// between steps (they stay in L1/L2), so the per-step body is exactly the single-step one.  Outputs step-major.
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock)
+poker_packed_rollout_kernel(PulsePokerPacked S, PokerParams pr, PackedPolicy pol, int K, int auto_reset, uint64_t seed,
+                            uint64_t env_base, int starting_bbs, int max_bbs, long long n, float* __restrict__ obs_final,
+                            float* __restrict__ reward_out, uint8_t* __restrict__ done_out, int64_t* __restrict__ action_out) {
+  const int W = 13 + 3 * (pr.M - 1);
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
+    PackedPolicy p = pol;
+    for (int k = 0; k < K; ++k) {
+      p.counter = pol.counter + (uint32_t)k;
+      p.chosen = action_out ? action_out + (long long)k * n : nullptr;
+      PokerTable<MAXP> t;
+      const PackedStepResult r = packed_step_core<MAXP, true, 1>(S, pr, static_cast<const int64_t*>(nullptr), auto_reset, seed,
+                                                                 env_base, starting_bbs, max_bbs, g, n, &p, t);
+      reward_out[(long long)k * n + g] = r.reward;
+      done_out[(long long)k * n + g] = r.done;
+      if (k == K - 1 && obs_final) {
+        float row[13 + 3 * 15];
+        pk_obs(t, pr, row);
+        for (int c = 0; c < W; ++c) obs_final[g * W + c] = row[c];
+      }
+    }
   }
 }
 
@@ -333,6 +415,11 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   // heads-up rows: direct 256-bit stores (PULSE_POKER_OBS_DIRECT=0 keeps the staged write-out, for A/B runs)
   static const bool direct_env = !(getenv("PULSE_POKER_OBS_DIRECT") && atoi(getenv("PULSE_POKER_OBS_DIRECT")) == 0);
   const bool direct = direct_env && (reinterpret_cast<uintptr_t>(obs_out) & 31u) == 0;
+  // auto_reset: finished tables are dealt by the compacting redeal pass that follows the step kernel.  Measured on
+  // B200 (profiles/r2e_bench_lines.jsonl): dealing them inside the step kernel tile by tile (PULSE_POKER_REDEAL_TILE=1,
+  // AUTO == 3) is 4-15% slower on every auto-reset workload -- the 128-table tile yields ~19 deals, two thirds of one
+  // warp, and the CTA waits for that warp -- so the separate pass stays the default.
+  static const bool redeal_pass = !(getenv("PULSE_POKER_REDEAL_TILE") && atoi(getenv("PULSE_POKER_REDEAL_TILE")) != 0);
 #define PKP_STEP_A(MP, MT, MINB, AUTO, SMEM)                                                              \
   do {                                                                                                    \
     if ((MT) == 2 && direct)                                                                              \
@@ -344,10 +431,11 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
           *st, pr, actions, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs, cfg->max_bbs, \
           (long long)cfg->n_games, l2_ahead_for(MINB, MP));                                               \
   } while (0)
-#define PKP_STEP_B(MP, MT, MINB, SMEM)                       \
-  do {                                                       \
-    if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);       \
-    else PKP_STEP_A(MP, MT, MINB, 0, SMEM);                  \
+#define PKP_STEP_B(MP, MT, MINB, SMEM)                                  \
+  do {                                                                  \
+    if (auto_reset && redeal_pass) PKP_STEP_A(MP, MT, MINB, 2, SMEM);   \
+    else if (auto_reset) PKP_STEP_A(MP, MT, MINB, 3, SMEM);             \
+    else PKP_STEP_A(MP, MT, MINB, 0, SMEM);                             \
   } while (0)
   // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 6 / 4 for the six- / ten-seat
   // builds (below), 8 (64) for the generic ones -- measured on B200 (profiles/r1c_poker_launch_bounds.md, r1r_exp5/6);
@@ -387,7 +475,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #undef PKP_STEP_A
 #undef PKP_SMEM4
   rc = pulse_check_launch("pulse_poker_packed_step");
-  if (rc || !auto_reset) return rc;
+  if (rc || !auto_reset || !redeal_pass) return rc;
   return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
 }
 
@@ -419,6 +507,7 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
   static const bool direct_env = !(getenv("PULSE_POKER_OBS_DIRECT") && atoi(getenv("PULSE_POKER_OBS_DIRECT")) == 0);
   const bool direct = direct_env && (reinterpret_cast<uintptr_t>(obs_out) & 31u) == 0;
+  static const bool redeal_pass = !(getenv("PULSE_POKER_REDEAL_TILE") && atoi(getenv("PULSE_POKER_REDEAL_TILE")) != 0);
 #define PKP_POL_A(MP, MT, MINB, AUTO, SMEM)                                                                \
   do {                                                                                                     \
     if ((MT) == 2 && direct)                                                                               \
@@ -430,10 +519,11 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
           *st, pr, actions_or_null, obs_out, reward_out, done_out, AUTO, seed, env_base, cfg->starting_bbs,  \
           cfg->max_bbs, (long long)cfg->n_games, l2_ahead_for(MINB, MP), pol);                             \
   } while (0)
-#define PKP_POL(MP, MT, MINB, SMEM)                          \
-  do {                                                       \
-    if (auto_reset) PKP_POL_A(MP, MT, MINB, 2, SMEM);        \
-    else PKP_POL_A(MP, MT, MINB, 0, SMEM);                   \
+#define PKP_POL(MP, MT, MINB, SMEM)                                     \
+  do {                                                                  \
+    if (auto_reset && redeal_pass) PKP_POL_A(MP, MT, MINB, 2, SMEM);    \
+    else if (auto_reset) PKP_POL_A(MP, MT, MINB, 3, SMEM);              \
+    else PKP_POL_A(MP, MT, MINB, 0, SMEM);                              \
   } while (0)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
   const bool aligned = (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0;
@@ -452,8 +542,35 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
 #undef PKP_POL_A
 #undef PKP_SMEM4
   rc = pulse_check_launch("pulse_poker_packed_step_policy");
-  if (rc || !auto_reset) return rc;
+  if (rc || !auto_reset || !redeal_pass) return rc;
   return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
+}
+
+int pulse_poker_packed_rollout(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const uint8_t* seat_kinds,
+                               uint32_t counter, int n_steps, int auto_reset, uint64_t seed, uint64_t env_base,
+                               float* obs_final_or_null, float* reward_out, uint8_t* done_out, int64_t* actions_out_or_null,
+                               cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  PULSE_REQUIRE(seat_kinds != nullptr, "seat_kinds is null");
+  PULSE_REQUIRE(n_steps >= 0, "n_steps < 0");
+  PackedPolicy pol;
+  for (int s = 0; s < 16; ++s) {
+    pol.kinds.kind[s] = s < cfg->n_players ? seat_kinds[s] : (uint8_t)PULSE_AGENT_RANDOM;
+    if (s < cfg->n_players)
+      PULSE_REQUIRE(pol.kinds.kind[s] >= PULSE_AGENT_RANDOM && pol.kinds.kind[s] <= PULSE_AGENT_SMALL_BALL,
+                    "a rollout plays every seat on the device: no PULSE_AGENT_EXTERNAL seats");
+  }
+  if (cfg->n_games == 0 || n_steps == 0) return PULSE_OK;
+  PULSE_REQUIRE(reward_out && done_out, "null buffer");
+  PULSE_REQUIRE(!auto_reset || st->hand_ctr, "auto_reset needs hand_ctr");
+  pol.chance2 = nullptr; pol.chosen = nullptr; pol.seat_before = nullptr; pol.counter = counter;
+  PokerParams pr = make_params(cfg);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_rollout_kernel<MP><<<grid, kBlock, 0, stream>>>(
+                         *st, pr, pol, n_steps, auto_reset, seed, env_base, cfg->starting_bbs, cfg->max_bbs,
+                         (long long)cfg->n_games, obs_final_or_null, reward_out, done_out, actions_out_or_null)));
+  return pulse_check_launch("pulse_poker_packed_rollout");
 }
 
 int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,

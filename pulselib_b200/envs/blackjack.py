@@ -89,40 +89,42 @@ class BlackJack(gym.Env):
         self._view = None
         return self.obs, self.rewards, self.terminated, None, self.get_info()
 
-    def rollout(self, actions, reset_first=False):
+    def rollout(self, actions, reset_first=False, n_hands=1):
         """K steps in ONE launch (pulse_blackjack_rollout): actions int64 or uint8 [K, N] -> (obs int32 [K, N, 3], rewards
         int32 [K, N], terminated bool [K, N]), exactly what K step() calls would return one after another.  With
-        reset_first the hand is dealt first (= reset(); the deal's observation is left in self.obs... of step -1:
-        returned as a fourth value).  The env's obs / rewards / terminated attributes are left at the last step's values."""
+        reset_first the hand is dealt first (= reset()) and the deal's observation is returned as a fourth value.
+        n_hands > 1: actions [n_hands * K, N]; every hand after the first (and the first with reset_first) starts with a
+        fresh deal -- what n_hands x (reset(), K x step()) would return; the deals' observations come back [n_hands, N, 3].
+        The env's obs / rewards / terminated attributes are left at the last step's values."""
         n, dev = self.batch_size, self.device
         actions = torch.as_tensor(actions, device=dev)
         if actions.dtype not in (torch.uint8, torch.int64):
             actions = actions.to(torch.int64)
         actions = actions.contiguous()
-        if actions.dim() != 2 or actions.shape[1] != n:
-            raise ValueError(f"actions must have shape (K, {n}), got {tuple(actions.shape)}")
-        K = int(actions.shape[0])
-        if self._st is None or reset_first:
+        H = int(n_hands)
+        if actions.dim() != 2 or actions.shape[1] != n or H < 1 or actions.shape[0] % H:
+            raise ValueError(f"actions must have shape (n_hands * K, {n}), got {tuple(actions.shape)}")
+        KT = int(actions.shape[0])
+        if self._st is None:
             if not reset_first:
                 raise _lib.PulseError("BlackJack.rollout called before reset")
-            if self._st is None:
-                self._st = torch.empty(n, dtype=torch.int32, device=dev)
-                self._deck = torch.empty((52, n), dtype=torch.uint8, device=dev)
-        obs = torch.empty((K, n, 3), dtype=torch.int32, device=dev)
-        rewards = torch.empty((K, n), dtype=torch.int32, device=dev)
-        term = torch.empty((K, n), dtype=torch.bool, device=dev)
-        first_obs = torch.empty((n, 3), dtype=torch.int32, device=dev) if reset_first else None
+            self._st = torch.empty(n, dtype=torch.int32, device=dev)
+            self._deck = torch.empty((52, n), dtype=torch.uint8, device=dev)
+        obs = torch.empty((KT, n, 3), dtype=torch.int32, device=dev)
+        rewards = torch.empty((KT, n), dtype=torch.int32, device=dev)
+        term = torch.empty((KT, n), dtype=torch.bool, device=dev)
+        deals = H - (0 if reset_first else 1)
+        first_obs = torch.empty((H, n, 3) if H > 1 else (n, 3), dtype=torch.int32, device=dev) if deals else None
         with _lib.device_guard(dev):
             _lib.check(self._lib.pulse_blackjack_rollout(
-                ptr(self._st), ptr(self._deck), ptr(actions), c_i(actions.element_size()), c_i(K), c_i(1 if reset_first else 0),
-                c_u64(self.seed_value), c_u64(self.env_base), c_u32(self._episode), ptr(first_obs), ptr(obs), ptr(rewards),
-                ptr(term), c_i(n), _lib.cuda_stream(dev)), "pulse_blackjack_rollout")
-        if reset_first:
-            self._episode += 1
-        if K:
+                ptr(self._st), ptr(self._deck), ptr(actions), c_i(actions.element_size()), c_i(KT // H), c_i(H),
+                c_i(1 if reset_first else 0), c_u64(self.seed_value), c_u64(self.env_base), c_u32(self._episode),
+                ptr(first_obs), ptr(obs), ptr(rewards), ptr(term), c_i(n), _lib.cuda_stream(dev)), "pulse_blackjack_rollout")
+        self._episode += deals
+        if KT:
             self.obs, self.rewards, self.terminated = obs[-1], rewards[-1], term[-1]
         self._view = None
-        return (obs, rewards, term, first_obs) if reset_first else (obs, rewards, term)
+        return (obs, rewards, term, first_obs) if deals else (obs, rewards, term)
 
     def get_obs(self):
         return self.obs

@@ -192,6 +192,29 @@ class PokerGPUPacked(gym.Env):
             info["seat_idx_before"] = seat
         return obs, rewards, done, self.is_truncated, info
 
+    def rollout_policy(self, seat_kinds, n_steps, counter=None, return_actions=True):
+        """K steps in ONE launch with every seat played by a device rule (pulse_poker_packed_rollout): returns
+        (final obs [N, W], rewards float32 [K, N], dones bool [K, N], actions int64 [K, N] or None) -- what K
+        step_policy() calls with counters counter .. counter + K - 1 would return one after another."""
+        kb = bytes(seat_kinds)
+        if len(kb) != self.n_players:
+            raise ValueError(f"seat_kinds must have {self.n_players} entries")
+        N, K, dev = self.n_games, int(n_steps), self.device
+        if counter is None:
+            counter = getattr(self, "_policy_counter", -1) + 1
+        self._policy_counter = counter + K - 1
+        rewards = torch.empty((K, N), dtype=torch.float32, device=dev)
+        done = torch.empty((K, N), dtype=torch.bool, device=dev)
+        chosen = torch.empty((K, N), dtype=torch.int64, device=dev) if return_actions else None
+        cfg = self._config()
+        with _lib.device_guard(dev):
+            _lib.check(self._lib.pulse_poker_packed_rollout(
+                C.byref(self._packed), C.byref(cfg), C.c_char_p(kb), c_u32(counter), c_i(K), c_i(1 if self.auto_reset else 0),
+                c_u64(self.seed_value), c_u64(self.env_base), ptr(self.obs), ptr(rewards), ptr(done), ptr(chosen),
+                _lib.cuda_stream(dev)), "pulse_poker_packed_rollout")
+        self._stepped = True
+        return self.obs, rewards, done, chosen
+
     def enumerated_strength(self):
         """float32 [N, active_players]: river hand strength averaged over the board cards still to come, per seat
         (see include/pulse_envs.h).  An optional reward input; step() keeps the reference's proxy."""

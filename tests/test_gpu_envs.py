@@ -381,3 +381,25 @@ def test_tfe_rollout_equals_k_steps(side, n, cuda_device):
         np.testing.assert_array_equal(a.boards.cpu().numpy(), b.boards.cpu().numpy())
     if side == 3:
         assert int(done_k.sum()) > 0
+
+
+def test_blackjack_rollout_many_hands_per_launch(cuda_device):
+    """n_hands hands of K steps in one launch == n_hands x (reset(), K x step())"""
+    import torch
+    from pulselib_b200.envs.blackjack import BlackJack
+
+    n, K, H = 4096, 8, 5
+    a = BlackJack(device=cuda_device, batch_size=n, seed=9, env_base=3)
+    b = BlackJack(device=cuda_device, batch_size=n, seed=9, env_base=3)
+    rng = np.random.default_rng(2)
+    acts = rng.integers(0, 2, (H * K, n)).astype(np.uint8)
+    obs, rew, term, deals = a.rollout(torch.from_numpy(acts).to(cuda_device), reset_first=True, n_hands=H)
+    for h in range(H):
+        o0, _ = b.reset()
+        np.testing.assert_array_equal(deals[h].cpu().numpy(), o0.cpu().numpy(), err_msg=f"hand {h} deal")
+        for k in range(K):
+            o, r, t, _, _ = b.step(torch.from_numpy(acts[h * K + k].astype(np.int64)).to(cuda_device))
+            i = h * K + k
+            np.testing.assert_array_equal(obs[i].cpu().numpy(), o.cpu().numpy(), err_msg=f"hand {h} step {k}")
+            np.testing.assert_array_equal(rew[i].cpu().numpy(), r.cpu().numpy())
+            np.testing.assert_array_equal(term[i].cpu().numpy(), t.cpu().numpy())

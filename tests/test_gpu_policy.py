@@ -94,3 +94,28 @@ def test_fused_packed_step_equals_oracle_policy_then_step(P, kinds, N, cuda_devi
         snap = env.unpack()
         for f in pu.INT_N + pu.INT_NP + ("board", "hands"):
             assert np.array_equal(snap[f].cpu().numpy(), getattr(orc, f)), f"hand {hand} field {f}"
+
+
+@pytest.mark.parametrize("P,auto", [(2, True), (6, False), (6, True)])
+def test_rollout_equals_k_policy_steps(P, auto, cuda_device):
+    """pulse_poker_packed_rollout: K steps in one launch == K step_policy() calls with the same tape counters"""
+    from pulselib_b200 import policy
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+    kw = dict(n_players=P, max_players=P, n_games=256, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3, K=100, alpha=50,
+              seed=11, env_base=5, auto_reset=auto)
+    kinds = bytes(([policy.TIGHT_AGGRESSIVE, policy.RANDOM, policy.SMALL_BALL, policy.LOOSE_PASSIVE, policy.HEURISTIC_HANDS,
+                    policy.RANDOM])[:P])
+    a, b = PokerGPUPacked(cuda_device, **kw), PokerGPUPacked(cuda_device, **kw)
+    a.reset(); b.reset()
+    K = 40
+    obs, rew, done, acts = a.rollout_policy(kinds, K, counter=100)
+    for k in range(K):
+        o, r, d, _, info = b.step_policy(kinds, counter=100 + k)
+        np.testing.assert_array_equal(acts[k].cpu().numpy(), info["actions"].cpu().numpy(), err_msg=f"step {k} actions")
+        np.testing.assert_array_equal(rew[k].cpu().numpy(), r.cpu().numpy(), err_msg=f"step {k} rewards")
+        np.testing.assert_array_equal(done[k].cpu().numpy(), d.cpu().numpy(), err_msg=f"step {k} dones")
+    np.testing.assert_array_equal(obs.cpu().numpy(), o.cpu().numpy())
+    sa, sb = a.unpack(), b.unpack()
+    for f in sa:
+        np.testing.assert_array_equal(sa[f].cpu().numpy(), sb[f].cpu().numpy(), err_msg=f)
