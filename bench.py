@@ -382,6 +382,24 @@ def run_gpu(args, wl, name):
     assert int(stats_all[0].item()) == world * N * e2e_steps
     hinfo = henv.info()
     htime = henv.timing()
+    # the same loop with the packed records left unexpanded (pulse_poker_host_step_records): what the link and a
+    # record-reading consumer can sustain when the host does not write 64 B of float32 per live table-step
+    def record_steps(k):
+        for i in range(k):
+            if i % L == 0:
+                henv.reset(expand=False)
+            henv.step_records(h_act[i % L])
+
+    record_steps(L)
+    barrier()
+    w0 = time.perf_counter()
+    record_steps(e2e_steps)
+    torch.cuda.synchronize(dev)
+    rec_ms = torch.tensor([(time.perf_counter() - w0) * 1e3], dtype=torch.float64, device=dev)
+    barrier()
+    if dist is not None:
+        dist.all_reduce(rec_ms, op=dist.ReduceOp.MAX)
+    rec_value = world * N * e2e_steps / (float(rec_ms.item()) * 1e-3)
     henv.close()
 
     if rank == 0:
@@ -414,6 +432,9 @@ def run_gpu(args, wl, name):
                     "reference_contract_bytes_per_table_step": 8 + 4 * env.obs_size + 4 + 1,
                     "host_ms_per_step": {k: round(1e3 * v / max(1.0, htime["calls"]), 4) for k, v in htime.items() if k != "calls"},
                     "timing": "wall clock around the host loop (the API is host-synchronous), device synchronised on both sides"},
+            "e2e_records": {"value": rec_value, "unit": "env-steps/s",
+                            "api": "PokerHostEnv.step_records (pulse_poker_host_step_records): same copies, the packed records stay "
+                                   "in pinned host memory, only the done flags are written out"},
             "run_stats_device": dict(zip(("env_steps", "episodes_done", "reward_sum", "reward_sq_sum"), dev_stats)),
             "run_stats_allreduce": {"env_steps": stats_all[0].item(), "done_flags_at_end": stats_all[1].item(),
                                     "reward_sum_at_end": stats_all[2].item(), "ranks": world,

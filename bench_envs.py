@@ -332,7 +332,7 @@ def _e2e_blackjack_rollout(dev, rank, steps, n):
 
     env = BlackJack(dev, n, seed=SEED, env_base=rank * n)
     KT = 128                                         # 16 hands of 8 steps per launch
-    hands = max(1, steps // KT)
+    hands = max(16, steps // KT)                     # launches timed
     h_act = torch.randint(0, 2, (KT, n), dtype=torch.uint8).pin_memory()
     d_act = torch.empty((KT, n), dtype=torch.uint8, device=dev)
     h_obs = torch.empty((KT, n, 3), dtype=torch.int32).pin_memory()

@@ -342,12 +342,23 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
                             size_t n_hand_ranks, uint64_t seed, uint64_t env_base, int device, int n_chunks,
                             int n_threads);
 void pulse_poker_host_destroy(PulsePokerHostEnv* env);
-/* reset (PokerGPU.py:73-157) with decks from the chance tape; active_players = the table size of this hand */
+/* reset (PokerGPU.py:73-157) with decks from the chance tape; active_players = the table size of this hand.
+ * obs_host == NULL: records only (every table's record is left in the pinned buffer, see pulse_poker_host_step_records) */
 int pulse_poker_host_reset(PulsePokerHostEnv* env, int active_players, int rotation, float* obs_host,
                            float* reward_host_or_null, uint8_t* done_host_or_null);
 /* step (:527-633); actions_host: uint8 [N] (action_bytes 1) or int64 [N] (action_bytes 8) */
 int pulse_poker_host_step(PulsePokerHostEnv* env, const void* actions_host, int action_bytes, float* obs_host,
                           float* reward_host, uint8_t* done_host);
+/* The step without the float32 expansion, for consumers that read the packed records themselves (csrc/poker_wire.cuh; or
+ * expand single rows on demand with pulse_poker_wire_expand_host): only done_host is written.  The records of the call
+ * stay in the env's pinned buffer until the next call: chunk c's records (table order), their number and the chunk's
+ * table range come from pulse_poker_host_records; a table has a record iff its bit is set in pulse_poker_host_live_mask
+ * (bit b of word w = table 32 w + b was live when the call began; after a reset every table has one).  Do not mix with
+ * pulse_poker_host_step on one env between resets (the float32 arrays would miss the skipped steps). */
+int pulse_poker_host_step_records(PulsePokerHostEnv* env, const void* actions_host, int action_bytes, uint8_t* done_host);
+int pulse_poker_host_records(const PulsePokerHostEnv* env, int chunk, const uint32_t** rows, long long* n_rows,
+                             long long* first_table, long long* n_tables);
+const uint32_t* pulse_poker_host_live_mask(const PulsePokerHostEnv* env);
 /* record size, observation width, chunk / thread counts, and the bytes the last call moved over PCIe */
 int pulse_poker_host_info(const PulsePokerHostEnv* env, int* row_bytes, int* obs_width, int* chunks, int* threads,
                           long long* last_h2d_bytes, long long* last_d2h_bytes);

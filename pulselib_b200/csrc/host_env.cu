@@ -151,6 +151,8 @@ struct PulsePokerHostEnv {
   uint8_t* h_act = nullptr; uint32_t* h_off = nullptr; uint32_t* h_wire = nullptr;
   std::vector<uint32_t> live;              // bit b of live[w]: table 32 w + b was not done after the last call
   std::vector<long long> chunk_rows;       // live tables per chunk at the start of the next step
+  std::vector<long long> last_rows;        // records per chunk of the last call (what sits in h_wire now)
+  bool last_compacted = false;
   std::vector<cudaStream_t> streams;
   std::vector<cudaEvent_t> events;
   // "chunk c has landed": the kernel writes the call's epoch into d_flag[c], a 4-byte copy queued behind the chunk's
@@ -252,8 +254,13 @@ int launch_step(PulsePokerHostEnv* e, const PokerParams& pr, long long first, lo
 // first runs `submit`, which queues the GPU work of every chunk: the others are already waiting for chunk 0 by then, so
 // queueing chunks 1.. overlaps chunk 0's transfer instead of preceding the whole phase.
 int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* reward, uint8_t* done, bool fresh,
-                  const std::function<int()>& submit) {
+                  const std::function<int()>& submit, bool records_only = false) {
   const int T = e->pool->size();
+  for (int c = 0; c < e->chunks; ++c) {
+    const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
+    e->last_rows[c] = compacted ? e->chunk_rows[c] : last - first;
+  }
+  e->last_compacted = compacted;
   for (int c = 0; c < e->chunks; ++c) e->remaining[c].store(T, std::memory_order_relaxed);
   std::atomic<int> failed{0};
   std::vector<double> waits((size_t)T, 0.0), works((size_t)T, 0.0);
@@ -286,7 +293,7 @@ int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* rewar
         a.off = compacted ? e->h_off + (first >> 5) + c : nullptr;
         a.live = e->live.data(); a.prev_live = e->prev_live.data(); a.chunk_first = first; a.g0 = g0; a.g1 = g1;
         a.row_words = e->R; a.obs_width = e->W; a.max_players = e->cfg.max_players;
-        a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh;
+        a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh; a.records_only = records_only;
         pulse_expand_range(a);
       }
       if (e->remaining[c].fetch_sub(1, std::memory_order_acq_rel) == 1) rebuild_offsets(e, c);
@@ -347,6 +354,7 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
   e->st.hand_ranks = hr; e->st.n_hand_ranks = 36875; e->st.idx = nullptr; e->st.prev_invested = nullptr;
   e->live.assign(N / 32 + 2, 0u);
   e->chunk_rows.assign(e->chunks, 0);
+  e->last_rows.assign(e->chunks, 0);
   for (int c = 0; c < e->chunks; ++c) {
     cudaStream_t s; cudaEvent_t ev;
     if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess ||
@@ -373,7 +381,7 @@ void pulse_poker_host_destroy(PulsePokerHostEnv* env) { delete env; }
 
 int pulse_poker_host_reset(PulsePokerHostEnv* e, int active_players, int rotation, float* obs_host, float* reward_host_or_null,
                            uint8_t* done_host_or_null) {
-  PULSE_REQUIRE(e && obs_host, "null argument");
+  PULSE_REQUIRE(e != nullptr, "null argument");   // obs_host == NULL: records only (see pulse_poker_host_step_records)
   PULSE_REQUIRE(active_players >= 2 && active_players <= e->cfg.n_players, "active_players must be in 2..n_players");
   HE_CUDA(cudaSetDevice(e->device));
   e->cfg.active_players = active_players;
@@ -407,12 +415,12 @@ int pulse_poker_host_reset(PulsePokerHostEnv* e, int active_players, int rotatio
     return 0;
   };
   e->last_h2d = 0; e->last_d2h = (long long)e->N * e->R * 4;
-  return expand_chunks(e, false, obs_host, rw, dn, true, submit);
+  return expand_chunks(e, false, obs_host, rw, dn, true, submit, obs_host == nullptr);
 }
 
-int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int action_bytes, float* obs_host,
-                          float* reward_host, uint8_t* done_host) {
-  PULSE_REQUIRE(e && actions_host && obs_host && reward_host && done_host, "null argument");
+static int host_step_impl(PulsePokerHostEnv* e, const void* actions_host, int action_bytes, float* obs_host,
+                          float* reward_host, uint8_t* done_host, bool records_only) {
+  PULSE_REQUIRE(e && actions_host && done_host && (records_only || (obs_host && reward_host)), "null argument");
   PULSE_REQUIRE(action_bytes == 1 || action_bytes == 8, "action_bytes must be 1 (uint8) or 8 (int64)");
   PULSE_REQUIRE(!e->first, "reset first");
   HE_CUDA(cudaSetDevice(e->device));
@@ -457,8 +465,36 @@ int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int ac
     }
     return 0;
   };
-  return expand_chunks(e, true, obs_host, reward_host, done_host, false, submit);
+  return expand_chunks(e, true, obs_host, reward_host, done_host, false, submit, records_only);
 }
+
+int pulse_poker_host_step(PulsePokerHostEnv* e, const void* actions_host, int action_bytes, float* obs_host,
+                          float* reward_host, uint8_t* done_host) {
+  return host_step_impl(e, actions_host, action_bytes, obs_host, reward_host, done_host, false);
+}
+
+// The step without the float32 expansion: the packed records stay in the env's pinned buffer (pulse_poker_host_records),
+// only the done flags are written out.  For consumers that read the records directly (or expand rows on demand with
+// pulse_poker_wire_expand_host); the host then touches ~4x less memory per step.
+int pulse_poker_host_step_records(PulsePokerHostEnv* e, const void* actions_host, int action_bytes, uint8_t* done_host) {
+  return host_step_impl(e, actions_host, action_bytes, nullptr, nullptr, done_host, true);
+}
+
+// chunk c of the last call: its records (in table order), how many, and the table range the chunk covers; the tables
+// that have a record are the set bits of pulse_poker_host_live_mask() within that range (all of them after a reset)
+int pulse_poker_host_records(const PulsePokerHostEnv* e, int chunk, const uint32_t** rows, long long* n_rows,
+                             long long* first_table, long long* n_tables) {
+  PULSE_REQUIRE(e && chunk >= 0 && chunk < e->chunks, "bad chunk");
+  const long long first = (long long)chunk * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
+  if (rows) *rows = e->h_wire + (size_t)first * e->R;
+  if (n_rows) *n_rows = e->last_rows[chunk];
+  if (first_table) *first_table = first;
+  if (n_tables) *n_tables = last - first;
+  return PULSE_OK;
+}
+
+// bit b of word w: table 32 w + b was live when the last call began, i.e. it has a record in that call's output
+const uint32_t* pulse_poker_host_live_mask(const PulsePokerHostEnv* e) { return e ? e->prev_live.data() : nullptr; }
 
 int pulse_poker_host_info(const PulsePokerHostEnv* e, int* row_bytes, int* obs_width, int* chunks, int* threads,
                           long long* last_h2d_bytes, long long* last_d2h_bytes) {
@@ -501,7 +537,7 @@ int pulse_poker_wire_expand_host(const uint32_t* rows, long long n_rows, int max
   std::vector<uint32_t> prev(live.size(), 0u);
   a.rows = rows; a.off = nullptr; a.live = live.data(); a.prev_live = prev.data(); a.chunk_first = 0; a.g0 = 0; a.g1 = n_rows;
   a.row_words = R; a.obs_width = W; a.max_players = max_players;
-  a.obs = obs_out; a.reward = reward_out; a.done = done_out; a.fresh = true;
+  a.obs = obs_out; a.reward = reward_out; a.done = done_out; a.fresh = true; a.records_only = false;
   pulse_expand_range(a);
   return PULSE_OK;
 }
@@ -523,7 +559,7 @@ int pulse_poker_wire_expand_step_host(const uint32_t* rows, uint32_t* live_inout
   a.rows = rows; a.off = fresh ? nullptr : off.data(); a.live = live_inout; a.prev_live = prev_live_inout;
   a.chunk_first = 0; a.g0 = 0; a.g1 = n_tables;
   a.row_words = pkw_row_words(max_players); a.obs_width = 13 + 3 * (max_players - 1); a.max_players = max_players;
-  a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh != 0;
+  a.obs = obs; a.reward = reward; a.done = done; a.fresh = fresh != 0; a.records_only = false;
   pulse_expand_range(a);
   return PULSE_OK;
 }

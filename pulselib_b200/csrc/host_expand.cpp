@@ -21,7 +21,7 @@ inline void expand_row_portable(const uint32_t* w, int W, int R, float* o, float
 }
 
 __attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, int W, int R, float* o, float* reward,
-                                                            uint8_t* done, bool line_rows) {
+                                                            uint8_t* done, bool line_rows, bool stream16) {
   const __m256i keep = _mm256_setr_epi32(0xFFFF, 0xFFFF, 0xFFFF, 0xFFFF, 0x7FFF, 0xFFFF, 0xFFFF, 0xFFFF);  // column 12: status without the done bit
   const __m256 f0 = _mm256_cvtepi32_ps(_mm256_cvtepi8_epi32(_mm_loadl_epi64(reinterpret_cast<const __m128i*>(w))));
   const __m256 f1 = _mm256_cvtepi32_ps(_mm256_and_si256(
@@ -29,6 +29,12 @@ __attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, i
   if (line_rows) {           // heads-up, 32-byte aligned rows: the whole cache line, streamed
     _mm256_stream_ps(o, f0);
     _mm256_stream_ps(o + 8, f1);
+  } else if (stream16) {     // wider rows (W a multiple of 4, 16-byte aligned): streamed in 16-byte pieces
+    _mm_stream_ps(o, _mm256_castps256_ps128(f0)); _mm_stream_ps(o + 4, _mm256_extractf128_ps(f0, 1));
+    _mm_stream_ps(o + 8, _mm256_castps256_ps128(f1)); _mm_stream_ps(o + 12, _mm256_extractf128_ps(f1, 1));
+    const uint16_t* u = reinterpret_cast<const uint16_t*>(w + 2);
+    for (int p = 8; p < W - 8; p += 4)
+      _mm_stream_ps(o + 8 + p, _mm_cvtepi32_ps(_mm_cvtepu16_epi32(_mm_loadl_epi64(reinterpret_cast<const __m128i*>(u + p)))));
   } else {
     _mm256_storeu_ps(o, f0);
     _mm256_storeu_ps(o + 8, f1);
@@ -77,8 +83,9 @@ void expand_range_portable(const PulseExpandArgs& a) {
 
 __attribute__((target("avx2"))) void expand_range_avx2(const PulseExpandArgs& a) {
   const bool line_rows = a.obs_width == 16 && (reinterpret_cast<uintptr_t>(a.obs) & 31u) == 0;
-  EXPAND_BODY(expand_row_avx2(w, W, R, a.obs + g * W, a.reward + g, &d, line_rows))
-  if (line_rows) _mm_sfence();
+  const bool stream16 = !line_rows && (a.obs_width & 3) == 0 && (reinterpret_cast<uintptr_t>(a.obs) & 15u) == 0;
+  EXPAND_BODY(expand_row_avx2(w, W, R, a.obs + g * W, a.reward + g, &d, line_rows, stream16))
+  if (line_rows || stream16) _mm_sfence();
 }
 
 bool have_avx2() {
@@ -88,7 +95,32 @@ bool have_avx2() {
 
 }  // namespace
 
+// records-only mode: the done flag of every record (bit 15 of the status column) into the caller's done array and
+// the live mask; nothing is expanded
+void scan_range_records(const PulseExpandArgs& a) {
+  const int R = a.row_words;
+  for (long long wg = a.g0 >> 5; wg < ((a.g1 + 31) >> 5); ++wg) {
+    const long long gb = wg << 5;
+    const int cnt = (int)((a.g1 - gb) < 32 ? (a.g1 - gb) : 32);
+    const uint32_t in_range = cnt == 32 ? 0xFFFFFFFFu : ((1u << cnt) - 1u);
+    const uint32_t mask = a.fresh ? 0xFFFFFFFFu : a.live[wg];
+    size_t slot = a.off ? a.off[wg - (a.chunk_first >> 5)] : (size_t)(gb - a.chunk_first);
+    uint32_t next = 0, m = mask & in_range;
+    a.prev_live[wg] = mask;
+    while (m) {
+      const int b = __builtin_ctz(m);
+      m &= m - 1;
+      const uint8_t d = (uint8_t)((a.rows[slot * R + 4] >> 15) & 1u);
+      ++slot;
+      a.done[gb + b] = d;
+      next |= (uint32_t)(d ? 0u : 1u) << b;
+    }
+    a.live[wg] = next;
+  }
+}
+
 void pulse_expand_range(const PulseExpandArgs& a) {
+  if (a.records_only) { scan_range_records(a); return; }
   if (have_avx2()) expand_range_avx2(a);
   else expand_range_portable(a);
 }

@@ -12,6 +12,7 @@ struct PulseExpandArgs {
   int row_words, obs_width, max_players;
   float* obs; float* reward; uint8_t* done;
   bool fresh;               // after a deal: every table has a record
+  bool records_only;        // the caller keeps the packed records: only done flags and the live mask are maintained
 };
 
 // Expands the records of tables [g0, g1).  Picks an AVX2 body when the CPU has it (checked once), else portable code.

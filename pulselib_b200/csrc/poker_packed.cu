@@ -105,13 +105,6 @@ __device__ __forceinline__ void store_row16(float* dst, const float (&r)[16]) {
                "f"(r[11]), "f"(r[12]), "f"(r[13]), "f"(r[14]), "f"(r[15]) : "memory");
 }
 
-// AUTO == 3, tile-local redeal (an experiment kept selectable, NOT the default -- see pulse_poker_packed_step): tables
-// that were already finished when the step began are not stepped; once the tile's
-// 128 tables are done, the CTA's first warp deals them their next hands -- compacted (one lane per finished table, so
-// the ~1,500-instruction deal runs at the density of a separate pass) and in place: the tile's state sectors were just
-// read and written by the step phase and sit in L2, so the deal's scattered 4-byte stores merge there.  The separate
-// redeal pass (AUTO == 2) re-read a counter for every table and paid a DRAM read-modify-write per scattered store --
-// 410 MB of traffic per 4M-table step, most of its 85 us (profiles/r2b_autoreset_redeal_raw.csv).
 template <int MAXP, int MT, int MINB, bool POLICY = false, int AUTO = 0, bool DIRECT = false>
 __global__ void __launch_bounds__(kBlock, MINB)
 poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __restrict__ actions,
@@ -120,9 +113,6 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
                          int starting_bbs, int max_bbs, long long n, int l2_ahead,
                          PackedPolicy pol = PackedPolicy()) {
   extern __shared__ float4 smem4[];
-  __shared__ int rd_list[AUTO == 3 ? kBlock : 1];
-  __shared__ int rd_count;
-  __shared__ uint32_t rd_deck[AUTO == 3 ? 13 * 32 : 1];
   if (l2_ahead > 0)  // bit 30 of l2_ahead: include the hand-value words
     packed_prefetch_tile<MAXP>(S, actions, pr.AP, ((long long)blockIdx.x + (l2_ahead & 0xFFFFF)) * kBlock, n,
                                (l2_ahead >> 30) & 1);
@@ -131,57 +121,14 @@ poker_packed_step_kernel(PulsePokerPacked S, PokerParams pr, const int64_t* __re
   const int W = 13 + 3 * (pr.M - 1);
   for (long long base = (long long)blockIdx.x * kBlock; base < n; base += (long long)gridDim.x * kBlock) {
     const long long g = base + threadIdx.x;
-    if (AUTO == 3) {
-      if (threadIdx.x == 0) rd_count = 0;
-      __syncthreads();
-    }
     float row[WT];
-    bool marked = false;
-    if (g < n) {
-      PokerTable<MAXP> t;
-      const PackedStepResult r = packed_step_core<MAXP, POLICY, AUTO>(S, pr, actions, auto_reset, seed, env_base,
-                                                                      starting_bbs, max_bbs, g, n, &pol, t);
-      marked = AUTO == 3 && auto_reset && r.was_done;
-      if (!marked) {
-        reward_out[g] = r.reward;
-        done_out[g] = r.done;
-      }
-      if (!(marked && DIRECT)) pk_obs(t, pr, row);
-    }
+    if (g < n)
+      packed_step_one<MAXP, POLICY, AUTO>(S, pr, actions, row, reward_out, done_out, auto_reset, seed, env_base,
+                                          starting_bbs, max_bbs, g, n, &pol);
     if (DIRECT && MT == 2) {
-      if (g < n && !marked) store_row16(obs_out + g * 16, reinterpret_cast<const float(&)[16]>(row));
+      if (g < n) store_row16(obs_out + g * 16, reinterpret_cast<const float(&)[16]>(row));
     } else {
       stage_obs_rows<MT, WT>(row, smem4, obs_out, base, g, n, W);
-    }
-    if (AUTO == 3) {
-      const unsigned lane = threadIdx.x & 31u;
-      const unsigned bal = __ballot_sync(0xFFFFFFFFu, marked);
-      if (bal) {
-        int pos = 0;
-        if (lane == 0) pos = atomicAdd(&rd_count, __popc(bal));
-        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
-        if (marked) rd_list[pos + __popc(bal & ((1u << lane) - 1u))] = (int)threadIdx.x;
-      }
-      __syncthreads();
-      if (threadIdx.x < 32) {
-        const int cnt = rd_count;
-        PackedDeckShared dk{reinterpret_cast<uint8_t*>(rd_deck) + 4 * threadIdx.x, 4 * 32};
-        for (int i = threadIdx.x; i < cnt; i += 32) {
-          const long long g2 = base + rd_list[i];
-          float nrow[WT];
-          packed_reset_one<MAXP>(S, pr, nullptr, seed, env_base, S.hand_ctr[g2] + 1u, 0, 4, starting_bbs, max_bbs, nrow, g2, n, dk);
-          reward_out[g2] = 0.0f;
-          done_out[g2] = 0;
-          float* dst = obs_out + g2 * W;
-          if (DIRECT && MT == 2) {
-            store_row16(dst, reinterpret_cast<const float(&)[16]>(nrow));
-          } else if ((W & 3) == 0 && (reinterpret_cast<uintptr_t>(obs_out) & 15u) == 0) {
-            for (int c = 0; c < W; c += 4) *reinterpret_cast<float4*>(dst + c) = make_float4(nrow[c], nrow[c + 1], nrow[c + 2], nrow[c + 3]);
-          } else {
-            for (int c = 0; c < W; ++c) dst[c] = nrow[c];
-          }
-        }
-      }
     }
   }
 }
@@ -415,11 +362,10 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   // heads-up rows: direct 256-bit stores (PULSE_POKER_OBS_DIRECT=0 keeps the staged write-out, for A/B runs)
   static const bool direct_env = !(getenv("PULSE_POKER_OBS_DIRECT") && atoi(getenv("PULSE_POKER_OBS_DIRECT")) == 0);
   const bool direct = direct_env && (reinterpret_cast<uintptr_t>(obs_out) & 31u) == 0;
-  // auto_reset: finished tables are dealt by the compacting redeal pass that follows the step kernel.  Measured on
-  // B200 (profiles/r2e_bench_lines.jsonl): dealing them inside the step kernel tile by tile (PULSE_POKER_REDEAL_TILE=1,
-  // AUTO == 3) is 4-15% slower on every auto-reset workload -- the 128-table tile yields ~19 deals, two thirds of one
-  // warp, and the CTA waits for that warp -- so the separate pass stays the default.
-  static const bool redeal_pass = !(getenv("PULSE_POKER_REDEAL_TILE") && atoi(getenv("PULSE_POKER_REDEAL_TILE")) != 0);
+  // auto_reset: finished tables are dealt by the compacting redeal pass that follows the step kernel.  Dealing them
+  // inside the step kernel, tile by tile, was built and measured in round 2 (profiles/r2e_bench_lines.jsonl): 4-15%
+  // slower on every auto-reset workload -- a 128-table tile yields ~19 deals, two thirds of one warp, and the CTA waits
+  // for that warp -- and was removed again.
 #define PKP_STEP_A(MP, MT, MINB, AUTO, SMEM)                                                              \
   do {                                                                                                    \
     if ((MT) == 2 && direct)                                                                              \
@@ -433,8 +379,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
   } while (0)
 #define PKP_STEP_B(MP, MT, MINB, SMEM)                                  \
   do {                                                                  \
-    if (auto_reset && redeal_pass) PKP_STEP_A(MP, MT, MINB, 2, SMEM);   \
-    else if (auto_reset) PKP_STEP_A(MP, MT, MINB, 3, SMEM);             \
+    if (auto_reset) PKP_STEP_A(MP, MT, MINB, 2, SMEM);                  \
     else PKP_STEP_A(MP, MT, MINB, 0, SMEM);                             \
   } while (0)
   // resident CTAs per SM the step kernel is compiled for: 10 (48 registers) heads-up, 6 / 4 for the six- / ten-seat
@@ -475,7 +420,7 @@ int pulse_poker_packed_step(const PulsePokerPacked* st, const PulsePokerConfig* 
 #undef PKP_STEP_A
 #undef PKP_SMEM4
   rc = pulse_check_launch("pulse_poker_packed_step");
-  if (rc || !auto_reset || !redeal_pass) return rc;
+  if (rc || !auto_reset) return rc;
   return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
 }
 
@@ -507,7 +452,6 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
   static const bool direct_env = !(getenv("PULSE_POKER_OBS_DIRECT") && atoi(getenv("PULSE_POKER_OBS_DIRECT")) == 0);
   const bool direct = direct_env && (reinterpret_cast<uintptr_t>(obs_out) & 31u) == 0;
-  static const bool redeal_pass = !(getenv("PULSE_POKER_REDEAL_TILE") && atoi(getenv("PULSE_POKER_REDEAL_TILE")) != 0);
 #define PKP_POL_A(MP, MT, MINB, AUTO, SMEM)                                                                \
   do {                                                                                                     \
     if ((MT) == 2 && direct)                                                                               \
@@ -521,8 +465,7 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
   } while (0)
 #define PKP_POL(MP, MT, MINB, SMEM)                                     \
   do {                                                                  \
-    if (auto_reset && redeal_pass) PKP_POL_A(MP, MT, MINB, 2, SMEM);    \
-    else if (auto_reset) PKP_POL_A(MP, MT, MINB, 3, SMEM);              \
+    if (auto_reset) PKP_POL_A(MP, MT, MINB, 2, SMEM);                   \
     else PKP_POL_A(MP, MT, MINB, 0, SMEM);                              \
   } while (0)
 #define PKP_SMEM4(MT) ((size_t)kBlock * (((13 + 3 * ((MT) - 1)) / 4) | 1) * sizeof(float4))
@@ -542,7 +485,7 @@ int pulse_poker_packed_step_policy(const PulsePokerPacked* st, const PulsePokerC
 #undef PKP_POL_A
 #undef PKP_SMEM4
   rc = pulse_check_launch("pulse_poker_packed_step_policy");
-  if (rc || !auto_reset || !redeal_pass) return rc;
+  if (rc || !auto_reset) return rc;
   return launch_redeal(st, cfg, pr, seed, env_base, obs_out, stream);
 }
 

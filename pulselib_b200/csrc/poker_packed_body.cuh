@@ -353,8 +353,7 @@ struct PackedPolicy {
 // already done when the step began is dealt a new hand instead (engine extension):
 // the action is ignored, reward 0, done 0 and the observation is the new hand's first one.
 // AUTO: what a table that was already done when the step began does -- 0 nothing (stays done), 1 deal inline
-// (host emulation of the semantics), 2 mark for the separate redeal pass, 3 leave it to the step kernel's own
-// tile-local redeal phase (device default).  A compile-time choice so the plain
+// (host emulation of the semantics), 2 mark for the redeal pass that follows on the same stream (device).  A compile-time choice so the plain
 // step kernel carries no shuffle / evaluator code at all.
 // Result of packed_step_core: what the step did to one table, for the caller to write out (float32 observation row
 // + reward + done arrays, or one compact wire row).
@@ -393,8 +392,6 @@ PULSE_HD PackedStepResult packed_step_core(const PulsePokerPacked& S, const Poke
     if (pol->chosen) pol->chosen[g] = a;
     if (pol->seat_before) pol->seat_before[g] = t.idx;
   }
-  if (AUTO == 3 && auto_reset && t.done)   // device path, tile-local redeal: the kernel deals this table after the tile's
-    return PackedStepResult{0.0f, true, false};   // steps (poker_packed.cu); nothing is written here
   if (AUTO == 2 && auto_reset && t.done) {
     // device path: the deal is left to the redeal pass that follows the step kernel on the same stream
     // (poker_packed.cu).  Dealing here would put the shuffle and 3 x AP hand evaluations into the step

@@ -44,9 +44,11 @@ class PokerHostEnv:
         self.rewards = _aligned((self.n_games,), np.float32)
         self.dones = _aligned((self.n_games,), np.uint8)
 
-    def reset(self, active_players=None, rotation=0):
+    def reset(self, active_players=None, rotation=0, expand=True):
+        """expand=False: records only (for step_records() consumers): self.obs is not written"""
         ap = self.n_players if active_players is None else int(active_players)
-        _lib.check(self._lib.pulse_poker_host_reset(self._h, C.c_int(ap), C.c_int(int(rotation)), _p(self.obs),
+        _lib.check(self._lib.pulse_poker_host_reset(self._h, C.c_int(ap), C.c_int(int(rotation)),
+                                                    _p(self.obs) if expand else C.c_void_p(0),
                                                     _p(self.rewards), _p(self.dones)), "pulse_poker_host_reset")
         self.active_players = ap
         return self.obs, {"active_players": ap}
@@ -60,6 +62,39 @@ class PokerHostEnv:
         _lib.check(self._lib.pulse_poker_host_step(self._h, _p(a), C.c_int(a.dtype.itemsize), _p(self.obs), _p(self.rewards),
                                                    _p(self.dones)), "pulse_poker_host_step")
         return self.obs, self.rewards, self.dones.view(np.bool_), False, {"active_players": self.active_players}
+
+    def step_records(self, actions):
+        """step() without the float32 expansion (pulse_poker_host_step_records): only `self.dones` is updated; the step's
+        packed records stay in the env's pinned buffer -- see records() / live_mask().  Do not mix with step() between
+        resets."""
+        a = np.ascontiguousarray(actions)
+        if a.dtype not in (np.uint8, np.int64):
+            a = a.astype(np.int64)
+        if a.shape != (self.n_games,):
+            raise ValueError(f"actions must have shape {(self.n_games,)}, got {a.shape}")
+        _lib.check(self._lib.pulse_poker_host_step_records(self._h, _p(a), C.c_int(a.dtype.itemsize), _p(self.dones)),
+                   "pulse_poker_host_step_records")
+        return self.dones.view(np.bool_)
+
+    def records(self):
+        """[(first_table, n_tables, rows uint32 [n_rows, words])] per chunk of the last call: zero-copy views of the pinned
+        record buffer, valid until the next call.  Rows are in table order; a table has one iff its live_mask() bit is set."""
+        words = self.info()["row_bytes"] // 4
+        out = []
+        for c in range(self.info()["chunks"]):
+            rows, n, first, cnt = C.POINTER(C.c_uint32)(), C.c_longlong(), C.c_longlong(), C.c_longlong()
+            _lib.check(self._lib.pulse_poker_host_records(self._h, C.c_int(c), C.byref(rows), C.byref(n), C.byref(first),
+                                                          C.byref(cnt)), "pulse_poker_host_records")
+            view = np.ctypeslib.as_array(rows, shape=(max(n.value, 1), words))[: n.value]
+            out.append((first.value, cnt.value, view))
+        return out
+
+    def live_mask(self) -> np.ndarray:
+        """bool [N]: the table was live when the last call began (= it has a record in that call's output)"""
+        self._lib.pulse_poker_host_live_mask.restype = C.POINTER(C.c_uint32)
+        p = self._lib.pulse_poker_host_live_mask(self._h)
+        words = np.ctypeslib.as_array(p, shape=((self.n_games + 31) // 32,))
+        return np.unpackbits(words.view(np.uint8), bitorder="little")[: self.n_games].astype(bool)
 
     def info(self) -> dict:
         v = [C.c_int() for _ in range(4)] + [C.c_longlong(), C.c_longlong()]

@@ -83,3 +83,37 @@ def test_host_env_refuses_unrepresentable_configs(cuda_device):
         PokerHostEnv(cuda_device, n_players=10, max_players=10, n_games=64, max_bbs=7000)   # 70,000 chips do not fit 16 bits
     with pytest.raises(_lib.PulseError):
         PokerHostEnv(cuda_device, n_players=3, max_players=10, n_games=64)                  # shape outside the specialised set
+
+
+@pytest.mark.parametrize("P,M,N,chunks", [(2, 2, 70_001, 3), (6, 6, 9_999, 2)])
+def test_records_mode_matches_float32_engine(P, M, N, chunks, cuda_device):
+    """pulse_poker_host_step_records: the packed records the env leaves in pinned memory, decoded row by row with the
+    library's own expander and scattered by the live mask, must rebuild exactly what the float32 engine returns."""
+    import torch
+
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+    from pulselib_b200.host_env import PokerHostEnv, expand_rows
+
+    henv = PokerHostEnv(cuda_device, n_players=P, max_players=M, n_games=N, seed=8, env_base=17, chunks=chunks, threads=3, **CFG)
+    denv = PokerGPUPacked(cuda_device, n_players=P, max_players=M, n_games=N, seed=8, env_base=17, **CFG)
+    rng = np.random.default_rng(N)
+    for hand in range(2):
+        obs = henv.reset()[0].copy()
+        rew = np.zeros(N, np.float32)
+        np.testing.assert_array_equal(obs, denv.reset()[0].cpu().numpy())
+        for t in range(18):
+            a = rng.integers(0, 13, N)
+            dones = henv.step_records(a.astype(np.uint8)).copy()
+            live = henv.live_mask()
+            rew[:] = 0
+            for first, cnt, rows in henv.records():
+                idx = first + np.flatnonzero(live[first:first + cnt])
+                assert len(idx) == len(rows)
+                o, r, d = expand_rows(np.array(rows), M)
+                obs[idx], rew[idx] = o, r
+                np.testing.assert_array_equal(d.astype(bool), dones[idx])
+            o2, r2, d2, _, _ = denv.step(torch.from_numpy(a).to(cuda_device))
+            np.testing.assert_array_equal(obs, o2.cpu().numpy(), err_msg=f"hand {hand} step {t}")
+            np.testing.assert_array_equal(rew.view(np.uint32), r2.cpu().numpy().view(np.uint32))
+            np.testing.assert_array_equal(dones, d2.cpu().numpy())
+    henv.close()
