@@ -423,6 +423,21 @@ int pulse_replay_append(const float* state, const float* next_state, int obs_wid
                         int64_t* action_buf, float* reward_buf, uint8_t* done_buf, long long capacity,
                         uint64_t* total_inout, uint64_t* appended_out, void* scratch, long long n_games,
                         pulse_stream_t stream);
+/* pulse_replay_append with no allocation anywhere -- no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and results as pulse_replay_append minus `scratch`: the scratch is a
+ * file-scope device array of the library (65,792 B per GPU that loads the library, held until exit), so the entry
+ * point calls no cudaMalloc / cudaFree / allocating library routine.  Limit: n_games <= pulse_replay_static_max_games()
+ * = 4,194,304 tables per call; larger batches are refused with PULSE_EINVAL and a message in pulse_last_error().
+ * All calls on one device share the array and nothing in it needs clearing between calls, but two calls that overlap
+ * on the GPU (different streams without a dependency) race: keep them on one stream or order them with events. */
+long long pulse_replay_static_max_games(void);
+int pulse_replay_append_static(const float* state, const float* next_state, int obs_width, const int64_t* actions,
+                               const float* rewards, const uint8_t* dones, const int32_t* seat_idx_before,
+                               const uint8_t* terminated_before_or_null, int q_seat, float* state_buf,
+                               float* next_state_buf, int64_t* action_buf, float* reward_buf, uint8_t* done_buf,
+                               long long capacity, uint64_t* total_inout, uint64_t* appended_out, long long n_games,
+                               pulse_stream_t stream);
 
 #ifdef __cplusplus
 }

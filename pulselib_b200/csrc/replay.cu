@@ -12,6 +12,8 @@
 // Bytes: 2 reads of 1-4 B per table to select, then 2 x (W x 4 B read + write) + 13 B per selected table.
 #include "common.cuh"
 
+#include <atomic>
+
 namespace {
 constexpr int kBlock = 256;
 
@@ -169,4 +171,65 @@ extern "C" int pulse_replay_append(const float* state, const float* next_state, 
   if (vec) RP_WRITE(true); else RP_WRITE(false);
 #undef RP_WRITE
   return pulse_check_launch("pulse_replay_append");
+}
+
+// ---- pulse_replay_append_static: the same append with NO allocation anywhere ------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it): the scratch of the three launches above lives in a file-scope device array instead of caller memory.  It has no
+// counterpart in the reference.
+//   * limit: n_games <= 4,194,304 (the bench's per-GPU batch); the array is 65,792 B and every GPU that loads the
+//     library holds it until the process exits;
+//   * every call on a device shares the array: calls that overlap on the GPU (different streams, no dependency) race.
+//     Nothing in it has to start at zero -- the count kernel writes counts[0 .. nb) and the scan kernel writes the base
+//     word before anything reads them -- so the last call's contents are simply overwritten;
+//   * in host code `g_replay_static_scratch` is a host-side stand-in, not a device address: the address the kernels
+//     get comes from cudaGetSymbolAddress, resolved once per device with that device current.
+namespace {
+constexpr long long kStaticMaxGames = 4194304;
+constexpr size_t kStaticScratchBytes = (size_t)(kStaticMaxGames / kBlock) * 4 + 256;   // counts + the base word, padded
+static __device__ __align__(256) unsigned char g_replay_static_scratch[kStaticScratchBytes];
+constexpr int kStaticMaxDevices = 64;
+std::atomic<void*> g_static_scratch_ptr[kStaticMaxDevices];   // zero-initialised: not resolved yet
+
+int replay_static_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { pulse_set_error("pulse_replay_append_static: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+  if (dev < 0 || dev >= kStaticMaxDevices) { pulse_set_error("pulse_replay_append_static: device ordinal %d out of range", dev); return PULSE_EINVAL; }
+  void* p = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(&p, g_replay_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      pulse_set_error("pulse_replay_append_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : PULSE_EINVAL;
+    }
+    g_static_scratch_ptr[dev].store(p, std::memory_order_release);   // two threads racing here store the same address
+  }
+  *out = p;
+  return PULSE_OK;
+}
+}  // namespace
+
+extern "C" long long pulse_replay_static_max_games(void) { return kStaticMaxGames; }
+
+extern "C" int pulse_replay_append_static(const float* state, const float* next_state, int obs_width,
+                                          const int64_t* actions, const float* rewards, const uint8_t* dones,
+                                          const int32_t* seat_idx_before, const uint8_t* terminated_before_or_null,
+                                          int q_seat, float* state_buf, float* next_state_buf, int64_t* action_buf,
+                                          float* reward_buf, uint8_t* done_buf, long long capacity,
+                                          uint64_t* total_inout, uint64_t* appended_out, long long n_games,
+                                          cudaStream_t stream) {
+  PULSE_REQUIRE(n_games >= 0, "bad sizes");
+  if (n_games > kStaticMaxGames) {
+    pulse_set_error("pulse_replay_append_static: n_games = %lld exceeds the static scratch's limit of %lld tables per call; "
+                    "use pulse_replay_append with caller scratch", n_games, kStaticMaxGames);
+    return PULSE_EINVAL;
+  }
+  static_assert(kStaticScratchBytes >= (size_t)(kStaticMaxGames / kBlock) * 4 + 32, "scratch holds counts + base");
+  void* scratch = nullptr;
+  const int rc = replay_static_scratch(&scratch);
+  if (rc != PULSE_OK) return rc;
+  return pulse_replay_append(state, next_state, obs_width, actions, rewards, dones, seat_idx_before,
+                             terminated_before_or_null, q_seat, state_buf, next_state_buf, action_buf, reward_buf,
+                             done_buf, capacity, total_inout, appended_out, scratch, n_games, stream);
 }
