@@ -306,6 +306,18 @@ int pulse_poker_packed_rollout(const PulsePokerPacked* st, const PulsePokerConfi
  * hands = 0.5.  An optional input for a caller's reward; the step's own reward keeps the reference's proxy. */
 int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,
                                            pulse_stream_t stream);
+/* Showdown equity (second half; no reference behaviour -- rl/depth_notes.txt:316-321 asks for equity
+ * "using ALL players card info" and calls it out of reach).  equity_out float32 [N, active_players]: the share of the
+ * pot each contender (status ACTIVE or ALLIN) wins at showdown, averaged over every completion of the board from the
+ * cards in nobody's hand and not on the visible board (folded seats' cards are dead); ties split; folded / sitting-out
+ * seats get 0; a sole contender gets 1.  River and settled hands: the one board; turn and flop: exact enumeration;
+ * preflop: preflop_samples (1..65536) boards drawn from the chance tape at (seed, env_base + table, counter, stream 8).
+ * Shares are integer counts, so the result is independent of launch shape and bit-identical to oracle/oracle_core.c::
+ * oracle_showdown_equity.  Rows of a table with at least one contender sum to 1 (within float rounding).  Reads the
+ * packed state only. */
+int pulse_poker_packed_showdown_equity(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* equity_out,
+                                       int preflop_samples, uint64_t seed, uint64_t env_base, uint32_t counter,
+                                       pulse_stream_t stream);
 /* packed -> reference-shaped tensors.  Writes every field of `compat` whose pointer is non-NULL except decks
  * (a pure function of the deal, see pulse_poker_unpack_full) and prev_invested.  sb / bb follow from button and
  * active_players (PokerGPU.py:123-128); equities / equity_dirty are the reference's cache as it stands after the

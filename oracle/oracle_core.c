@@ -238,3 +238,116 @@ void oracle_enumerated_strength_batch(const int32_t* stages, const int32_t* hand
       out[g * ap + s] = oracle_enumerated_strength(stages[g], hands[(g * P + s) * 2], hands[(g * P + s) * 2 + 1],
                                                    board + g * 5);
 }
+
+/* Showdown equity (second half) -- no reference code computes it (its notes ask for equity "using ALL
+ * players card info" and call it out of reach, /root/reference/rl/depth_notes.txt:316-321); this restates the DEFINITION
+ * in include/pulse_envs.h (pulse_poker_packed_showdown_equity) from the reference-shaped arrays: for every completion of
+ * the board from the cards in nobody's hand and not on the visible board, the contenders (status 0 ACTIVE or 2 ALLIN,
+ * PokerGPU.py:11) compare seven-card values as the reference's showdown does (table walk, :437-444, when `hr` is given;
+ * the brute-force evaluator above otherwise) and the best share one pot unit.  Flop / turn / river exact; preflop
+ * `samples` boards, board q a forward Fisher-Yates over the unseen cards in (suit, rank) order driven by tape block
+ * (seed, env_id, stream 8 | q << 4, counter): first two picks from word 0 (one draw in [0, m (m - 1))), then words 1..3. */
+static int eq_value7(const int32_t* hr, const int32_t* c7) {
+  return hr ? oracle_handranks_walk(hr, c7, 7) : oracle_eval_bruteforce(c7, 7);
+}
+static void eq_score(const int32_t* hr, const int32_t* hands, const int* contender, int ap, const int32_t* b5,
+                     long long* num) {
+  int val[10], best = -1, k = 0;
+  for (int s = 0; s < ap; ++s) {
+    if (!contender[s]) continue;
+    int32_t c7[7] = {hands[2 * s], hands[2 * s + 1], b5[0], b5[1], b5[2], b5[3], b5[4]};
+    val[s] = eq_value7(hr, c7);
+    if (val[s] > best) best = val[s];
+  }
+  for (int s = 0; s < ap; ++s) if (contender[s] && val[s] == best) ++k;
+  for (int s = 0; s < ap; ++s) if (contender[s] && val[s] == best) num[s] += 2520 / k;
+}
+static int eq_cmp_suit_rank(const void* a, const void* b) {
+  int x = *(const int32_t*)a - 1, y = *(const int32_t*)b - 1;
+  return ((x & 3) * 16 + (x >> 2)) - ((y & 3) * 16 + (y >> 2));
+}
+void oracle_showdown_equity(const int32_t* hr, const int32_t* hands, const int32_t* status, const int32_t* board, int ap,
+                            int samples, uint64_t seed, uint64_t env_id, uint32_t counter, float* out) {
+  char used[53] = {0};
+  int contender[10], nc = 0;
+  long long num[10] = {0}, boards = 0;
+  for (int s = 0; s < ap; ++s) {
+    used[hands[2 * s]] = used[hands[2 * s + 1]] = 1;
+    contender[s] = status[s] == 0 || status[s] == 2;
+    nc += contender[s];
+  }
+  int32_t b5[5];
+  int vis = 0;
+  for (int i = 0; i < 5; ++i) if (board[i] >= 1) { b5[vis++] = board[i]; used[board[i]] = 1; }
+  int32_t unseen[52];
+  int m = 0;
+  for (int c = 1; c <= 52; ++c) if (!used[c]) unseen[m++] = c;
+  qsort(unseen, m, sizeof(int32_t), eq_cmp_suit_rank);
+  if (nc == 0) { for (int s = 0; s < ap; ++s) out[s] = 0.0f; return; }
+  if (vis == 5) { eq_score(hr, hands, contender, ap, b5, num); boards = 1; }
+  else if (vis == 4) {
+    for (int i = 0; i < m; ++i) { b5[4] = unseen[i]; eq_score(hr, hands, contender, ap, b5, num); ++boards; }
+  } else if (vis == 3) {
+    for (int i = 0; i < m; ++i)
+      for (int j = i + 1; j < m; ++j) { b5[3] = unseen[i]; b5[4] = unseen[j]; eq_score(hr, hands, contender, ap, b5, num); ++boards; }
+  } else if (vis == 0) {
+    for (int q = 0; q < samples; ++q) {
+      uint32_t w[4];
+      int32_t list[52];
+      oracle_tape(seed, env_id, 8u | ((uint32_t)q << 4), counter, w);
+      memcpy(list, unseen, sizeof(int32_t) * m);
+      uint32_t a = (uint32_t)(((uint64_t)w[0] * (uint64_t)(m * (m - 1))) >> 32);
+      int pick[5] = {(int)(a / (uint32_t)(m - 1)), 1 + (int)(a % (uint32_t)(m - 1)),
+                     2 + (int)(((uint64_t)w[1] * (uint64_t)(m - 2)) >> 32), 3 + (int)(((uint64_t)w[2] * (uint64_t)(m - 3)) >> 32),
+                     4 + (int)(((uint64_t)w[3] * (uint64_t)(m - 4)) >> 32)};
+      for (int k = 0; k < 5; ++k) { int32_t x = list[pick[k]]; list[pick[k]] = list[k]; list[k] = x; b5[k] = x; }
+      eq_score(hr, hands, contender, ap, b5, num);
+      ++boards;
+    }
+  }
+  for (int s = 0; s < ap; ++s) out[s] = boards ? (float)((double)num[s] / ((double)boards * 2520.0)) : 0.0f;
+}
+
+/* out [n, ap]; hands [n, P, 2], status [n, P], board [n, 5] (-1 = not dealt yet), reference-shaped int32 */
+void oracle_showdown_equity_batch(const int32_t* hr, const int32_t* hands, const int32_t* status, const int32_t* board,
+                                  int P, int ap, long long n, int samples, uint64_t seed, uint64_t env_base,
+                                  uint32_t counter, float* out) {
+  init_keys();
+#pragma omp parallel for schedule(dynamic, 4)
+  for (long long g = 0; g < n; ++g)
+    oracle_showdown_equity(hr, hands + g * P * 2, status + g * P, board + g * 5, ap, samples, seed,
+                           env_base + (uint64_t)g, counter, out + g * ap);
+}
+
+/* Exact preflop showdown equity of ONE table by full enumeration of C(m, 5) boards (heads-up: 1,712,304) -- the
+ * yardstick the sampled preflop value is checked against.  Needs the HandRanks table. */
+void oracle_showdown_equity_preflop_exact(const int32_t* hr, const int32_t* hands, const int32_t* status, int ap,
+                                          double* out) {
+  char used[53] = {0};
+  int contender[10];
+  for (int s = 0; s < ap; ++s) {
+    used[hands[2 * s]] = used[hands[2 * s + 1]] = 1;
+    contender[s] = status[s] == 0 || status[s] == 2;
+  }
+  int32_t u[52];
+  int m = 0;
+  for (int c = 1; c <= 52; ++c) if (!used[c]) u[m++] = c;
+  long long tot[10] = {0}, boards = 0;
+#pragma omp parallel
+  {
+    long long num[10] = {0}, nb = 0;
+#pragma omp for schedule(dynamic, 1)
+    for (int a = 0; a < m; ++a)
+      for (int b = a + 1; b < m; ++b)
+        for (int c = b + 1; c < m; ++c)
+          for (int d = c + 1; d < m; ++d)
+            for (int e = d + 1; e < m; ++e) {
+              int32_t b5[5] = {u[a], u[b], u[c], u[d], u[e]};
+              eq_score(hr, hands, contender, ap, b5, num);
+              ++nb;
+            }
+#pragma omp critical
+    { for (int s = 0; s < ap; ++s) tot[s] += num[s]; boards += nb; }
+  }
+  for (int s = 0; s < ap; ++s) out[s] = (double)tot[s] / ((double)boards * 2520.0);
+}

@@ -152,6 +152,31 @@ def enumerated_strength(stages, hands, board, active_players):
     return out
 
 
+def showdown_equity(hands, status, board, active_players, samples=256, seed=0, env_base=0, counter=0, hand_ranks=None):
+    """oracle_showdown_equity_batch: all-in equity of every seat with all hole cards known, [n, ap] float32.
+    hands [n, P, 2], status [n, P], board [n, 5] (-1 = not dealt yet); hand_ranks: the HandRanks table (the reference's
+    own showdown evaluation, a table walk) or None for the brute-force evaluator."""
+    h = np.ascontiguousarray(hands, dtype=np.int32)
+    st = np.ascontiguousarray(status, dtype=np.int32)
+    b = np.ascontiguousarray(board, dtype=np.int32)
+    hr = None if hand_ranks is None else np.ascontiguousarray(hand_ranks, dtype=np.int32)
+    out = np.zeros((h.shape[0], int(active_players)), np.float32)
+    lib().oracle_showdown_equity_batch(p(hr), p(h), p(st), p(b), C.c_int(h.shape[1]), C.c_int(int(active_players)),
+                                       C.c_longlong(h.shape[0]), C.c_int(int(samples)), C.c_uint64(seed),
+                                       C.c_uint64(env_base), C.c_uint32(counter), p(out))
+    return out
+
+
+def showdown_equity_preflop_exact(hands, status, hand_ranks):
+    """Full enumeration of C(52 - 2 ap, 5) boards for ONE table (hands [ap, 2], status [ap]) -> float64 [ap]."""
+    h = np.ascontiguousarray(hands, dtype=np.int32)
+    st = np.ascontiguousarray(status, dtype=np.int32)
+    hr = np.ascontiguousarray(hand_ranks, dtype=np.int32)
+    out = np.zeros(h.shape[0], np.float64)
+    lib().oracle_showdown_equity_preflop_exact(p(hr), p(h), p(st), C.c_int(h.shape[0]), p(out))
+    return out
+
+
 def hand_stats_update(vec, q_stacks, initial, stages, button, done, terminated, q_seat, active_players):
     """Numpy restatement of one step of the reference's hand bookkeeping
     (/root/reference/scripts/Poker/trainGPU_performance.py:186-206 + utils/performance.py:55-59, :170-174) folded into

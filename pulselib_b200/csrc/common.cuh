@@ -20,6 +20,7 @@
 #define PULSE_STREAM_BJ_DECK 5u
 #define PULSE_STREAM_P2D_INIT 6u
 #define PULSE_STREAM_TETRIS_PIECE 7u
+#define PULSE_STREAM_EQUITY 8u   // | sample index << 4 (poker_packed_body.cuh, showdown equity)
 
 void pulse_set_error(const char* fmt, ...);
 int pulse_check_launch(const char* what);

@@ -268,6 +268,36 @@ poker_packed_strength_kernel(PulsePokerPacked S, int AP, float* __restrict__ out
   }
 }
 
+// Showdown equity: one WARP per table -- tables of a batch sit on different streets (1 to 1,081 boards each), so
+// lanes split a table's boards instead of tables splitting a warp.  Every lane loads the table (same addresses: one
+// transaction per warp), scores its boards, and the per-seat integer sums are added across the warp.
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock)
+poker_packed_showdown_equity_kernel(PulsePokerPacked S, PokerParams pr, int samples, uint64_t seed, uint64_t env_base,
+                                    uint32_t counter, float* __restrict__ out, long long n) {
+  const int lane = threadIdx.x & 31;
+  const long long nw = ((long long)gridDim.x * kBlock) >> 5;
+  for (long long g = ((long long)blockIdx.x * kBlock + threadIdx.x) >> 5; g < n; g += nw) {
+    PokerTable<MAXP> t;
+    uint32_t fb;
+    packed_load(t, fb, S, g, n, pr.AP);
+    int32_t num[MAXP];
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) num[s] = 0;
+    const int boards = packed_showdown_equity_part<MAXP>(t, pr.AP, samples, seed, env_base + (uint64_t)g, counter, lane,
+                                                         32, num);
+    float mine = 0.0f;
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) {
+      int v = num[s];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+      if (lane == s) mine = pkq_equity((int64_t)v, boards);
+    }
+    if (lane < pr.AP) out[g * pr.AP + lane] = mine;
+  }
+}
+
 int check_cfg(const void* st, const PulsePokerConfig* cfg) {
   if (!st || !cfg) { pulse_set_error("null state/config"); return PULSE_EINVAL; }
   if (cfg->n_players < 2 || cfg->n_players > 10) { pulse_set_error("n_players must be in 2..10"); return PULSE_EINVAL; }
@@ -514,6 +544,21 @@ int pulse_poker_packed_rollout(const PulsePokerPacked* st, const PulsePokerConfi
                          *st, pr, pol, n_steps, auto_reset, seed, env_base, cfg->starting_bbs, cfg->max_bbs,
                          (long long)cfg->n_games, obs_final_or_null, reward_out, done_out, actions_out_or_null)));
   return pulse_check_launch("pulse_poker_packed_rollout");
+}
+
+int pulse_poker_packed_showdown_equity(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* equity_out,
+                                       int preflop_samples, uint64_t seed, uint64_t env_base, uint32_t counter,
+                                       cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  PULSE_REQUIRE(preflop_samples >= 1 && preflop_samples <= PKQ_MAX_SAMPLES, "preflop_samples must be in 1..65536");
+  if (cfg->n_games == 0) return PULSE_OK;
+  PULSE_REQUIRE(equity_out != nullptr, "equity_out is null");
+  PokerParams pr = make_params(cfg);
+  const int grid = pulse_grid_for((long long)cfg->n_games * 32, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_showdown_equity_kernel<MP><<<grid, kBlock, 0, stream>>>(
+                         *st, pr, preflop_samples, seed, env_base, counter, equity_out, (long long)cfg->n_games)));
+  return pulse_check_launch("pulse_poker_packed_showdown_equity");
 }
 
 int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,

@@ -532,6 +532,120 @@ PULSE_HD float packed_enumerated_strength(int stage, int h0, int h1, uint32_t fb
   return PULSE_FDIV((float)sum, PULSE_FMUL((float)count, 32765.0f));
 }
 
+// ---- showdown equity (second half) -------------------------------------------------------
+// What the reference's notes ask for and call out of reach: equity "using ALL players card info (not just 100%
+// accuracy with current players hand)" (/root/reference/rl/depth_notes.txt:316-321).  The env knows every seat's hole
+// cards, so this is the all-in equity of the table as it stands: over every completion of the board from the cards
+// that are in nobody's hand (folded seats' cards are dead) and not on the visible board, the share of the pot a
+// contender (status ACTIVE or ALLIN) would win at showdown -- 1 for a sole best seven-card value, 1/k in a k-way
+// tie, by the same evaluator values the settlement compares (poker_core.cuh::pk_showdown).
+//   river / settled hand: the one board;  turn: every river card (52 - 2 AP - 4 boards);  flop: every turn/river
+//   pair (heads-up C(45,2) = 990, ten seats C(29,2) = 406);  preflop: C(52 - 2 AP, 5) is 1.7 M boards heads-up, so
+//   `samples` boards are drawn instead, board q from one block of the chance tape at (seed, table id, counter,
+//   stream PULSE_STREAM_EQUITY | q << 4): a forward Fisher-Yates over the unseen cards in (suit, rank) order.
+// Shares are summed as integers in units of 1/2520 (lcm of 1..10), so the result does not depend on how the boards
+// are split over lanes: equity = float(double(sum) / (double(boards) * 2520)).  Folded / sitting-out seats: 0.
+constexpr int PKQ_UNIT = 2520;
+constexpr int PKQ_MAX_SAMPLES = 65536;
+
+template <int MAXP>
+PULSE_HD void pkq_score(const uint64_t (&hole)[MAXP], uint32_t contenders, uint64_t board, int32_t (&num)[MAXP]) {
+  int best = -1;
+  uint32_t win = 0;
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {
+    if ((contenders >> s) & 1u) {
+      const int v = pe_eval_mask64(hole[s] | board);
+      if (v > best) { best = v; win = 1u << s; }
+      else if (v == best) win |= 1u << s;
+    }
+  }
+  const int k = PULSE_POPC(win);
+  const int share = PKQ_UNIT / (k > 0 ? k : 1);
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) num[s] += ((win >> s) & 1u) ? share : 0;
+}
+
+// Adds to num[] the shares of the boards with index == lane (mod nl); returns the number of boards of ALL lanes.
+template <int MAXP>
+PULSE_HD int packed_showdown_equity_part(const PokerTable<MAXP>& t, int AP, int samples, uint64_t seed, uint64_t env_id,
+                                         uint32_t counter, int lane, int nl, int32_t (&num)[MAXP]) {
+  uint64_t hole[MAXP];
+  uint64_t dead = 0;
+  uint32_t contenders = 0;
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {
+    hole[s] = 0;
+    if (s < AP) {
+      hole[s] = pe_add_card64(t.hole1[s], pe_add_card64(t.hole0[s], 0));
+      dead |= hole[s];
+      const int st = pk_status(t.st, s);
+      if (st == PK_ACTIVE || st == PK_ALLIN) contenders |= 1u << s;
+    }
+  }
+  uint64_t board = 0;
+  int vis = 0;
+#pragma unroll
+  for (int i = 0; i < 5; ++i)
+    if (t.board[i] >= 1) { board = pe_add_card64(t.board[i], board); ++vis; }
+  dead |= board;
+  if (PULSE_POPC(contenders) <= 1) {            // everybody else folded: every board is his
+    if (lane == 0) {
+#pragma unroll
+      for (int s = 0; s < MAXP; ++s) num[s] += ((contenders >> s) & 1u) ? PKQ_UNIT : 0;
+    }
+    return 1;
+  }
+  if (vis == 5) {
+    if (lane == 0) pkq_score<MAXP>(hole, contenders, board, num);
+    return 1;
+  }
+  uint8_t pos[52];                              // bit positions (16 suit + rank) of the unseen cards, ascending
+  int m = 0;
+  for (int b = 0; b < 64; ++b)
+    if ((b & 15) < 13 && !((dead >> b) & 1ull)) pos[m++] = (uint8_t)b;
+  if (vis == 4) {
+    for (int i = lane; i < m; i += nl) pkq_score<MAXP>(hole, contenders, board | (1ull << pos[i]), num);
+    return m;
+  }
+  if (vis == 3) {
+    // pair (i, j), i < j, in row-major order; row i holds m - 1 - i pairs; this lane owns every nl-th pair
+    int i = 0, r = lane;
+    while (i < m - 1 && r >= m - 1 - i) { r -= m - 1 - i; ++i; }
+    while (i < m - 1) {
+      pkq_score<MAXP>(hole, contenders, board | (1ull << pos[i]) | (1ull << pos[i + 1 + r]), num);
+      r += nl;
+      while (i < m - 1 && r >= m - 1 - i) { r -= m - 1 - i; ++i; }
+    }
+    return m * (m - 1) / 2;
+  }
+  // preflop (vis == 0): sampled boards
+  for (int q = lane; q < samples; q += nl) {
+    const PulseU4 w = pulse_tape(seed, env_id, PULSE_STREAM_EQUITY | ((uint32_t)q << 4), counter);
+    const uint32_t a = pulse_mulhi32(w.x, (uint32_t)(m * (m - 1)));
+    int pick[5];
+    pick[0] = (int)(a / (uint32_t)(m - 1));
+    pick[1] = 1 + (int)(a % (uint32_t)(m - 1));
+    pick[2] = 2 + (int)pulse_mulhi32(w.y, (uint32_t)(m - 2));
+    pick[3] = 3 + (int)pulse_mulhi32(w.z, (uint32_t)(m - 3));
+    pick[4] = 4 + (int)pulse_mulhi32(w.w, (uint32_t)(m - 4));
+    uint64_t bd = 0;
+    for (int k = 0; k < 5; ++k) {               // forward Fisher-Yates: slot k takes the card at slot pick[k] >= k
+      const uint8_t x = pos[pick[k]]; pos[pick[k]] = pos[k]; pos[k] = x;
+      bd |= 1ull << x;
+    }
+    pkq_score<MAXP>(hole, contenders, bd, num);
+    for (int k = 4; k >= 0; --k) {              // undo, so the next sample starts from the sorted list again
+      const uint8_t x = pos[k]; pos[k] = pos[pick[k]]; pos[pick[k]] = x;
+    }
+  }
+  return samples;
+}
+
+PULSE_HD float pkq_equity(int64_t sum, int boards) {
+  return (float)((double)sum / ((double)boards * (double)PKQ_UNIT));
+}
+
 // packed -> reference-shaped tensors: the mirror behind attribute access on the drop-in env class, and the
 // inspection path of the parity tests.  Every pointer of C may be NULL (field not wanted).  decks: re-drawn from the
 // tape (or copied from the prefixed decks of the last reset) when `with_decks`; equities / equity_dirty: the

@@ -226,6 +226,22 @@ class PokerGPUPacked(gym.Env):
                        "pulse_poker_packed_enumerated_strength")
         return out
 
+    def showdown_equity(self, preflop_samples=256, counter=None):
+        """float32 [n_games, active_players]: every seat's all-in equity with ALL hole cards known (SURVEY 8(f) N4;
+        /root/reference/rl/depth_notes.txt:316-321 asks for it).  Flop, turn and river are enumerated exactly; preflop
+        averages `preflop_samples` boards drawn from the chance tape at `counter` (default: a counter of this env
+        that advances with every call, so repeated calls average independent samples)."""
+        if counter is None:
+            counter = self._equity_counter = getattr(self, "_equity_counter", -1) + 1
+        out = torch.empty((self.n_games, self.active_players), dtype=torch.float32, device=self.device)
+        cfg = self._config()
+        with _lib.device_guard(self.device):
+            _lib.check(self._lib.pulse_poker_packed_showdown_equity(
+                C.byref(self._packed), C.byref(cfg), ptr(out), c_i(int(preflop_samples)), c_u64(self.seed_value),
+                c_u64(self.env_base), c_u32(int(counter) & 0xFFFFFFFF), _lib.cuda_stream(self.device)),
+                "pulse_poker_packed_showdown_equity")
+        return out
+
     def get_info(self):
         # what build_actions and the trainers read (environments/Poker/utils.py:108-123, scripts/Poker/trainGPU.py:75-96):
         # real tensors -- `info["seat_idx"] == q_seat` is a bool tensor, `info["stacks"][:, q_seat]` a row of the

@@ -160,6 +160,14 @@ class EmuPokerPacked(EmuPoker):
         return self.obs, self.rewards, self.is_done.astype(bool)
 
 
+    def showdown_equity(self, samples=256, counter=0, lanes=1):
+        """csrc/poker_packed_body.cuh::packed_showdown_equity_part on the host, boards split over `lanes` workers"""
+        out = np.zeros((self.n_games, self.active_players), np.float32)
+        s = self._packed()
+        lib().emu_showdown_equity(C.byref(s), C.byref(self.cfg), p(out), C.c_int(samples), C.c_uint64(self.seed),
+                                  C.c_uint64(self.env_base), C.c_uint32(counter), C.c_int(lanes))
+        return out
+
     def wire_rows(self):
         """the compact step record (csrc/poker_wire.cuh) of every table, reward = self.rewards"""
         words = 3 + (13 + 3 * (self.max_players - 1) - 8 + 1) // 2

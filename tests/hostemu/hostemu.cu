@@ -116,6 +116,28 @@ int emu_poker_wire_rows(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
   return 0;
 }
 float emu_enumerated_strength(int stage, int h0, int h1, uint32_t fb) { return packed_enumerated_strength(stage, h0, h1, fb); }
+// showdown equity of every table, the boards of a table split over `nl` emulated lanes (1 = serial, 32 = as the kernel's warp)
+int emu_showdown_equity(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* out, int samples, uint64_t seed,
+                        uint64_t env_base, uint32_t counter, int nl) {
+  PokerParams pr = mk(cfg);
+  const long long n = cfg->n_games;
+#define EMU_EQ(MPV)                                                                                          \
+  for (long long g = 0; g < n; ++g) {                                                                        \
+    PokerTable<MPV> t; uint32_t fb;                                                                          \
+    packed_load(t, fb, *st, g, n, pr.AP);                                                                    \
+    int64_t tot[MPV] = {0};                                                                                  \
+    int boards = 0;                                                                                          \
+    for (int lane = 0; lane < nl; ++lane) {                                                                  \
+      int32_t num[MPV] = {0};                                                                                \
+      boards = packed_showdown_equity_part<MPV>(t, pr.AP, samples, seed, env_base + (uint64_t)g, counter, lane, nl, num); \
+      for (int s = 0; s < MPV; ++s) tot[s] += num[s];                                                        \
+    }                                                                                                        \
+    for (int s = 0; s < pr.AP; ++s) out[g * pr.AP + s] = pkq_equity(tot[s], boards);                         \
+  }
+  if (pr.P <= 2) { EMU_EQ(2) } else if (pr.P <= 4) { EMU_EQ(4) } else if (pr.P <= 6) { EMU_EQ(6) } else { EMU_EQ(10) }
+#undef EMU_EQ
+  return 0;
+}
 int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg) {
   PokerParams pr = mk(cfg);
   for (long long g = 0; g < cfg->n_games; ++g)
