@@ -96,9 +96,12 @@ def tfe(boards=256, steps_each=400):
     return {"env_steps_per_s": n / spent, "boards": boards, "what": "TFE.step (TFE.py:152-189), one board per object, Python loop, one core"}
 
 
-for name, fn in (("poker_hu_65536", lambda: poker(2, 65536, 16)), ("poker_hu_1048576", lambda: poker(2, 1 << 20, 16)),
+ONLY = set(sys.argv[1:])   # optional: names to (re)measure; the others are left out of the printed file
+for name, fn in (("poker_hu_256", lambda: poker(2, 256, 16, min_s=10.0)), ("poker_hu_65536", lambda: poker(2, 65536, 16)), ("poker_hu_1048576", lambda: poker(2, 1 << 20, 16)),
                  ("poker_6max_65536", lambda: poker(6, 65536, 24)), ("poker_10max_65536", lambda: poker(10, 65536, 32)),
                  ("blackjack_4096", blackjack), ("particle2d_16M", particle), ("tfe_4x4_single_board_loop", tfe)):
+    if ONLY and name not in ONLY:
+        continue
     t0 = time.time()
     out["results"][name] = fn()
     out["results"][name]["seconds"] = round(time.time() - t0, 1)

@@ -336,6 +336,9 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
   long long nc = ((e->N + n_chunks - 1) / n_chunks + 1023) & ~1023LL;
   e->Nc = nc; e->chunks = (int)((e->N + nc - 1) / nc);
   if (n_threads < 1) { n_threads = (int)std::thread::hardware_concurrency(); if (n_threads < 1) n_threads = 1; }
+  // a worker hand-off costs a few microseconds: below ~16 K tables per worker the pool is slower than the caller's own
+  // thread (256 tables, the reference's benchmark size: 87 us per step with 16 workers)
+  if ((long long)n_threads > (e->N + 16383) / 16384) n_threads = (int)((e->N + 16383) / 16384);
   int rc = 0;
   auto fail = [&](int code) { delete e; return code; };
   if (cudaSetDevice(device) != cudaSuccess) { pulse_set_error("cudaSetDevice(%d) failed", device); return fail(PULSE_EINVAL); }
