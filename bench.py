@@ -508,6 +508,7 @@ def run_env_workload(args, name):
             "e2e": {"value": world * e["value"] * (e["ms"] / e2e_ms), "unit": "env-steps/s",
                     "h2d_bytes_per_step": e["h2d_bytes_per_step"], "d2h_bytes_per_step": e["d2h_bytes_per_step"],
                     "steps": e["steps"], "chunks": e["chunks"],
+                    **{k: e[k] for k in ("api", "host_threads") if k in e},
                     "timing": "wall clock around the host loop, all streams synchronised"},
             "gpu_launches": m["launches"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -554,7 +555,8 @@ def extra_workloads(dev, rank, steps=256):
             if name == "tfe_4x4":      # the metric's second env: end to end and the CPU port beside it
                 e = be.e2e(name, dev, rank, 64)
                 out[name]["e2e"] = {"value": e["value"], "unit": "env-steps/s", "h2d_bytes_per_step": e["h2d_bytes_per_step"],
-                                    "d2h_bytes_per_step": e["d2h_bytes_per_step"], "steps": e["steps"], "chunks": e["chunks"]}
+                                    "d2h_bytes_per_step": e["d2h_bytes_per_step"], "steps": e["steps"], "chunks": e["chunks"],
+                                    **{k: e[k] for k in ("api", "host_threads") if k in e}}
                 out[name]["cpu_baseline"] = be.cpu_baseline(name, 5.0)[0]
         except Exception as ex:  # an extra must never take the headline down with it
             out[name] = {"error": f"{type(ex).__name__}: {ex}"}

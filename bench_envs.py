@@ -288,8 +288,8 @@ def e2e(name, dev, rank, steps, n=None, chunks=4):
     n = int(n or spec["n"])
     if name == "blackjack":
         return _e2e_blackjack_rollout(dev, rank, steps, n)
-    if name == "tfe_4x4_rollout":   # end to end the link carries the same 69 B per board-step either way: measured per step
-        name, spec = "tfe_4x4", SPECS["tfe_4x4"]
+    if name in ("tfe_4x4", "tfe_4x4_rollout"):
+        return _e2e_tfe_host(dev, rank, steps, n, min(chunks, 4))   # 1M boards: three to six chunks measure the same, eight lose 10%
     chunks = chunks if n >= 1 << 16 else 1
     nc = n // chunks
     made = [_make(name, dev, nc, rank * 64 + 32 + c, e2e=True) for c in range(chunks)]
@@ -322,6 +322,36 @@ def e2e(name, dev, rank, steps, n=None, chunks=4):
     d2h = sum(h.numel() * h.element_size() for hs in h_out for h in hs)
     return dict(value=nc * chunks * steps / (ms * 1e-3), ms=ms, steps=steps, chunks=chunks, h2d_bytes_per_step=h2d,
                 d2h_bytes_per_step=d2h)
+
+
+def _e2e_tfe_host(dev, rank, steps, n, chunks):
+    """2048 end to end through the host-buffer env (pulselib_b200.host_env.TFEHostEnv -> pulse_tfe_host_step): numpy uint8
+    moves in, int32 tile values [N, 4, 4] + int32 rewards + bool dones out in host arrays every step.  1 B per board goes
+    to the GPU, the packed 8 B board + 5 B come back, host threads rebuild the tile values.  Host-synchronous API: wall
+    clock around the loop."""
+    import numpy as np
+    import torch
+
+    from pulselib_b200.host_env import TFEHostEnv
+
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    threads = max(1, avail // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))
+    env = TFEHostEnv(dev, n_envs=n, side=4, seed=SEED, env_base=rank * n, auto_reset=True, chunks=chunks, threads=threads)
+    acts = np.random.default_rng(SEED + rank).integers(0, 4, (16, n)).astype(np.uint8)
+    env.reset()
+    for i in range(3):
+        env.step(acts[i])
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    for i in range(steps):
+        env.step(acts[i % 16])
+    torch.cuda.synchronize(dev)
+    ms = (time.perf_counter() - w0) * 1e3
+    inf = env.info()
+    env.close()
+    return dict(value=n * steps / (ms * 1e-3), ms=ms, steps=steps, chunks=inf["chunks"], host_threads=inf["threads"],
+                h2d_bytes_per_step=inf["last_h2d_bytes"], d2h_bytes_per_step=inf["last_d2h_bytes"],
+                api="pulselib_b200.host_env.TFEHostEnv.step (pulse_tfe_host_step): host arrays in and out, packed boards over PCIe")
 
 
 def _e2e_blackjack_rollout(dev, rank, steps, n):

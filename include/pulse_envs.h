@@ -391,6 +391,31 @@ int pulse_poker_wire_expand_step_host(const uint32_t* rows, uint32_t* live_inout
                                       uint8_t* done);
 const char* pulse_poker_host_expand_isa(void);
 
+/* ---- host-buffer 2048 (the end-to-end path of the batched 2048 env) ------------------------------------------------
+ * TFE.reset / TFE.step (/root/reference/environments/2048/TFE.py:143-189) for N boards whose arrays live in HOST memory
+ * (pageable is fine).  What crosses PCIe is 1 B of action per board in and the engine's packed board (8 B) + reward
+ * (4 B) + done (1 B) out; host threads rebuild the reference's int32 tile values [N, side, side] (:121) in the
+ * caller's array, chunk by chunk while the next chunk's step and copies run.  Chance from the tape only, keyed by
+ * (seed, env_base + board, call counter): results equal pulse_tfe_reset / pulse_tfe_step called once per reset / step
+ * with counters 0, 1, 2, ...  auto_reset as pulse_tfe_step.  n_chunks / n_threads: 0 = one chunk / all host threads.
+ * The handle owns device state, pinned staging, streams and threads; calls on one handle are serial and synchronous. */
+typedef struct PulseTfeHostEnv PulseTfeHostEnv;
+int pulse_tfe_host_create(PulseTfeHostEnv** out, long long n_envs, int side, int auto_reset, uint64_t seed,
+                          uint64_t env_base, int device, int n_chunks, int n_threads);
+void pulse_tfe_host_destroy(PulseTfeHostEnv* env);
+/* obs_host int32 [N, side, side] or NULL; done_host_or_null uint8 [N] (cleared) */
+int pulse_tfe_host_reset(PulseTfeHostEnv* env, int32_t* obs_host, uint8_t* done_host_or_null);
+/* actions_host uint8 or int64 [N] (action_bytes 1 or 8); obs_host int32 [N, side, side] or NULL (boards only, see
+ * pulse_tfe_host_boards); reward_host int32 [N]; done_host uint8 [N] */
+int pulse_tfe_host_step(PulseTfeHostEnv* env, const void* actions_host, int action_bytes, int32_t* obs_host,
+                        int32_t* reward_host, uint8_t* done_host);
+const uint64_t* pulse_tfe_host_boards(const PulseTfeHostEnv* env);   /* packed boards of the last call, pinned host memory */
+int pulse_tfe_host_scores(PulseTfeHostEnv* env, int64_t* score_host); /* TFE.total_score (:183) of every board */
+int pulse_tfe_host_info(const PulseTfeHostEnv* env, int* chunks, int* threads, long long* last_h2d_bytes,
+                        long long* last_d2h_bytes);
+/* pure host function: n packed boards -> int32 tile values [n, side, side], through the env's own expander */
+int pulse_tfe_expand_host(const uint64_t* boards, long long n, int side, int32_t* obs_out);
+
 /* ---- run statistics (the vector that is all-reduced across GPUs) -------------------
  * stats4 double [4] on the device: += {n, number of done flags set, sum(reward), sum(reward^2)}.
  * reward: float32 [n] (reward_is_float != 0) or int32 [n]. */

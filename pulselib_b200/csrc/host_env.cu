@@ -14,6 +14,7 @@
 // threads; the caller's arrays may be pageable.  One handle = one env on one GPU; calls on one handle are serial.
 #include "poker_packed_body.cuh"
 #include "host_expand.h"
+#include "host_pool.h"
 
 #include <emmintrin.h>
 
@@ -88,54 +89,6 @@ poker_host_rows_kernel(PulsePokerPacked S, PokerParams pr, uint32_t* __restrict_
   }
 }
 
-// ---- host side: a small persistent thread pool ------------------------------------------------------------------
-class Pool {
- public:
-  explicit Pool(int n) : n_(n < 1 ? 1 : n) {
-    for (int i = 1; i < n_; ++i) th_.emplace_back([this, i] { loop(i); });
-  }
-  ~Pool() {
-    { std::lock_guard<std::mutex> lk(m_); stop_ = true; ++gen_; }
-    cv_.notify_all();
-    for (auto& t : th_) t.join();
-  }
-  int size() const { return n_; }
-  // fn(worker) on every worker, the caller being worker 0; returns when all are done
-  void run(const std::function<void(int)>& fn) {
-    if (n_ == 1) { fn(0); return; }
-    { std::lock_guard<std::mutex> lk(m_); fn_ = &fn; pending_ = n_ - 1; ++gen_; }
-    cv_.notify_all();
-    fn(0);
-    std::unique_lock<std::mutex> lk(m_);
-    done_cv_.wait(lk, [this] { return pending_ == 0; });
-  }
-
- private:
-  void loop(int id) {
-    unsigned long long seen = 0;
-    for (;;) {
-      const std::function<void(int)>* fn;
-      {
-        std::unique_lock<std::mutex> lk(m_);
-        cv_.wait(lk, [&] { return gen_ != seen; });
-        seen = gen_;
-        if (stop_) return;
-        fn = fn_;
-      }
-      (*fn)(id);
-      { std::lock_guard<std::mutex> lk(m_); if (--pending_ == 0) done_cv_.notify_one(); }
-    }
-  }
-  int n_;
-  std::vector<std::thread> th_;
-  std::mutex m_;
-  std::condition_variable cv_, done_cv_;
-  const std::function<void(int)>* fn_ = nullptr;
-  unsigned long long gen_ = 0;
-  int pending_ = 0;
-  bool stop_ = false;
-};
-
 }  // namespace
 
 struct PulsePokerHostEnv {
@@ -162,7 +115,7 @@ struct PulsePokerHostEnv {
   uint32_t epoch = 0;
   std::vector<uint32_t> prev_live;         // the live mask as it was when the previous call began (reward zeroing)
   std::atomic<int>* remaining = nullptr;   // per chunk: workers still expanding it (the last one rebuilds its offsets)
-  Pool* pool = nullptr;
+  pulse_host::Pool* pool = nullptr;
   long long last_h2d = 0, last_d2h = 0;
   // seconds, accumulated over calls: staging the actions, submitting GPU work, the expansion phase (wall), and summed
   // over workers: time spent waiting for records / time spent expanding
@@ -366,7 +319,7 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
     }
     e->streams.push_back(s); e->events.push_back(ev);
   }
-  e->pool = new Pool(n_threads);
+  e->pool = new pulse_host::Pool(n_threads);
   e->remaining = new std::atomic<int>[e->chunks];
   for (int c = 0; c < e->chunks; ++c) e->remaining[c].store(0);
   {

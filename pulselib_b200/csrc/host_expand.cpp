@@ -126,3 +126,44 @@ void pulse_expand_range(const PulseExpandArgs& a) {
 }
 
 const char* pulse_expand_isa(void) { return have_avx2() ? "avx2" : "portable"; }
+
+// ---- 2048: packed board -> int32 tile values ---------------------------------------------------------------------
+namespace {
+
+inline void tfe_expand_portable(const uint64_t* boards, int32_t* obs, long long g0, long long g1, int side) {
+  for (long long g = g0; g < g1; ++g) {
+    const uint64_t b = boards[g];
+    int32_t* o = obs + g * side * side;
+    for (int r = 0; r < side; ++r)
+      for (int c = 0; c < side; ++c) {
+        const unsigned e = (unsigned)((b >> (16 * r + 4 * c)) & 15u);
+        o[r * side + c] = e ? (int32_t)(1u << e) : 0;
+      }
+  }
+}
+
+// 4 x 4 boards, 32-byte aligned rows: nibbles -> bytes, two byte shuffles look up the low and high byte of 1 << e
+// (0 for e = 0), widened to int32 and streamed as one 64-byte line
+__attribute__((target("avx2"))) void tfe_expand_avx2_side4(const uint64_t* boards, int32_t* obs, long long g0, long long g1) {
+  const __m128i lut_lo = _mm_setr_epi8(0, 2, 4, 8, 16, 32, 64, (char)128, 0, 0, 0, 0, 0, 0, 0, 0);
+  const __m128i lut_hi = _mm_setr_epi8(0, 0, 0, 0, 0, 0, 0, 0, 1, 2, 4, 8, 16, 32, 64, (char)128);
+  const __m128i nib = _mm_set1_epi8(0x0F);
+  for (long long g = g0; g < g1; ++g) {
+    const __m128i x = _mm_cvtsi64_si128((long long)boards[g]);
+    const __m128i lo = _mm_and_si128(x, nib), hi = _mm_and_si128(_mm_srli_epi64(x, 4), nib);
+    const __m128i e = _mm_unpacklo_epi8(lo, hi);                       // 16 exponents in cell order
+    const __m128i vl = _mm_shuffle_epi8(lut_lo, e), vh = _mm_shuffle_epi8(lut_hi, e);
+    const __m128i w0 = _mm_unpacklo_epi8(vl, vh), w1 = _mm_unpackhi_epi8(vl, vh);   // 8 x u16 each
+    int32_t* o = obs + g * 16;
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(o), _mm256_cvtepu16_epi32(w0));
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(o + 8), _mm256_cvtepu16_epi32(w1));
+  }
+  _mm_sfence();
+}
+
+}  // namespace
+
+void pulse_tfe_expand_range(const uint64_t* boards, int32_t* obs, long long g0, long long g1, int side) {
+  if (side == 4 && have_avx2() && (reinterpret_cast<uintptr_t>(obs) & 31u) == 0) tfe_expand_avx2_side4(boards, obs, g0, g1);
+  else tfe_expand_portable(boards, obs, g0, g1, side);
+}

@@ -18,3 +18,7 @@ struct PulseExpandArgs {
 // Expands the records of tables [g0, g1).  Picks an AVX2 body when the CPU has it (checked once), else portable code.
 void pulse_expand_range(const PulseExpandArgs& a);
 const char* pulse_expand_isa(void);
+
+// 2048 host-buffer path (csrc/tfe_host_env.cu): packed boards (tile exponents, 4 bits per cell, cell (r, c) at bits
+// 16 r + 4 c) -> the reference's int32 tile values [side, side] per board (TFE.py:121), boards [g0, g1).
+void pulse_tfe_expand_range(const uint64_t* boards, int32_t* obs, long long g0, long long g1, int side);

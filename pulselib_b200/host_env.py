@@ -147,3 +147,82 @@ def expand_isa() -> str:
     lib = _lib.load()
     lib.pulse_poker_host_expand_isa.restype = C.c_char_p
     return lib.pulse_poker_host_expand_isa().decode()
+
+
+class TFEHostEnv:
+    """Batched 2048 with host (numpy) buffers: `pulse_tfe_host_*` (include/pulse_envs.h, csrc/tfe_host_env.cu).
+
+    The reference's step contract per board -- int32 tile values [side, side], reward, done
+    (/root/reference/environments/2048/TFE.py:152-189) -- for N boards whose arrays live in host memory: 1 B of action
+    per board goes to the GPU, the packed 8 B board + reward + done come back, and native threads rebuild the tile
+    values in `self.obs`.  Same trajectories as `TFEBatched(seed, env_base, auto_reset)` stepped from the tape."""
+
+    def __init__(self, device=0, n_envs=1024, side=4, seed=0, env_base=0, auto_reset=True, chunks=4, threads=0):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise _lib.PulseError("TFEHostEnv needs a CUDA device: the engine has no CPU fallback")
+        if int(side) not in (2, 3, 4):
+            raise ValueError("side must be 2, 3 or 4")
+        self._lib = _lib.load()
+        dev = torch.device(device) if not isinstance(device, int) else torch.device("cuda", device)
+        self.device_index = dev.index if dev.index is not None else torch.cuda.current_device()
+        self.n_envs, self.side = int(n_envs), int(side)
+        self._h = C.c_void_p()
+        _lib.check(self._lib.pulse_tfe_host_create(C.byref(self._h), C.c_longlong(self.n_envs), C.c_int(self.side),
+                                                   C.c_int(1 if auto_reset else 0), C.c_uint64(int(seed)),
+                                                   C.c_uint64(int(env_base)), C.c_int(self.device_index),
+                                                   C.c_int(int(chunks)), C.c_int(int(threads))), "pulse_tfe_host_create")
+        self.obs = _aligned((self.n_envs, self.side, self.side), np.int32)   # 4 x 4 boards: one 64-byte line each
+        self.rewards = _aligned((self.n_envs,), np.int32)
+        self.dones = _aligned((self.n_envs,), np.uint8)
+
+    def reset(self):
+        _lib.check(self._lib.pulse_tfe_host_reset(self._h, _p(self.obs), _p(self.dones)), "pulse_tfe_host_reset")
+        self.rewards[:] = 0
+        return self.obs, {}
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions)
+        if a.dtype not in (np.uint8, np.int64):
+            a = a.astype(np.int64)
+        if a.shape != (self.n_envs,):
+            raise ValueError(f"actions must have shape {(self.n_envs,)}, got {a.shape}")
+        _lib.check(self._lib.pulse_tfe_host_step(self._h, _p(a), C.c_int(a.dtype.itemsize), _p(self.obs), _p(self.rewards),
+                                                 _p(self.dones)), "pulse_tfe_host_step")
+        return self.obs, self.rewards, self.dones.view(np.bool_), False, {}
+
+    def boards(self) -> np.ndarray:
+        """the packed boards of the last call (uint64 [N], a view of the env's pinned buffer)"""
+        self._lib.pulse_tfe_host_boards.restype = C.POINTER(C.c_uint64)
+        return np.ctypeslib.as_array(self._lib.pulse_tfe_host_boards(self._h), shape=(self.n_envs,))
+
+    def scores(self) -> np.ndarray:
+        out = np.zeros(self.n_envs, np.int64)
+        _lib.check(self._lib.pulse_tfe_host_scores(self._h, _p(out)), "pulse_tfe_host_scores")
+        return out
+
+    def info(self) -> dict:
+        v = [C.c_int(), C.c_int(), C.c_longlong(), C.c_longlong()]
+        _lib.check(self._lib.pulse_tfe_host_info(self._h, *[C.byref(x) for x in v]), "pulse_tfe_host_info")
+        return dict(chunks=v[0].value, threads=v[1].value, last_h2d_bytes=v[2].value, last_d2h_bytes=v[3].value)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.pulse_tfe_host_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def expand_boards(boards: np.ndarray, side: int = 4) -> np.ndarray:
+    """Packed 2048 boards (uint64 [n]) -> int32 tile values [n, side, side] through the host env's expander; host only."""
+    lib = _lib.load()
+    b = np.ascontiguousarray(boards, dtype=np.uint64)
+    out = _aligned((b.shape[0], side, side), np.int32)
+    _lib.check(lib.pulse_tfe_expand_host(_p(b), C.c_longlong(b.shape[0]), C.c_int(int(side)), _p(out)), "pulse_tfe_expand_host")
+    return out

@@ -117,3 +117,61 @@ def test_records_mode_matches_float32_engine(P, M, N, chunks, cuda_device):
             np.testing.assert_array_equal(rew.view(np.uint32), r2.cpu().numpy().view(np.uint32))
             np.testing.assert_array_equal(dones, d2.cpu().numpy())
     henv.close()
+
+
+# ---- 2048 with host buffers -----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("N,side,chunks,threads,auto", [(100_003, 4, 3, 4, True), (1 << 20, 4, 8, 0, True), (33_333, 3, 2, 2, True),
+                                                         (5_000, 4, 4, 3, False), (257, 2, 1, 1, True)])
+def test_tfe_host_env_matches_device_env(N, side, chunks, threads, auto, cuda_device):
+    """TFEHostEnv (host arrays, packed boards over PCIe, native threads rebuilding the tile values) must return exactly
+    what TFEBatched returns from device buffers: observations, rewards, done flags and scores, step for step."""
+    import numpy as np
+    import torch
+
+    from pulselib_b200.envs.tfe import TFEBatched
+    from pulselib_b200.host_env import TFEHostEnv
+
+    ref = TFEBatched(cuda_device, N, side=side, seed=21, env_base=1 << 35, auto_reset=auto)
+    henv = TFEHostEnv(cuda_device, n_envs=N, side=side, seed=21, env_base=1 << 35, auto_reset=auto, chunks=chunks, threads=threads)
+    inf = henv.info()
+    assert inf["chunks"] <= max(1, chunks) and inf["threads"] >= 1
+    o, _ = ref.reset()
+    ho, _ = henv.reset()
+    np.testing.assert_array_equal(ho, o.cpu().numpy())
+    assert not henv.dones.any()
+    rng = np.random.default_rng(N)
+    steps = 60 if N <= 200_000 else 12
+    for t in range(steps):
+        a = rng.integers(0, 4, N)
+        a = a.astype(np.uint8) if t % 2 == 0 else a.astype(np.int64)
+        o, r, d, _, info = ref.step(torch.from_numpy(a).to(cuda_device))
+        ho, hr, hd, _, _ = henv.step(a)
+        np.testing.assert_array_equal(ho, o.cpu().numpy(), err_msg=f"step {t}: observations")
+        np.testing.assert_array_equal(hr, r.cpu().numpy(), err_msg=f"step {t}: rewards")
+        np.testing.assert_array_equal(hd, d.cpu().numpy(), err_msg=f"step {t}: done flags")
+    np.testing.assert_array_equal(henv.scores(), ref.total_score.cpu().numpy())
+    np.testing.assert_array_equal(henv.boards().view(np.int64), ref.boards.cpu().numpy())
+    assert henv.info()["last_d2h_bytes"] == 13 * N and henv.info()["last_h2d_bytes"] == N
+    # a second hand on the same handle
+    o, _ = ref.reset()
+    ho, _ = henv.reset()
+    np.testing.assert_array_equal(ho, o.cpu().numpy())
+    henv.close()
+
+
+def test_tfe_host_env_rejects_bad_arguments(cuda_device):
+    import numpy as np
+
+    from pulselib_b200 import _lib
+    from pulselib_b200.host_env import TFEHostEnv
+
+    with pytest.raises(ValueError):
+        TFEHostEnv(cuda_device, n_envs=64, side=5)
+    with pytest.raises(_lib.PulseError):
+        TFEHostEnv(cuda_device, n_envs=0)
+    env = TFEHostEnv(cuda_device, n_envs=64)
+    with pytest.raises(_lib.PulseError):
+        env.step(np.zeros(64, np.uint8))          # before reset
+    env.reset()
+    with pytest.raises(ValueError):
+        env.step(np.zeros(63, np.uint8))

@@ -78,3 +78,26 @@ def test_host_env_bookkeeping_through_whole_hands(P, M, N, hr_table):
             np.testing.assert_array_equal(obs[:N], o, err_msg=f"hand {hand} step {t} obs")
             np.testing.assert_array_equal(rew[:N].view(np.uint32), r.view(np.uint32), err_msg=f"hand {hand} step {t} reward")
             np.testing.assert_array_equal(done[:N].astype(bool), d)
+
+
+# ---- 2048 host path: packed boards -> int32 tile values ------------------------------------------------------------
+@pytest.mark.parametrize("side", [4, 3, 2])
+def test_tfe_board_expander_matches_numpy(side):
+    """csrc/host_expand.cpp::pulse_tfe_expand_range (AVX2 for aligned 4 x 4 boards, portable otherwise) against the
+    definition: cell (r, c) holds exponent e at bits 16 r + 4 c, tile value = 2^e, 0 for e = 0."""
+    from pulselib_b200.host_env import expand_boards
+
+    rng = np.random.default_rng(side)
+    n = 4099
+    e = rng.integers(0, 16, (n, 4, 4)).astype(np.uint64)
+    e[:, side:, :] = 0
+    e[:, :, side:] = 0
+    e[0] = 0
+    e[1, :side, :side] = 15
+    b = np.zeros(n, np.uint64)
+    for r in range(4):
+        for c in range(4):
+            b |= e[:, r, c] << np.uint64(16 * r + 4 * c)
+    ex = e[:, :side, :side].astype(np.int64)
+    want = np.where(ex > 0, 1 << ex, 0).astype(np.int32)
+    np.testing.assert_array_equal(expand_boards(b, side), want)
