@@ -446,7 +446,11 @@ def run_gpu(args, wl, name):
             "gpu_launches": n_launch,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "poker_packed_step_kernel", "kernel_ms": kernel_ms,
-                         "algorithmic_bytes_per_table_step": A, "peak_source": peak_src},
+                         "algorithmic_bytes_per_table_step": A, "peak_source": peak_src,
+                         # the same fraction by the DRAM bytes ncu counted for one launch (profiles/traffic.json): the
+                         # packed layout moves fewer bytes than the fixed algorithmic figure, so this is the one that
+                         # says how busy HBM really is
+                         "frac_by_traffic": (traffic / (kernel_ms * 1e-3) / 1e9 / peak) if traffic else None},
             "clocks": sampler.summary(),
         }
         if base is not None:
@@ -512,7 +516,8 @@ def run_env_workload(args, name):
                     "timing": "wall clock around the host loop, all streams synchronised"},
             "gpu_launches": m["launches"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": spec["kernel"], "kernel_ms": kernel_ms,
+                         "traffic": traffic, "frac_by_traffic": (traffic / (kernel_ms * 1e-3) / 1e9 / peak) if traffic else None,
+                         "kernel": spec["kernel"], "kernel_ms": kernel_ms,
                          "kernel_time": m["kernel_time"], "algorithmic_bytes_per_env_step": A, "peak_source": peak_src},
             "clocks": sampler.summary(),
         }
