@@ -541,7 +541,8 @@ def extra_workloads(dev, rank, steps=256):
 
     peak, _ = peaks()
     out = {}
-    for name in ("tfe_4x4", "tfe_4x4_rollout", "tetris", "particle2d", "blackjack", "poker_hu_autoreset", "poker_hu_scripted"):
+    for name in ("tfe_4x4", "tfe_4x4_rollout", "tetris", "particle2d", "blackjack", "poker_hu_autoreset", "poker_hu_scripted",
+                 "poker_hu_rollout", "poker_hu_rollout_tape"):
         try:
             m = be.measure(name, dev, rank, 1, steps, 3)
             A = be.SPECS[name]["algo_bytes"]
@@ -575,7 +576,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=32)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="poker_hu",
-                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tfe_4x4_rollout", "tetris", "particle2d", "blackjack", "blackjack_per_step", "poker_hu_autoreset", "poker_hu_scripted", "poker_hu_train_loop"])
+                    choices=sorted(WORKLOADS) + ["tfe_4x4", "tfe_4x4_rollout", "tetris", "particle2d", "blackjack", "blackjack_per_step", "poker_hu_autoreset", "poker_hu_scripted", "poker_hu_train_loop", "poker_hu_rollout", "poker_hu_rollout_tape"])
     ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` block of the poker line")
     ap.add_argument("--tables", type=int, default=0, help="tables per GPU (default: the workload's)")
     ap.add_argument("--e2e-chunks", type=int, default=8)

@@ -41,6 +41,21 @@ SPECS = {
                               desc="PokerGPU heads-up, {n} tables/GPU, seats played by the scripted TightAggressive and "
                                    "SmallBall rules inside the step kernel (no action tensor), draws from the chance "
                                    "tape, per-table auto-reset"),
+    # SURVEY 8(b) pulse_poker_rollout, "on-device random policy, K steps per launch": one call deals the whole batch and
+    # plays a 16-step hand with every seat's action drawn on the device (PULSE_AGENT_RANDOM, chance tape) -- the
+    # headline's workload without an action tensor and with one launch per hand instead of sixteen.  Written per step:
+    # reward + done of every table ([16, N]); the observation only after the last step.
+    "poker_hu_rollout": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_rollout_kernel<2> (+ reset)", graph=0, actions=16,
+                             steps_per_call=16,
+                             desc="PokerGPU heads-up, {n} tables/GPU, uniform random actions 0..12 drawn ON THE DEVICE from the "
+                                  "chance tape, 16 steps per launch, whole-batch reset before every launch (inside the timed "
+                                  "region), rewards / dones of every step and the final observation written"),
+    # the headline's own trajectories (supplied uniform random actions), 16 steps per launch: pulse_poker_packed_rollout_actions
+    "poker_hu_rollout_tape": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_rollout_kernel<2> (+ reset)", graph=0, actions=16,
+                                  steps_per_call=16,
+                                  desc="PokerGPU heads-up, {n} tables/GPU, uniform random actions 0..12 supplied as a uint8 [16, N] "
+                                       "tape, 16 steps per launch, whole-batch reset before every launch (inside the timed region), "
+                                       "rewards / dones of every step and the final observation written"),
     # SURVEY 8(d) config 3, convention (ii): supplied uniform random actions, per-table auto-reset -- no table ever
     # idles; a table that finished is dealt its next hand by the step that follows (that step plays no action for it).
     "poker_hu_autoreset": dict(n=1 << 22, algo_bytes=201, kernel="poker_packed_step_kernel<2, 2, 10, false, 2> + redeal pass",
@@ -125,6 +140,30 @@ def _make(name, dev, n, rank, e2e=False):
         def step(e, a):
             o, r, d, _, info = e.step_policy(kinds)
             return o, r, d, info["actions"]
+    elif name == "poker_hu_rollout":
+        from pulselib_b200 import policy
+        from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+        env = PokerGPUPacked(dev, n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3,
+                             K=100, alpha=50, seed=SEED, env_base=rank * n, auto_reset=False, live_info=False)
+        acts = torch.zeros((L, 1), dtype=torch.int64, device=dev)
+        kinds = bytes([policy.RANDOM, policy.RANDOM])
+
+        def step(e, a):                                  # one hand: deal + one launch of 16 steps
+            e.reset()
+            o, r, d, _ = e.rollout_policy(kinds, L, return_actions=False)
+            return o, r[-1], d[-1]
+    elif name == "poker_hu_rollout_tape":
+        from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+        env = PokerGPUPacked(dev, n_players=2, max_players=2, n_games=n, starting_bbs=100, max_bbs=1000, w1=.5, w2=.3,
+                             K=100, alpha=50, seed=SEED, env_base=rank * n, auto_reset=False, live_info=False)
+        acts = torch.randint(0, 13, (L, n), dtype=torch.uint8, device=dev, generator=gen)
+
+        def step(e, a):                                  # one hand: deal + one launch of 16 steps on the tape
+            e.reset()
+            o, r, d = e.rollout_actions(acts)
+            return o, r[-1], d[-1]
     elif name == "poker_hu_autoreset":
         from pulselib_b200.envs.poker_packed import PokerGPUPacked
 
@@ -271,7 +310,7 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
     barrier()
     total_ms = t0.elapsed_time(t1)
     kernel_ms = (sum(a.elapsed_time(b) for a, b in pairs) / len(pairs) / spc) if pairs else total_ms / steps
-    launches = steps // 16 + 1 if name == "tfe_4x4_rollout" else steps // 128 + 1 if name == "blackjack" else steps + (steps // 8 + 1 if name == "blackjack_per_step" else 0)
+    launches = steps // 16 + 1 if name == "tfe_4x4_rollout" else 2 * (steps // 16 + 1) if name in ("poker_hu_rollout", "poker_hu_rollout_tape") else steps // 128 + 1 if name == "blackjack" else steps + (steps // 8 + 1 if name == "blackjack_per_step" else 0)
     return dict(n=n, total_ms=total_ms, kernel_ms=kernel_ms, launches=launches, replicas=replicas, live_fraction=live_fraction,
                 mode=f"cuda graph of {chunk} steps" if graph is not None else "eager launches",
                 kernel_time="graph time / steps (includes inter-kernel gaps)" if graph is not None

@@ -298,6 +298,13 @@ int pulse_poker_packed_rollout(const PulsePokerPacked* st, const PulsePokerConfi
                                uint32_t counter, int n_steps, int auto_reset, uint64_t seed, uint64_t env_base,
                                float* obs_final_or_null, float* reward_out, uint8_t* done_out, int64_t* actions_out_or_null,
                                pulse_stream_t stream);
+/* K steps per launch on SUPPLIED actions (open-loop tapes: replays, random-policy benchmarks): actions uint8 [K, N]
+ * (255 = a negative id, which matches no branch).  Exactly what K calls of pulse_poker_packed_step without auto_reset
+ * would return one after another -- reward_out float32 [K, N], done_out uint8 [K, N], obs_final_or_null = the
+ * observation after the last step -- but the table is loaded once, stepped K times in registers and stored once. */
+int pulse_poker_packed_rollout_actions(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const uint8_t* actions,
+                                       int n_steps, float* obs_final_or_null, float* reward_out, uint8_t* done_out,
+                                       pulse_stream_t stream);
 
 /* Enumerated hand strength (no reference behaviour -- the reference's notes call its table-walk
  * proxy a known weakness, rl/depth_notes.txt:302-333).  strength_out float32 [N, active_players]: the expectation over

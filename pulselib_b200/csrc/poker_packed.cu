@@ -225,15 +225,54 @@ template <int MAXP>
 __global__ void __launch_bounds__(kBlock)
 poker_packed_rollout_kernel(PulsePokerPacked S, PokerParams pr, PackedPolicy pol, int K, int auto_reset, uint64_t seed,
                             uint64_t env_base, int starting_bbs, int max_bbs, long long n, float* __restrict__ obs_final,
-                            float* __restrict__ reward_out, uint8_t* __restrict__ done_out, int64_t* __restrict__ action_out) {
+                            float* __restrict__ reward_out, uint8_t* __restrict__ done_out, int64_t* __restrict__ action_out,
+                            const uint8_t* __restrict__ tape) {
   const int W = 13 + 3 * (pr.M - 1);
+  if (auto_reset == 0) {
+    // No redeals inside the launch: the table is loaded once, stepped K times in registers and stored once -- the K - 1
+    // intermediate load / decode / pack / store rounds (a fifth of the single step's instructions and all of its state
+    // traffic) never happen.  What a step writes: reward, done and, when asked, the action played.
+    for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
+      PackedEv<MAXP, (MAXP <= 2)> evw{S.ev, g, n};
+      evw.prefetch(pr.AP);
+      PokerTable<MAXP> t;
+      uint32_t fb;
+      packed_load(t, fb, S, g, n, pr.AP);
+      const PokerTable<MAXP> t0 = t;
+      int prev_inv = 0;
+      for (int k = 0; k < K; ++k) {
+        long long a;
+        if (tape) {                                       // supplied actions, uint8 [K, N]; 255 = "negative" (matches no branch)
+          a = (long long)tape[(long long)k * n + g];
+          if (a == 255) a = -1;
+        } else {
+          const int kind = pol.kinds.kind[t.idx & 15];    // build_actions: from the pre-step state, done or not (utils.py:108-123)
+          const PulseU4 b = pulse_tape(seed, env_base + (uint64_t)g, PULSE_STREAM_ACTION, pol.counter + (uint32_t)k);
+          a = pulse_policy_action(kind, pk_sel(t.hole0, t.idx), pk_sel(t.hole1, t.idx), (float)t.pot, b.x, b.y);
+        }
+        if (action_out) action_out[(long long)k * n + g] = a;
+        const PackedStepResult r = packed_step_regs<MAXP>(t, fb, evw, pr, a, prev_inv);
+        reward_out[(long long)k * n + g] = r.reward;
+        done_out[(long long)k * n + g] = r.done;
+      }
+      if (S.prev_invested) S.prev_invested[g] = prev_inv;
+      packed_store(t, t0, S, g, n, pr.AP);
+      if (S.idx && t.idx != t0.idx) S.idx[g] = t.idx;
+      if (obs_final) {
+        float row[13 + 3 * 15];
+        pk_obs(t, pr, row);
+        for (int c = 0; c < W; ++c) obs_final[g * W + c] = row[c];
+      }
+    }
+    return;
+  }
   for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock) {
     PackedPolicy p = pol;
     for (int k = 0; k < K; ++k) {
       p.counter = pol.counter + (uint32_t)k;
       p.chosen = action_out ? action_out + (long long)k * n : nullptr;
       PokerTable<MAXP> t;
-      const PackedStepResult r = packed_step_core<MAXP, true, 1>(S, pr, static_cast<const int64_t*>(nullptr), auto_reset, seed,
+      const PackedStepResult r = packed_step_core<MAXP, true, 1>(S, pr, static_cast<const int64_t*>(nullptr), auto_reset & 1, seed,
                                                                  env_base, starting_bbs, max_bbs, g, n, &p, t);
       reward_out[(long long)k * n + g] = r.reward;
       done_out[(long long)k * n + g] = r.done;
@@ -540,10 +579,34 @@ int pulse_poker_packed_rollout(const PulsePokerPacked* st, const PulsePokerConfi
   pol.chance2 = nullptr; pol.chosen = nullptr; pol.seat_before = nullptr; pol.counter = counter;
   PokerParams pr = make_params(cfg);
   const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  // PULSE_POKER_ROLLOUT_REGS=0: step through global memory between steps even without auto_reset (the A/B switch of
+  // the registers-resident path; bit 1 of the kernel's auto_reset argument)
+  static const bool regs_env = !(getenv("PULSE_POKER_ROLLOUT_REGS") && atoi(getenv("PULSE_POKER_ROLLOUT_REGS")) == 0);
+  if (!auto_reset && !regs_env) auto_reset = 2;
+  else auto_reset = auto_reset ? 1 : 0;
   PKP_DISPATCH(pr.P, (poker_packed_rollout_kernel<MP><<<grid, kBlock, 0, stream>>>(
                          *st, pr, pol, n_steps, auto_reset, seed, env_base, cfg->starting_bbs, cfg->max_bbs,
-                         (long long)cfg->n_games, obs_final_or_null, reward_out, done_out, actions_out_or_null)));
+                         (long long)cfg->n_games, obs_final_or_null, reward_out, done_out, actions_out_or_null, nullptr)));
   return pulse_check_launch("pulse_poker_packed_rollout");
+}
+
+int pulse_poker_packed_rollout_actions(const PulsePokerPacked* st, const PulsePokerConfig* cfg, const uint8_t* actions,
+                                       int n_steps, float* obs_final_or_null, float* reward_out, uint8_t* done_out,
+                                       cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  PULSE_REQUIRE(n_steps >= 0, "n_steps < 0");
+  if (cfg->n_games == 0 || n_steps == 0) return PULSE_OK;
+  PULSE_REQUIRE(actions && reward_out && done_out, "null buffer");
+  PackedPolicy pol;
+  for (int s = 0; s < 16; ++s) pol.kinds.kind[s] = (uint8_t)PULSE_AGENT_EXTERNAL;
+  pol.chance2 = nullptr; pol.chosen = nullptr; pol.seat_before = nullptr; pol.counter = 0;
+  PokerParams pr = make_params(cfg);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_rollout_kernel<MP><<<grid, kBlock, 0, stream>>>(
+                         *st, pr, pol, n_steps, 0, 0, 0, cfg->starting_bbs, cfg->max_bbs, (long long)cfg->n_games,
+                         obs_final_or_null, reward_out, done_out, nullptr, actions)));
+  return pulse_check_launch("pulse_poker_packed_rollout_actions");
 }
 
 int pulse_poker_packed_showdown_equity(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* equity_out,

@@ -363,6 +363,37 @@ struct PackedStepResult {
   bool done;       // done flag to report
 };
 
+// The step proper on a table held in registers (PokerGPU.py:531-632): no loads, no stores.  evw hands out the seats'
+// per-deal hand-value words; prev_inv = the actor's current_round_bet before the action (:539).
+template <int MAXP, class Ev>
+PULSE_HD PackedStepResult packed_step_regs(PokerTable<MAXP>& t, uint32_t fb, const Ev& evw, const PokerParams& pr,
+                                           long long a, int& prev_inv) {
+  const PackedDeck deck{fb, 2 * pr.AP};
+  const bool prev_done = t.done;
+  const int actor = t.idx;                                           // :531
+  const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537
+  prev_inv = pk_sel(t.crb, actor);                                   // :539
+  // the reference refreshes its equity cache here when the street has changed since the last step (:542);
+  // the packed layout only remembers for which street the cache stands
+  if (t.stage >= 1 && t.stage <= 3) t.eq_stage = t.stage;
+  float e = 0.5f;
+  if (legal)  // the reward is zeroed otherwise (:632), so the equity is only needed for legal actors
+    e = (t.stage >= 1 && t.stage <= 3) ? pkp_equity_from(evw.word(actor), t.stage) : 0.5f;
+  pk_execute(t, a);                                                  // :546
+  pk_advance(t, pr, deck);                                           // :547-616
+  if (t.done && !prev_done) {                                        // :619-622
+    pk_fold_winner(t, pr);
+    pk_showdown(t, pr, deck, evw);
+  }
+  if (t.done) {                                                      // :625-628
+#pragma unroll
+    for (int s = 0; s < MAXP; ++s) { t.crb[s] = 0; t.inv[s] = 0; }
+    t.highest = 0;
+  }
+  const float reward = legal ? pk_reward(t, pr, a, e, prev_inv) : 0.0f;   // :631-632
+  return PackedStepResult{reward, prev_done, t.done};
+}
+
 template <int MAXP, bool POLICY = false, int AUTO = 1, class ActT = int64_t>
 PULSE_HD PackedStepResult packed_step_core(const PulsePokerPacked& S, const PokerParams& pr, const ActT* __restrict__ actions,
                                            int auto_reset, uint64_t seed, uint64_t env_base, int starting_bbs, int max_bbs,
@@ -410,33 +441,12 @@ PULSE_HD PackedStepResult packed_step_core(const PulsePokerPacked& S, const Poke
     return PackedStepResult{0.0f, true, false};
   }
   const PokerTable<MAXP> t0 = t;
-  const PackedDeck deck{fb, 2 * AP};
-  const bool prev_done = t.done;
-  const int actor = t.idx;                                           // :531
-  const bool legal = pk_status(t.st, actor) == PK_ACTIVE && !prev_done;  // :532-537
-  const int prev_inv = pk_sel(t.crb, actor);                         // :539
+  int prev_inv = 0;
+  const PackedStepResult r = packed_step_regs<MAXP>(t, fb, evw, pr, a, prev_inv);
   if (S.prev_invested) S.prev_invested[g] = prev_inv;
-  // the reference refreshes its equity cache here when the street has changed since the last step (:542);
-  // the packed layout only remembers for which street the cache stands
-  if (t.stage >= 1 && t.stage <= 3) t.eq_stage = t.stage;
-  float e = 0.5f;
-  if (legal)  // the reward is zeroed otherwise (:632), so the equity is only needed for legal actors
-    e = (t.stage >= 1 && t.stage <= 3) ? pkp_equity_from(evw.word(actor), t.stage) : 0.5f;
-  pk_execute(t, a);                                                  // :546
-  pk_advance(t, pr, deck);                                           // :547-616
-  if (t.done && !prev_done) {                                        // :619-622
-    pk_fold_winner(t, pr);
-    pk_showdown(t, pr, deck, evw);
-  }
-  if (t.done) {                                                      // :625-628
-#pragma unroll
-    for (int s = 0; s < MAXP; ++s) { t.crb[s] = 0; t.inv[s] = 0; }
-    t.highest = 0;
-  }
-  const float reward = legal ? pk_reward(t, pr, a, e, prev_inv) : 0.0f;   // :631-632
   packed_store(t, t0, S, g, n, AP);
   if (S.idx && t.idx != t0.idx) S.idx[g] = t.idx;
-  return PackedStepResult{reward, prev_done, t.done};
+  return r;
 }
 
 // The step with the reference's own outputs: float32 observation row (:633), reward and done arrays.

@@ -215,6 +215,26 @@ class PokerGPUPacked(gym.Env):
         self._stepped = True
         return self.obs, rewards, done, chosen
 
+    def rollout_actions(self, actions):
+        """K steps in ONE launch on supplied actions (pulse_poker_packed_rollout_actions): actions uint8 [K, N] ->
+        (obs after the last step, rewards float32 [K, N], dones bool [K, N]) -- what K step() calls would return one
+        after another (no auto_reset: finished tables idle, as in the reference)."""
+        a = torch.as_tensor(actions, device=self.device)
+        if a.dim() != 2 or a.shape[1] != self.n_games:
+            raise ValueError(f"actions must have shape (K, {self.n_games}), got {tuple(a.shape)}")
+        if a.dtype != torch.uint8 or not a.is_contiguous():
+            a = torch.where(a < 0, torch.full_like(a, 255), a.clamp(max=13)).to(torch.uint8).contiguous()
+        K, N, dev = int(a.shape[0]), self.n_games, self.device
+        rewards = torch.empty((K, N), dtype=torch.float32, device=dev)
+        done = torch.empty((K, N), dtype=torch.bool, device=dev)
+        cfg = self._config()
+        with _lib.device_guard(dev):
+            _lib.check(self._lib.pulse_poker_packed_rollout_actions(
+                C.byref(self._packed), C.byref(cfg), ptr(a), c_i(K), ptr(self.obs), ptr(rewards), ptr(done),
+                _lib.cuda_stream(dev)), "pulse_poker_packed_rollout_actions")
+        self._stepped = True
+        return self.obs, rewards, done
+
     def enumerated_strength(self):
         """float32 [N, active_players]: river hand strength averaged over the board cards still to come, per seat
         (see include/pulse_envs.h).  An optional reward input; step() keeps the reference's proxy."""

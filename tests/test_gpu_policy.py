@@ -119,3 +119,32 @@ def test_rollout_equals_k_policy_steps(P, auto, cuda_device):
     sa, sb = a.unpack(), b.unpack()
     for f in sa:
         np.testing.assert_array_equal(sa[f].cpu().numpy(), sb[f].cpu().numpy(), err_msg=f)
+
+
+@pytest.mark.parametrize("P,N", [(2, 10_007), (6, 3_001), (10, 1_025)])
+def test_rollout_on_supplied_actions_equals_k_steps(P, N, cuda_device):
+    """pulse_poker_packed_rollout_actions: the table is loaded once, stepped K times in registers and stored once; rewards,
+    done flags, the final observation and the whole final state must equal K single-step launches on the same actions
+    (negative and oversized action ids included)."""
+    from pulselib_b200.envs.poker_packed import PokerGPUPacked
+
+    kw = dict(n_players=P, max_players=P, n_games=N, starting_bbs=60, max_bbs=400, w1=.5, w2=.3, K=100, alpha=50, seed=9,
+              env_base=123, track_prev_invested=True)
+    a, b = PokerGPUPacked(cuda_device, **kw), PokerGPUPacked(cuda_device, **kw)
+    K = 4 * P + 3
+    g = torch.Generator(device=cuda_device).manual_seed(P)
+    for hand in range(2):
+        a.reset(); b.reset()
+        acts = torch.randint(-1, 15, (K, N), generator=g, device=cuda_device)
+        obs, rew, done = a.rollout_actions(acts)
+        for k in range(K):
+            o2, r2, d2, _, _ = b.step(acts[k])
+            assert torch.equal(rew[k], r2), f"hand {hand} step {k}: rewards"
+            assert torch.equal(done[k], d2), f"hand {hand} step {k}: done flags"
+        assert torch.equal(obs, o2)
+        sa, sb = a.unpack(), b.unpack()
+        for f in sa:
+            assert torch.equal(sa[f], sb[f]), f"hand {hand}: state field {f}"
+        assert torch.equal(a._prev_inv, b._prev_inv) and torch.equal(a._idx, b._idx)
+        assert torch.equal(a._ev[:, :], b._ev[:, :])
+    assert bool(done.any()) and not bool(done[0].all())
