@@ -2,8 +2,16 @@
 // stores: value = (category << 12) + rank_in_category, category 1 high card .. 9 straight flush,
 // rank ascending with strength (category sizes 1277, 2860, 858, 858, 10, 1277, 156, 156, 10).
 // The reference walks a 130 MB table with 7 dependent gathers per seat
-// (/root/reference/environments/Poker/PokerGPU.py:437-444, :477-478); on B200 the same integers are
-// computed from four 13-bit suit masks in registers (~100 ALU ops, no memory traffic).  The table
+// (/root/reference/environments/Poker/PokerGPU.py:437-444, :477-478); on B200 the same integers come from
+// four 13-bit suit masks in registers and at most ONE read of a small table that stays in L1:
+//   all ranks distinct, no flush (high card / straight): pe_tab_unique[rank mask]            16 KB
+//   flush / straight flush:                              pe_tab_flush[the suit's rank mask]  16 KB
+//   one pair:                                            pe_tab_kick3[kickers, pair squeezed out]  8 KB
+//   two pair, trips, full house, quads: a handful of integer operations, no table.
+// The tables (tools/gen_eval_tables.py -> poker_eval_tables.inc) replaced the combinatorial-number-system arithmetic the
+// first version did in registers: a warp's 32 hands fall into five or six categories, every category's code runs for
+// the whole warp, and the binomials of the high-card and pair branches alone were a third of the deal kernel's
+// instructions (profiles/r2t_reset_raw.csv: the evaluator was 59% of the whole-batch reset).  The table
 // generator (handranks_gen.cpp) uses this very function for its leaves, and the tests check it
 // against an independent brute-force evaluator in oracle/.
 //
@@ -14,6 +22,21 @@
 #define __host__
 #define __device__
 #define __forceinline__ inline
+#endif
+
+// one copy for host code and, under nvcc, one in device memory (read through the non-coherent path: L1-resident)
+#define PE_TAB(name, n) static const uint16_t name##_h[n]
+#include "poker_eval_tables.inc"
+#undef PE_TAB
+#ifdef __CUDACC__
+#define PE_TAB(name, n) static __device__ const uint16_t name##_d[n]
+#include "poker_eval_tables.inc"
+#undef PE_TAB
+#endif
+#ifdef __CUDA_ARCH__
+#define PE_LOOKUP(name, i) ((int)__ldg(&name##_d[i]))
+#else
+#define PE_LOOKUP(name, i) ((int)name##_h[i])
 #endif
 
 __host__ __device__ __forceinline__ int pe_hb(uint32_t x) {  // index of highest set bit, x != 0
@@ -31,11 +54,6 @@ __host__ __device__ __forceinline__ int pe_popc(uint32_t x) {
 #endif
 }
 __host__ __device__ __forceinline__ int pe_c2(int b) { return (b * (b - 1)) >> 1; }
-__host__ __device__ __forceinline__ int pe_c3(int b) { return (b * (b - 1) * (b - 2)) / 6; }
-__host__ __device__ __forceinline__ int pe_c4(int b) { return (b * (b - 1) * (b - 2) * (b - 3)) / 24; }
-__host__ __device__ __forceinline__ int pe_c5(int b) {
-  return (b * (b - 1) * (b - 2) * (b - 3) * (b - 4)) / 120;
-}
 
 // Straight rank 1..10 (wheel = 1, broadway = 10) of a 13-bit rank mask, or 0.
 __host__ __device__ __forceinline__ int pe_straight(uint32_t m) {
@@ -44,29 +62,12 @@ __host__ __device__ __forceinline__ int pe_straight(uint32_t m) {
   return run ? pe_hb(run) + 1 : 0;
 }
 
-// Rank 1..1277 of the five highest bits of m among all non-straight 5-rank sets in ascending
-// strength (numeric order of the masks).  m must hold >= 5 bits and its top five must not be a
-// straight.
-__host__ __device__ __forceinline__ int pe_highcard_rank(uint32_t m) {
-  int b5 = pe_hb(m); m ^= 1u << b5;
-  int b4 = pe_hb(m); m ^= 1u << b4;
-  int b3 = pe_hb(m); m ^= 1u << b3;
-  int b2 = pe_hb(m); m ^= 1u << b2;
-  int b1 = pe_hb(m);
-  int comb = pe_c5(b5) + pe_c4(b4) + pe_c3(b3) + pe_c2(b2) + b1;
-  // straights numerically below: 6-high..(b5-high - 1) and, for ace-high sets, the wheel
-  return 1 + comb - (b5 - 4) - (b5 == 12);
-}
-
 // any/pairs/trips/quads: rank masks with count >= 1 / == 2 / == 3 / == 4; flush: rank mask of the
 // suit holding >= 5 cards, else 0.
 __host__ __device__ __forceinline__ int pe_eval_core(uint32_t any, uint32_t pairs, uint32_t trips,
                                                      uint32_t quads, uint32_t flush) {
-  if (flush) {
-    int sf = pe_straight(flush);
-    if (sf) return (9 << 12) + sf;
-    return (6 << 12) + pe_highcard_rank(flush);
-  }
+  if (flush) return PE_LOOKUP(pe_tab_flush, flush & 0x1FFFu);               // straight flush (9) or flush (6)
+  if (!(pairs | trips | quads)) return PE_LOOKUP(pe_tab_unique, any & 0x1FFFu);  // straight (5) or high card (1)
   if (quads) {
     int q = pe_hb(quads);
     int k = pe_hb(any & ~(1u << q));
@@ -77,7 +78,7 @@ __host__ __device__ __forceinline__ int pe_eval_core(uint32_t any, uint32_t pair
     int p = pe_hb((trips & ~(1u << t)) | pairs);
     return (7 << 12) + t * 12 + (p - (p > t)) + 1;
   }
-  int st = pe_straight(any);
+  int st = pe_straight(any);            // six or seven cards: a straight next to a pair / two pair / trips
   if (st) return (5 << 12) + st;
   if (trips) {
     int t = pe_hb(trips);
@@ -94,16 +95,11 @@ __host__ __device__ __forceinline__ int pe_eval_core(uint32_t any, uint32_t pair
     k -= (k > p1) + (k > p2);
     return (3 << 12) + (pe_c2(p1) + p2) * 11 + k + 1;
   }
-  if (pairs) {
-    int p = pe_hb(pairs);
-    uint32_t s = any & ~(1u << p);
-    int k1 = pe_hb(s); s ^= 1u << k1;
-    int k2 = pe_hb(s); s ^= 1u << k2;
-    int k3 = pe_hb(s);
-    k1 -= (k1 > p); k2 -= (k2 > p); k3 -= (k3 > p);
-    return (2 << 12) + p * 220 + pe_c3(k1) + pe_c2(k2) + k3 + 1;
-  }
-  return (1 << 12) + pe_highcard_rank(any);
+  // one pair: the three best kickers, numbered as if the pair's rank did not exist
+  int p = pe_hb(pairs);
+  uint32_t s = any & ~(1u << p);
+  s = (s & ((1u << p) - 1u)) | ((s >> (p + 1)) << p);
+  return (2 << 12) + p * 220 + PE_LOOKUP(pe_tab_kick3, s & 0xFFFu) + 1;
 }
 
 // Evaluates 5..7 distinct cards given as four per-suit rank masks.

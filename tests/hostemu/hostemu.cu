@@ -153,6 +153,32 @@ int emu_poker_unpack_full(const PulsePokerPacked* st, const PulsePokerState* com
   return 0;
 }
 
+// the computed evaluator (csrc/poker_eval.cuh) against a HandRanks table walk over every stride-th n-card hand in
+// lexicographic order; returns the number of disagreements, *checked = hands compared
+long long emu_eval_vs_table(const int32_t* hr, int n_cards, int stride, long long* checked) {
+  int c[7];
+  long long bad = 0, seen = 0, idx = 0;
+  for (int i = 0; i < n_cards; ++i) c[i] = i + 1;
+  for (;;) {
+    if (idx % stride == 0) {
+      uint64_t m = 0;
+      int p = 53;
+      for (int i = 0; i < n_cards; ++i) { m = pe_add_card64(c[i], m); p = hr[p + c[i]]; }
+      if (n_cards < 7) p = hr[p];
+      bad += pe_eval_mask64(m) != p;
+      ++seen;
+    }
+    ++idx;
+    int k = n_cards - 1;
+    while (k >= 0 && c[k] == 52 - (n_cards - 1 - k)) --k;
+    if (k < 0) break;
+    ++c[k];
+    for (int j = k + 1; j < n_cards; ++j) c[j] = c[j - 1] + 1;
+  }
+  if (checked) *checked = seen;
+  return bad;
+}
+
 // ---- Blackjack ----
 int emu_blackjack_reset(uint32_t* st, uint8_t* deck, const uint8_t* injected, uint64_t seed, uint64_t env_base,
                         uint32_t episode, int32_t* obs, int32_t* rewards, uint8_t* terminated, int n) {
