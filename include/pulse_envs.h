@@ -325,6 +325,15 @@ int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const Pul
 int pulse_poker_packed_showdown_equity(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* equity_out,
                                        int preflop_samples, uint64_t seed, uint64_t env_base, uint32_t counter,
                                        pulse_stream_t stream);
+/* reference-shaped tensors -> packed (SURVEY.md 8(b) pulse_poker_pack): puts state that was edited through the
+ * reference's attributes back onto the throughput layout.  Needs every state tensor of `compat` (equities,
+ * equity_dirty, prev_invested, sb, bb optional).  The visible board comes from `board`, the cards still to come from
+ * `decks`, the per-deal hand values are recomputed, hand_ctr is left alone.  *bad_count_or_null (device int) is
+ * incremented for every table the packed layout cannot express exactly -- deck position other than the street's
+ * (2 AP + 0 / 4 / 6 / 8), a board card beyond the street's visible ones, a card outside 1..52, seat / status / street
+ * numbers out of range -- such a table is stored with the offending field forced into range and must not be trusted. */
+int pulse_poker_pack(const PulsePokerState* compat, const PulsePokerPacked* st, const PulsePokerConfig* cfg,
+                     int* bad_count_or_null, pulse_stream_t stream);
 /* packed -> reference-shaped tensors.  Writes every field of `compat` whose pointer is non-NULL except decks
  * (a pure function of the deal, see pulse_poker_unpack_full) and prev_invested.  sb / bb follow from button and
  * active_players (PokerGPU.py:123-128); equities / equity_dirty are the reference's cache as it stands after the

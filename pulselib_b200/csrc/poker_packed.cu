@@ -293,6 +293,18 @@ poker_packed_unpack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr
     packed_unpack_one<MAXP>(S, C, pr, g, n, with_decks, prefixed, seed, env_base, fresh);
 }
 
+template <int MAXP>
+__global__ void __launch_bounds__(kBlock)
+poker_packed_pack_kernel(PulsePokerPacked S, PulsePokerState C, PokerParams pr, long long n, int* __restrict__ bad) {
+  int mine = 0;
+  for (long long g = (long long)blockIdx.x * kBlock + threadIdx.x; g < n; g += (long long)gridDim.x * kBlock)
+    mine += packed_pack_one<MAXP>(S, C, pr, g, n) ? 0 : 1;
+  if (bad) {
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(bad, mine);
+  }
+}
+
 // one thread per (table, seat): seat-major so a warp reads 32 consecutive tables' hole cards and table words
 __global__ void __launch_bounds__(kBlock)
 poker_packed_strength_kernel(PulsePokerPacked S, int AP, float* __restrict__ out, long long n) {
@@ -622,6 +634,23 @@ int pulse_poker_packed_showdown_equity(const PulsePokerPacked* st, const PulsePo
   PKP_DISPATCH(pr.P, (poker_packed_showdown_equity_kernel<MP><<<grid, kBlock, 0, stream>>>(
                          *st, pr, preflop_samples, seed, env_base, counter, equity_out, (long long)cfg->n_games)));
   return pulse_check_launch("pulse_poker_packed_showdown_equity");
+}
+
+int pulse_poker_pack(const PulsePokerState* compat, const PulsePokerPacked* st, const PulsePokerConfig* cfg,
+                     int* bad_count_or_null, cudaStream_t stream) {
+  int rc = check_cfg(st, cfg);
+  if (rc) return rc;
+  PULSE_REQUIRE(compat != nullptr, "compat state is null");
+  if (cfg->n_games == 0) return PULSE_OK;
+  PULSE_REQUIRE(compat->decks && compat->deck_positions && compat->board && compat->pots && compat->stages && compat->stacks &&
+                    compat->hands && compat->current_round_bet && compat->total_invested && compat->status && compat->button &&
+                    compat->idx && compat->highest && compat->agg && compat->acted && compat->last_raise_size && compat->is_done,
+                "pack needs every state tensor (equities, equity_dirty, prev_invested, sb, bb are optional)");
+  PokerParams pr = make_params(cfg);
+  const int grid = pulse_grid_for(cfg->n_games, kBlock);
+  PKP_DISPATCH(pr.P, (poker_packed_pack_kernel<MP><<<grid, kBlock, 0, stream>>>(*st, *compat, pr, (long long)cfg->n_games,
+                                                                               bad_count_or_null)));
+  return pulse_check_launch("pulse_poker_pack");
 }
 
 int pulse_poker_packed_enumerated_strength(const PulsePokerPacked* st, const PulsePokerConfig* cfg, float* strength_out,

@@ -507,6 +507,96 @@ PULSE_HD void packed_reset_one(const PulsePokerPacked& S, const PokerParams& pr,
                          g, n, dk);
 }
 
+// reference-shaped tensors -> packed: the inverse of packed_unpack_one (SURVEY 8(b) pulse_poker_pack), for state that was
+// edited through the reference's attributes (white-box tests, hand-written positions) and should go back onto the
+// throughput layout.  The packed layout holds less than the tensors can express, so the function says whether the
+// table was representable: deck position as the street implies (2 AP + 0 / 4 / 6 / 8), no board card beyond the
+// street's visible ones, cards 1..52 for dealt seats, seat / status / street numbers in range.  The visible board is
+// taken from `board` (authoritative after an edit), the cards still to come from `decks`; the per-deal hand-value
+// words are recomputed; the equity cache's street is the one whose values the `equities` tensor holds (when given),
+// else the street itself (one before it when equity_dirty).  hand_ctr is left alone.
+template <int MAXP>
+PULSE_HD bool packed_pack_one(const PulsePokerPacked& S, const PulsePokerState& C, const PokerParams& pr, long long g,
+                              long long n) {
+  const int P = pr.P, AP = pr.AP;
+  bool ok = true;
+  PokerTable<MAXP> t;
+  const int stage = C.stages[g];
+  ok &= stage >= 0 && stage <= 5;
+  t.stage = stage & 7;
+  t.idx = C.idx[g]; t.agg = C.agg[g]; t.button = C.button[g]; t.acted = C.acted[g];
+  ok &= t.idx >= 0 && t.idx < AP && t.agg >= 0 && t.agg < 16 && t.button >= 0 && t.button < AP && t.acted >= 0;
+  t.idx &= 15; t.agg &= 15; t.button &= 15;
+  if (t.acted < 0) t.acted = 0;
+  t.done = C.is_done[g] != 0;
+  t.pot = C.pots[g]; t.highest = C.highest[g]; t.last_raise = C.last_raise_size[g];
+  uint32_t st = 0xFFFFFFFFu;
+#pragma unroll
+  for (int s = 0; s < MAXP; ++s) {
+    t.stack[s] = 0; t.crb[s] = 0; t.inv[s] = 0; t.hole0[s] = -1; t.hole1[s] = -1;
+    if (s < P) {
+      const long long off = g * P + s;
+      t.stack[s] = C.stacks[off]; t.crb[s] = C.current_round_bet[off]; t.inv[s] = C.total_invested[off];
+      const int v = C.status[off];
+      ok &= v >= 0 && v <= 3 && (s < AP || v == PK_SITOUT);
+      st = pk_set_status(st, s, v & 3);
+      const int h0 = C.hands[2 * off], h1 = C.hands[2 * off + 1];
+      if (s < AP) { ok &= h0 >= 1 && h0 <= 52 && h1 >= 1 && h1 <= 52; t.hole0[s] = h0; t.hole1[s] = h1; }
+      else ok &= h0 == -1 && h1 == -1;
+    }
+  }
+  t.st = st;
+  const int vis = stage == 0 ? 0 : stage == 1 ? 3 : stage == 2 ? 4 : 5;
+  const int dpos = 2 * AP + (stage == 0 ? 0 : stage == 1 ? 4 : stage == 2 ? 6 : 8);
+  ok &= C.deck_positions[g] == dpos;
+  const int32_t* deck = C.decks + g * 52;
+  const int b0 = 2 * AP;
+  int card[5] = {deck[b0 + 1], deck[b0 + 2], deck[b0 + 3], deck[b0 + 5], deck[b0 + 7]};
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int b = C.board[g * 5 + i];
+    if (i < vis) { ok &= b >= 1 && b <= 52; card[i] = b; }
+    else ok &= b == -1;
+    ok &= card[i] >= 1 && card[i] <= 52;
+    card[i] &= 63;
+  }
+  const uint32_t fb = (uint32_t)card[0] | ((uint32_t)card[1] << 6) | ((uint32_t)card[2] << 12) | ((uint32_t)card[3] << 18) |
+                      ((uint32_t)card[4] << 24);
+  // hand values of every dealt seat on the flop, turn and river boards (as packed_deal)
+  const uint64_t flop = pe_add_card64(card[2], pe_add_card64(card[1], pe_add_card64(card[0], 0)));
+  const uint64_t turn = pe_add_card64(card[3], flop), river = pe_add_card64(card[4], turn);
+  for (int s = 0; s < AP; ++s) {
+    const uint64_t h = pe_add_card64(pk_sel(t.hole1, s), pe_add_card64(pk_sel(t.hole0, s), 0));
+    const int v5 = pe_eval_mask64(h | flop), v6 = pe_eval_mask64(h | turn), v7 = pe_eval_mask64(h | river);
+    const int f = (v5 >= 0 && v5 < S.n_hand_ranks) ? PULSE_LDG(S.hand_ranks + v5) : 0;
+    S.ev[(long long)s * n + g] = (uint64_t)(uint32_t)v7 | ((uint64_t)(uint32_t)v6 << 16) | ((uint64_t)(uint32_t)f << 32);
+  }
+  // the street the reference's equity cache stands for
+  int eq = 0;
+  if (stage >= 1 && stage <= 3) eq = (C.equity_dirty && C.equity_dirty[g]) ? stage - 1 : stage;
+  else if (stage >= 4) eq = 3;
+  if (C.equities) {
+    int found = -1;
+    for (int k = 0; k < 5 && found < 0; ++k) {
+      const int cand = k == 0 ? eq : k - 1;
+      bool same = true;
+      for (int s = 0; s < AP; ++s) {
+        const float want = cand == 0 ? 0.5f : pkp_equity_from(S.ev[(long long)s * n + g], cand);
+        same &= C.equities[g * AP + s] == want;
+      }
+      if (same) found = cand;
+    }
+    if (found >= 0) eq = found;
+  }
+  t.eq_stage = eq;
+  t.deck_pos = dpos; t.dirty = false;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) t.board[i] = i < vis ? card[i] : -1;
+  packed_store_all(t, fb, S, g, n, P);
+  if (S.prev_invested) S.prev_invested[g] = C.prev_invested ? C.prev_invested[g] : 0;
+  return ok;
+}
+
 // ---- enumerated hand strength ---------------------------------------------------------
 // The reference's equity is a table-walk proxy that its own notes call a known weakness
 // (/root/reference/rl/depth_notes.txt:302-333): on the turn and flop it feeds 6- and 5-card table values through

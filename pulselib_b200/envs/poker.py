@@ -392,6 +392,35 @@ class PokerGPU(PokerGPUCompat):
         if d["prev_invested"] is None:
             d["prev_invested"] = torch.zeros(self.n_games, dtype=torch.int32, device=self.device)
 
+    def repack(self) -> bool:
+        """Back onto the packed throughput layout after the reference-shaped tensors were edited (white-box tests,
+        hand-written positions): pulse_poker_pack.  Returns False -- and carries on reference-shaped -- when some table
+        is not expressible in the packed layout (e.g. a deck position the street does not imply), when
+        `calculate_equities` was replaced on the instance, or when the env was built reference-shaped for good."""
+        d = self.__dict__
+        if d["_mode"] == "packed":
+            return bool(d["_eng_live"])
+        if d["_force_compat"] or d["_eng"] is None or "calculate_equities" in d or d.get("stacks") is None:
+            return False
+        eng, N = d["_eng"], self.n_games
+        eng.active_players = int(self.active_players)
+        for n in ("w1", "w2", "K", "alpha"):
+            setattr(eng, n, d["_host_" + n])
+        if eng.pack_from(self._state()) != 0:
+            return False
+        eng._stack.copy_(self._tensor("stacks", torch.int32).t())       # seats beyond active_players keep their chips
+        eng._prefixed = self._tensor("decks", torch.int32)              # the mirror hands these decks back
+        eng.obs = d["obs"]
+        done = self._tensor("is_done", torch.bool)
+        for n in _MIRROR + _DERIVED:
+            d.pop(n, None)
+        d["_ver"], d["_materialised"], d["_touched"] = {}, None, False
+        d["stacks"], d["idx"], d["prev_invested"] = eng._stack.t(), eng._idx, eng._prev_inv
+        d["is_done"] = done
+        d["_mode"], d["_eng_live"] = "packed", True
+        self._record_live()
+        return True
+
     # ---- reset / step -------------------------------------------------------------------------------------------
     def reset(self, seed=None, options=None, rotation=0):
         d = self.__dict__

@@ -312,6 +312,19 @@ class PokerGPUPacked(gym.Env):
                                                         _lib.cuda_stream(dev)), "pulse_poker_unpack")
         return out
 
+    def pack_from(self, state) -> int:
+        """Reference-shaped state -> the packed layout (pulse_poker_pack), e.g. after edits made through the reference's
+        attributes.  `state`: a ctypes _State (envs/poker.py) of device tensors of the reference's shapes / dtypes.
+        Returns the number of tables the packed layout cannot express (0 = all good); reads that count back, so it
+        synchronises the stream."""
+        bad = torch.zeros(1, dtype=torch.int32, device=self.device)
+        cfg = self._config()
+        with _lib.device_guard(self.device):
+            _lib.check(self._lib.pulse_poker_pack(C.byref(state), C.byref(self._packed), C.byref(cfg), ptr(bad),
+                                                  _lib.cuda_stream(self.device)), "pulse_poker_pack")
+        self._stepped = True
+        return int(bad.item())
+
     def unpack(self, fields=None) -> dict:
         """Reference-shaped int32 snapshot of the packed state (one kernel launch)."""
         return self.unpack_into(self.alloc_mirror(fields if fields is not None else _SNAPSHOT))

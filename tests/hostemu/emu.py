@@ -160,6 +160,12 @@ class EmuPokerPacked(EmuPoker):
         return self.obs, self.rewards, self.is_done.astype(bool)
 
 
+    def pack_from_mirror(self):
+        """csrc/poker_packed_body.cuh::packed_pack_one on the host: the reference-shaped arrays of this object -> the
+        packed arrays; returns the number of tables the packed layout could not express."""
+        s, c = self._packed(), self._state()
+        return int(lib().emu_poker_pack(C.byref(c), C.byref(s), C.byref(self.cfg)))
+
     def showdown_equity(self, samples=256, counter=0, lanes=1):
         """csrc/poker_packed_body.cuh::packed_showdown_equity_part on the host, boards split over `lanes` workers"""
         out = np.zeros((self.n_games, self.active_players), np.float32)

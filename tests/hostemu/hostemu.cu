@@ -138,6 +138,16 @@ int emu_showdown_equity(const PulsePokerPacked* st, const PulsePokerConfig* cfg,
 #undef EMU_EQ
   return 0;
 }
+int emu_poker_pack(const PulsePokerState* compat, const PulsePokerPacked* st, const PulsePokerConfig* cfg) {
+  PokerParams pr = mk(cfg);
+  int bad = 0;
+  for (long long g = 0; g < cfg->n_games; ++g) {
+    bool ok = true;
+    EMU_DISPATCH(pr.P, (ok = packed_pack_one<MP>(*st, *compat, pr, g, (long long)cfg->n_games)));
+    bad += ok ? 0 : 1;
+  }
+  return bad;
+}
 int emu_poker_unpack(const PulsePokerPacked* st, const PulsePokerState* compat, const PulsePokerConfig* cfg) {
   PokerParams pr = mk(cfg);
   for (long long g = 0; g < cfg->n_games; ++g)
