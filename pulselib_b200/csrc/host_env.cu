@@ -113,7 +113,7 @@ struct PulsePokerHostEnv {
   // callbacks cost 20-50 us each and are run one at a time by a thread the spinning workers can starve).
   uint32_t* d_flag = nullptr; volatile uint32_t* h_flag = nullptr;
   uint32_t epoch = 0;
-  std::vector<uint32_t> prev_live;         // the live mask as it was when the previous call began (reward zeroing)
+  std::vector<uint32_t> prev_live;         // the live mask as it was when the last call began (= which tables have a record)
   std::atomic<int>* remaining = nullptr;   // per chunk: workers still expanding it (the last one rebuilds its offsets)
   pulse_host::Pool* pool = nullptr;
   long long last_h2d = 0, last_d2h = 0;

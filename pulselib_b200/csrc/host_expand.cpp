@@ -48,7 +48,12 @@ __attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, i
   memcpy(reward, w + R - 1, 4);
 }
 
-#define EXPAND_BODY(ROW_CALL)                                                                                   \
+// One 32-table group at a time.  Rewards and done flags of the WHOLE group are rebuilt in two small local arrays --
+// a table that had already finished: reward 0 (PokerGPU.py:632), done 1, its observation row stays as it is -- and
+// written out as whole lines (STORE_GROUP), so the reward / done arrays are never read: storing only the live tables'
+// entries made every line of both arrays a read-for-ownership plus a write-back (40 MB of the ~190 MB a 4M-table
+// step moves through host memory).
+#define EXPAND_BODY(ROW_CALL, STORE_GROUP)                                                                      \
   const int R = a.row_words, W = a.obs_width;                                                                   \
   for (long long wg = a.g0 >> 5; wg < ((a.g1 + 31) >> 5); ++wg) {                                               \
     const long long gb = wg << 5;                                                                               \
@@ -56,12 +61,11 @@ __attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, i
     const uint32_t mask = a.fresh ? 0xFFFFFFFFu : a.live[wg];                                                   \
     uint32_t next = 0;                                                                                          \
     size_t slot = a.off ? a.off[wg - (a.chunk_first >> 5)] : (size_t)(gb - a.chunk_first);                      \
-    /* a table that finished on the previous step: reward 0 from now on (PokerGPU.py:632); done stays 1 and the   \
-       row stays as it is.  Tables finished earlier were zeroed then. */                                         \
     const uint32_t in_range = cnt == 32 ? 0xFFFFFFFFu : ((1u << cnt) - 1u);   /* the batch's last group may be short */ \
-    uint32_t z = a.fresh ? 0u : (a.prev_live[wg] & ~mask & in_range);                                            \
-    while (z) { a.reward[gb + __builtin_ctz(z)] = 0.0f; z &= z - 1; }                                            \
     a.prev_live[wg] = mask;                                                                                      \
+    alignas(32) float rw[32];                                                                                    \
+    alignas(32) uint8_t dn[32];                                                                                  \
+    for (int i = 0; i < 32; ++i) { rw[i] = 0.0f; dn[i] = 1; }                                                    \
     uint32_t m = mask & in_range;                                                                               \
     while (m) {                                                                                                 \
       const int b = __builtin_ctz(m);                                                                           \
@@ -71,21 +75,34 @@ __attribute__((target("avx2"))) inline void expand_row_avx2(const uint32_t* w, i
       ++slot;                                                                                                   \
       uint8_t d;                                                                                                \
       ROW_CALL;                                                                                                 \
-      a.done[g] = d;                                                                                            \
+      dn[b] = d;                                                                                                \
       next |= (uint32_t)(d ? 0u : 1u) << b;                                                                     \
     }                                                                                                           \
+    STORE_GROUP;                                                                                                \
     a.live[wg] = next;                                                                                          \
   }
 
+#define STORE_GROUP_PLAIN                                                            \
+  do {                                                                               \
+    memcpy(a.reward + gb, rw, (size_t)cnt * sizeof(float));                          \
+    memcpy(a.done + gb, dn, (size_t)cnt);                                            \
+  } while (0)
+
 void expand_range_portable(const PulseExpandArgs& a) {
-  EXPAND_BODY(expand_row_portable(w, W, R, a.obs + g * W, a.reward + g, &d))
+  EXPAND_BODY(expand_row_portable(w, W, R, a.obs + g * W, rw + b, &d), STORE_GROUP_PLAIN)
 }
 
 __attribute__((target("avx2"))) void expand_range_avx2(const PulseExpandArgs& a) {
   const bool line_rows = a.obs_width == 16 && (reinterpret_cast<uintptr_t>(a.obs) & 31u) == 0;
   const bool stream16 = !line_rows && (a.obs_width & 3) == 0 && (reinterpret_cast<uintptr_t>(a.obs) & 15u) == 0;
-  EXPAND_BODY(expand_row_avx2(w, W, R, a.obs + g * W, a.reward + g, &d, line_rows, stream16))
-  if (line_rows || stream16) _mm_sfence();
+  // whole groups on 32-byte aligned arrays: four streamed 32-byte pieces of rewards, one of done flags
+  const bool stream_rd = (reinterpret_cast<uintptr_t>(a.reward) & 31u) == 0 && (reinterpret_cast<uintptr_t>(a.done) & 31u) == 0;
+  EXPAND_BODY(expand_row_avx2(w, W, R, a.obs + g * W, rw + b, &d, line_rows, stream16),
+              if (stream_rd && cnt == 32) {
+                for (int i = 0; i < 4; ++i) _mm256_stream_ps(a.reward + gb + 8 * i, _mm256_load_ps(rw + 8 * i));
+                _mm256_stream_si256(reinterpret_cast<__m256i*>(a.done + gb), _mm256_load_si256(reinterpret_cast<const __m256i*>(dn)));
+              } else STORE_GROUP_PLAIN)
+  _mm_sfence();
 }
 
 bool have_avx2() {

@@ -6,8 +6,8 @@ struct PulseExpandArgs {
   const uint32_t* rows;     // the chunk's records (compacted in table order, or one per table when off == nullptr)
   const uint32_t* off;      // the chunk's per-32-table record offsets, or nullptr: slot = table - chunk_first
   uint32_t* live;           // whole-batch live mask, bit b of live[w] = table 32 w + b is not done; read, then rewritten
-  uint32_t* prev_live;      // the live mask as the PREVIOUS call found it: a table that was live then and is not now
-                            // finished on the previous step, so its reward (still that step's) is zeroed once; rewritten
+  uint32_t* prev_live;      // rewritten with the live mask as THIS call found it (= which tables have a record in this
+                            // call's output; pulse_poker_host_live_mask)
   long long chunk_first, g0, g1;   // tables [g0, g1) of the chunk starting at chunk_first (g0 a multiple of 32)
   int row_words, obs_width, max_players;
   float* obs; float* reward; uint8_t* done;
