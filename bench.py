@@ -386,6 +386,7 @@ def run_gpu(args, wl, name):
     assert int(stats_all[0].item()) == world * N * e2e_steps
     hinfo = henv.info()
     htime = henv.timing()
+    hchunks = [(round(1e3 * a / max(1.0, htime["calls"]), 4), round(1e3 * b / max(1.0, htime["calls"]), 4)) for a, b in henv.chunk_timing()]
     # the same loop with the packed records left unexpanded (pulse_poker_host_step_records): what the link and a
     # record-reading consumer can sustain when the host does not write 64 B of float32 per live table-step
     def record_steps(k):
@@ -435,6 +436,7 @@ def run_gpu(args, wl, name):
                            "reset every %d steps; records of live tables only cross PCIe and are expanded by host threads" % (env.obs_size, L),
                     "reference_contract_bytes_per_table_step": 8 + 4 * env.obs_size + 4 + 1,
                     "host_ms_per_step": {k: round(1e3 * v / max(1.0, htime["calls"]), 4) for k, v in htime.items() if k != "calls"},
+                    "chunk_ms_seen_done": hchunks,   # per chunk: ms into a call's expansion phase when its records were seen / expanded (last worker)
                     "timing": "wall clock around the host loop (the API is host-synchronous), device synchronised on both sides"},
             "e2e_records": {"value": rec_value, "unit": "env-steps/s",
                             "api": "PokerHostEnv.step_records (pulse_poker_host_step_records): same copies, the packed records stay "

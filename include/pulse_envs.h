@@ -394,6 +394,10 @@ int pulse_poker_host_info(const PulsePokerHostEnv* env, int* row_bytes, int* obs
  * GPU work, expansion phase (wall clock), worker seconds waiting for records, worker seconds expanding}; reset != 0
  * clears the counters */
 int pulse_poker_host_timing(PulsePokerHostEnv* env, double* out6, int reset);
+/* diagnostic: per chunk c, seconds (summed over the calls since the last timing reset) after a call's expansion phase
+ * began at which the last worker saw the chunk's records land (out[2 c]) and finished its slice (out[2 c + 1]); returns
+ * the number of chunks */
+int pulse_poker_host_chunk_timing(const PulsePokerHostEnv* env, double* out, int max_chunks);
 /* pure host function: n_rows packed records (pkw_row_words(M) 32-bit words each) -> float32 rows [n_rows, 13 + 3 (M - 1)],
  * rewards, dones.  vectorised != 0: through the host env's own expander (AVX2 when the CPU has it, see
  * pulse_poker_host_expand_isa), else the portable definition -- the two must agree bit for bit. */

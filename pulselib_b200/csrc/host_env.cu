@@ -120,6 +120,7 @@ struct PulsePokerHostEnv {
   // seconds, accumulated over calls: staging the actions, submitting GPU work, the expansion phase (wall), and summed
   // over workers: time spent waiting for records / time spent expanding
   double t_stage = 0, t_submit = 0, t_expand = 0, t_wait_sum = 0, t_work_sum = 0;
+  std::vector<double> t_chunk_seen, t_chunk_done;   // diagnostic: seconds after the expansion phase began at which the LAST worker saw chunk c land / finished its slice of it, summed over calls
   long long calls = 0;
   ~PulsePokerHostEnv() {
     delete pool;
@@ -237,6 +238,7 @@ int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* rewar
       }
       std::atomic_thread_fence(std::memory_order_acquire);
       const double w1 = now_s();
+      if (wk == T - 1) e->t_chunk_seen[c] += w1 - t0;
       const long long first = c * e->Nc, last = (first + e->Nc < e->N) ? first + e->Nc : e->N;
       const long long per = (((last - first) + T - 1) / T + 31) & ~31LL;
       const long long g0 = first + wk * per, g1 = (g0 + per < last) ? g0 + per : last;
@@ -251,6 +253,7 @@ int expand_chunks(PulsePokerHostEnv* e, bool compacted, float* obs, float* rewar
       }
       if (e->remaining[c].fetch_sub(1, std::memory_order_acq_rel) == 1) rebuild_offsets(e, c);
       const double w2 = now_s();
+      if (wk == T - 1) e->t_chunk_done[c] += w2 - t0;
       waits[wk] += w1 - w0; works[wk] += w2 - w1;
     }
   });
@@ -329,6 +332,7 @@ int pulse_poker_host_create(PulsePokerHostEnv** out, const PulsePokerConfig* cfg
     e->h_flag = hf;
   }
   e->prev_live.assign(N / 32 + 2, 0u);
+  e->t_chunk_seen.assign(e->chunks, 0.0); e->t_chunk_done.assign(e->chunks, 0.0);
   *out = e;
   return PULSE_OK;
 }
@@ -471,8 +475,21 @@ int pulse_poker_host_timing(PulsePokerHostEnv* e, double* out6, int reset) {
   PULSE_REQUIRE(e && out6, "null argument");
   out6[0] = (double)e->calls; out6[1] = e->t_stage; out6[2] = e->t_submit; out6[3] = e->t_expand;
   out6[4] = e->t_wait_sum; out6[5] = e->t_work_sum;
-  if (reset) { e->calls = 0; e->t_stage = e->t_submit = e->t_expand = e->t_wait_sum = e->t_work_sum = 0; }
+  if (reset) {
+    e->calls = 0; e->t_stage = e->t_submit = e->t_expand = e->t_wait_sum = e->t_work_sum = 0;
+    for (auto& v : e->t_chunk_seen) v = 0;
+    for (auto& v : e->t_chunk_done) v = 0;
+  }
   return PULSE_OK;
+}
+
+// diagnostic: per chunk, seconds (summed over the calls since the last timing reset, resets included) after the
+// expansion phase began at which the last worker saw the chunk's records land (out[2 c]) and finished its slice of it
+// (out[2 c + 1]); n_chunks entries are written, at most max_chunks
+int pulse_poker_host_chunk_timing(const PulsePokerHostEnv* e, double* out, int max_chunks) {
+  PULSE_REQUIRE(e && out, "null argument");
+  for (int c = 0; c < e->chunks && c < max_chunks; ++c) { out[2 * c] = e->t_chunk_seen[c]; out[2 * c + 1] = e->t_chunk_done[c]; }
+  return e->chunks;
 }
 
 // pure host function (no GPU): one record -> the reference's float32 row; exported for tests and for callers that

@@ -31,9 +31,11 @@ struct PulseTfeHostEnv {
   uint64_t* d_boards = nullptr; int64_t* d_score = nullptr; uint8_t* d_done = nullptr; uint8_t* d_act = nullptr;
   int32_t* d_reward = nullptr;
   uint64_t* h_boards = nullptr; uint8_t* h_act = nullptr; int32_t* h_reward = nullptr; uint8_t* h_done = nullptr;
-  // "chunk c has landed": a 4-byte host-to-host copy of the call's epoch, queued on the chunk's stream behind its
-  // device-to-host copies, which the workers poll in pinned memory
-  volatile uint32_t* h_flag = nullptr; uint32_t* h_epoch = nullptr;
+  // "chunk c has landed": the call's epoch goes to a device word at the head of the chunk's stream work and comes back
+  // with a 4-byte copy queued behind the chunk's device-to-host copies; the workers poll it in pinned memory.  (Both
+  // hops are real DMA copies: a host-to-host cudaMemcpyAsync is carried out by the calling thread once the stream has
+  // drained, which would turn the submission loop into a wait -- profiles/r2z_zerocopy_probe.jsonl, "dma_chain".)
+  volatile uint32_t* h_flag = nullptr; uint32_t* h_epoch = nullptr; uint32_t* d_flag = nullptr;
   uint32_t epoch = 0;
   std::vector<cudaStream_t> streams;
   std::vector<void*> dev_allocs, pin_allocs;
@@ -138,7 +140,8 @@ int pulse_tfe_host_create(PulseTfeHostEnv** out, long long n_envs, int side, int
   if ((rc = dev_alloc(e, &e->d_boards, N)) || (rc = dev_alloc(e, &e->d_score, N)) || (rc = dev_alloc(e, &e->d_done, N)) ||
       (rc = dev_alloc(e, &e->d_act, N)) || (rc = dev_alloc(e, &e->d_reward, N)) || (rc = pin_alloc(e, &e->h_boards, N)) ||
       (rc = pin_alloc(e, &e->h_act, N)) || (rc = pin_alloc(e, &e->h_reward, N)) || (rc = pin_alloc(e, &e->h_done, N)) ||
-      (rc = pin_alloc(e, &hf, (size_t)e->chunks + 32)) || (rc = pin_alloc(e, &e->h_epoch, 16)))
+      (rc = pin_alloc(e, &hf, (size_t)e->chunks + 32)) || (rc = pin_alloc(e, &e->h_epoch, 16)) ||
+      (rc = dev_alloc(e, &e->d_flag, (size_t)e->chunks + 32)))
     return fail(rc);
   e->h_flag = hf;
   for (int c = 0; c < e->chunks; ++c) {
@@ -166,10 +169,11 @@ int pulse_tfe_host_reset(PulseTfeHostEnv* e, int32_t* obs_host, uint8_t* done_ho
                              e->side, e->streams[0]);
     if (rc) return rc;
     cudaStream_t s = e->streams[0];
+    TH_CUDA(cudaMemcpyAsync(e->d_flag, e->h_epoch, 4, cudaMemcpyHostToDevice, s));
     TH_CUDA(cudaMemcpyAsync(e->h_boards, e->d_boards, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
     TH_CUDA(cudaMemsetAsync(e->d_reward, 0, (size_t)e->N * 4, s));
     for (int c = 0; c < e->chunks; ++c)
-      TH_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(e->h_flag) + c, e->h_epoch, 4, cudaMemcpyHostToHost, s));
+      TH_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(e->h_flag) + c, e->d_flag, 4, cudaMemcpyDeviceToHost, s));
     return 0;
   };
   memset(e->h_reward, 0, (size_t)e->N * 4);
@@ -205,6 +209,7 @@ int pulse_tfe_host_step(PulseTfeHostEnv* e, const void* actions_host, int action
     for (int c = 0; c < e->chunks; ++c) {
       const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
       cudaStream_t s = e->streams[c];
+      TH_CUDA(cudaMemcpyAsync(e->d_flag + c, e->h_epoch, 4, cudaMemcpyHostToDevice, s));
       TH_CUDA(cudaMemcpyAsync(e->d_act + first, e->h_act + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
       const int rc = pulse_tfe_step(e->d_boards + first, e->d_act + first, 1, nullptr, nullptr, e->seed, e->env_base + (uint64_t)first,
                                     e->t, nullptr, e->auto_reset, nullptr, e->d_reward + first, e->d_done + first,
@@ -213,7 +218,7 @@ int pulse_tfe_host_step(PulseTfeHostEnv* e, const void* actions_host, int action
       TH_CUDA(cudaMemcpyAsync(e->h_boards + first, e->d_boards + first, (size_t)cnt * 8, cudaMemcpyDeviceToHost, s));
       TH_CUDA(cudaMemcpyAsync(e->h_reward + first, e->d_reward + first, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s));
       TH_CUDA(cudaMemcpyAsync(e->h_done + first, e->d_done + first, (size_t)cnt, cudaMemcpyDeviceToHost, s));
-      TH_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(e->h_flag) + c, e->h_epoch, 4, cudaMemcpyHostToHost, s));
+      TH_CUDA(cudaMemcpyAsync(const_cast<uint32_t*>(e->h_flag) + c, e->d_flag + c, 4, cudaMemcpyDeviceToHost, s));
     }
     return 0;
   };

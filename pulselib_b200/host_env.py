@@ -108,6 +108,14 @@ class PokerHostEnv:
         keys = ("calls", "stage_s", "submit_s", "expand_wall_s", "worker_wait_s", "worker_expand_s")
         return dict(zip(keys, (float(v) for v in out)))
 
+    def chunk_timing(self):
+        """diagnostic: [(seconds until chunk c's records were seen, seconds until its slice was expanded)] summed over
+        the calls since timing(reset=True), as observed by the last worker, measured from the start of each call's
+        expansion phase"""
+        out = (C.c_double * 128)()
+        n = self._lib.pulse_poker_host_chunk_timing(self._h, out, C.c_int(64))
+        return [(out[2 * c], out[2 * c + 1]) for c in range(min(n, 64))]
+
     def close(self):
         if getattr(self, "_h", None):
             self._lib.pulse_poker_host_destroy(self._h)
