@@ -347,7 +347,8 @@ def run_gpu(args, wl, name):
     torch.cuda.empty_cache()
     henv = PokerHostEnv(dev, n_players=P, max_players=M, n_games=N, seed=SEED, env_base=rank * N, chunks=args.e2e_chunks,
                         threads=threads, **CFG)
-    h_act = np.random.default_rng(SEED + rank).integers(0, 13, (L, N)).astype(np.uint8)
+    h_act = PokerHostEnv.pinned_bytes((L, N))          # pinned host memory, as the contract's inputs are
+    h_act[...] = np.random.default_rng(SEED + rank).integers(0, 13, (L, N)).astype(np.uint8)
     h2d = d2h = 0
 
     def host_steps(k, start, count=False):

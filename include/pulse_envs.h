@@ -374,7 +374,9 @@ void pulse_poker_host_destroy(PulsePokerHostEnv* env);
  * obs_host == NULL: records only (every table's record is left in the pinned buffer, see pulse_poker_host_step_records) */
 int pulse_poker_host_reset(PulsePokerHostEnv* env, int active_players, int rotation, float* obs_host,
                            float* reward_host_or_null, uint8_t* done_host_or_null);
-/* step (:527-633); actions_host: uint8 [N] (action_bytes 1) or int64 [N] (action_bytes 8) */
+/* step (:527-633); actions_host: uint8 [N] (action_bytes 1) or int64 [N] (action_bytes 8).  A uint8 array that is
+ * page-locked (cudaHostAlloc / cudaHostRegister) is handed to the copy engine where it lies; anything else is staged
+ * into the env's own pinned buffer first. */
 int pulse_poker_host_step(PulsePokerHostEnv* env, const void* actions_host, int action_bytes, float* obs_host,
                           float* reward_host, uint8_t* done_host);
 /* The step without the float32 expansion, for consumers that read the packed records themselves (csrc/poker_wire.cuh; or

@@ -385,9 +385,18 @@ static int host_step_impl(PulsePokerHostEnv* e, const void* actions_host, int ac
   PULSE_REQUIRE(!e->first, "reset first");
   HE_CUDA(cudaSetDevice(e->device));
   const PokerParams pr = params_of(e->cfg);
-  // stage the actions in pinned memory as bytes
+  // stage the actions in pinned memory as bytes -- unless the caller's byte array is page-locked already (the copy
+  // engine can read it where it lies: 0.09 ms of a 2 ms step)
   const double t_stage0 = now_s();
-  e->pool->run([=](int wk) {
+  const uint8_t* act_src = e->h_act;
+  if (action_bytes == 1) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, actions_host) == cudaSuccess && at.type == cudaMemoryTypeHost)
+      act_src = static_cast<const uint8_t*>(actions_host);
+    else
+      (void)cudaGetLastError();   // an ordinary pageable pointer is not an error worth keeping
+  }
+  if (act_src == e->h_act) e->pool->run([=](int wk) {
     const int T = e->pool->size();
     const long long per = ((e->N + T - 1) / T + 63) & ~63LL;
     const long long a = wk * per, b = (a + per < e->N) ? a + per : e->N;
@@ -408,13 +417,13 @@ static int host_step_impl(PulsePokerHostEnv* e, const void* actions_host, int ac
     d2h += e->chunk_rows[c] * e->R * 4 + 4;
   }
   e->last_h2d = h2d; e->last_d2h = d2h; e->calls += 1;
-  auto submit = [e, pr]() -> int {
+  auto submit = [e, pr, act_src]() -> int {
     for (int c = 0; c < e->chunks; ++c) {
       const long long first = c * e->Nc, cnt = ((first + e->Nc < e->N) ? first + e->Nc : e->N) - first;
       const long long n_off = ((cnt + 31) >> 5) + 1;
       cudaStream_t s = e->streams[c];
       uint32_t* d_off = e->d_off + (first >> 5) + c;
-      HE_CUDA(cudaMemcpyAsync(e->d_act + first, e->h_act + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
+      HE_CUDA(cudaMemcpyAsync(e->d_act + first, act_src + first, (size_t)cnt, cudaMemcpyHostToDevice, s));
       HE_CUDA(cudaMemcpyAsync(d_off, e->h_off + (first >> 5) + c, (size_t)n_off * 4, cudaMemcpyHostToDevice, s));
       uint32_t* d_rows = e->d_wire + (size_t)first * e->R;
       int rc = launch_step(e, pr, first, cnt, d_off, d_rows, e->d_flag + c, s);

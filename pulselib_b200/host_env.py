@@ -16,6 +16,9 @@ from . import _lib, handranks
 from .envs.poker import _Config
 
 
+_PINNED_KEEPALIVE = []
+
+
 class PokerHostEnv:
     NUM_ACTIONS = 13
 
@@ -107,6 +110,17 @@ class PokerHostEnv:
         _lib.check(self._lib.pulse_poker_host_timing(self._h, out, C.c_int(1 if reset else 0)), "pulse_poker_host_timing")
         keys = ("calls", "stage_s", "submit_s", "expand_wall_s", "worker_wait_s", "worker_expand_s")
         return dict(zip(keys, (float(v) for v in out)))
+
+    @staticmethod
+    def pinned_bytes(shape):
+        """A page-locked uint8 numpy array (e.g. [steps, n_games] of actions): `step` hands rows of it to the copy
+        engine where they lie instead of staging them first."""
+        import torch
+
+        t = torch.empty(tuple(int(v) for v in np.atleast_1d(shape)), dtype=torch.uint8).pin_memory()
+        a = t.numpy()
+        _PINNED_KEEPALIVE.append(t)      # the array does not own the pinned allocation
+        return a
 
     def chunk_timing(self):
         """diagnostic: [(seconds until chunk c's records were seen, seconds until its slice was expanded)] summed over

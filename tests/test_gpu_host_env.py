@@ -175,3 +175,26 @@ def test_tfe_host_env_rejects_bad_arguments(cuda_device):
     env.reset()
     with pytest.raises(ValueError):
         env.step(np.zeros(63, np.uint8))
+
+
+def test_host_env_reads_pinned_byte_actions_in_place(cuda_device):
+    """a page-locked uint8 action array is copied from where it lies (no staging): same results as a pageable one"""
+    import numpy as np
+
+    from pulselib_b200.host_env import PokerHostEnv
+
+    N = 70_001
+    kw = dict(n_players=2, max_players=2, n_games=N, seed=5, env_base=3, chunks=3, threads=4, starting_bbs=100, w1=.5, w2=.3, K=100, alpha=50)
+    a, b = PokerHostEnv(cuda_device, **kw), PokerHostEnv(cuda_device, **kw)
+    acts = np.random.default_rng(1).integers(0, 13, (12, N)).astype(np.uint8)
+    pinned = PokerHostEnv.pinned_bytes((12, N))
+    pinned[...] = acts
+    a.reset(); b.reset()
+    for t in range(12):
+        oa, ra, da, _, _ = a.step(pinned[t])
+        ob, rb, db, _, _ = b.step(acts[t].copy())
+        np.testing.assert_array_equal(oa, ob, err_msg=f"step {t}")
+        np.testing.assert_array_equal(ra, rb)
+        np.testing.assert_array_equal(da, db)
+    assert a.timing()["stage_s"] < 0.25 * max(b.timing()["stage_s"], 1e-9) or a.timing()["stage_s"] < 1e-4
+    a.close(); b.close()
