@@ -254,18 +254,24 @@ def run_gpu(args, wl, name):
         else:
             env.reset()
 
+    # kernel time: CUDA events around every 5th step launch of the timed region (5 is coprime with the hand length, so
+    # every step index of a hand is sampled).  Events around EVERY launch cost 2.9% of the region themselves
+    # (profiles/r2ah_event_overhead.txt); PULSE_BENCH_EVENT_EVERY=1 restores that.
+    KERNEL_EVENT_EVERY = max(1, int(os.environ.get("PULSE_BENCH_EVENT_EVERY", "5")))
+
     def run_steps(k, start, pairs=None):
         for i in range(k):
             j = (start + i) % L
             if j == 0:
                 one_reset()
                 launches[0] += 1
-            if pairs is not None:
+            timed = pairs is not None and i % KERNEL_EVENT_EVERY == 0   # a sample of the launches: two event records per
+            if timed:                                                   # step are themselves 2-3% of a 0.12 ms step
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
             one_step(j)
             launches[0] += 1
-            if pairs is not None:
+            if timed:
                 e1.record(stream)
                 pairs.append((e0, e1))
 
@@ -449,6 +455,7 @@ def run_gpu(args, wl, name):
             "gpu_launches": n_launch,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "kernel": "poker_packed_step_kernel", "kernel_ms": kernel_ms,
+                         "kernel_time": "CUDA events around every %d%s step launch of the timed region (%d samples)" % (KERNEL_EVENT_EVERY, "th" if KERNEL_EVENT_EVERY != 1 else "st", len(pairs)),
                          "algorithmic_bytes_per_table_step": A, "peak_source": peak_src,
                          # the same fraction by the DRAM bytes ncu counted for one launch (profiles/traffic.json): the
                          # packed layout moves fewer bytes than the fixed algorithmic figure, so this is the one that

@@ -252,15 +252,17 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
         chunk = max(chunk, replicas)
 
     spc = int(spec.get("steps_per_call", 1))   # rollout workloads: one call (= one launch) plays this many steps
+    EVENT_EVERY = max(1, int(os.environ.get("PULSE_BENCH_EVENT_EVERY", "5"))) if spc == 1 else 1
 
     def eager(k, start, pairs=None):
-        for i in range(0, k, spc):
+        for n_call, i in enumerate(range(0, k, spc)):
             j = start + i
-            if pairs is not None:
+            timed = pairs is not None and n_call % EVENT_EVERY == 0   # a sample of the launches (see bench.py)
+            if timed:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
             step(envs[j % replicas], acts[j % L])
-            if pairs is not None:
+            if timed:
                 e1.record(stream)
                 pairs.append((e0, e1))
 
@@ -314,7 +316,7 @@ def measure(name, dev, rank, world, steps, warmup, n=None, dist=None):
     return dict(n=n, total_ms=total_ms, kernel_ms=kernel_ms, launches=launches, replicas=replicas, live_fraction=live_fraction,
                 mode=f"cuda graph of {chunk} steps" if graph is not None else "eager launches",
                 kernel_time="graph time / steps (includes inter-kernel gaps)" if graph is not None
-                else "CUDA events around each step launch",
+                else ("CUDA events around every %dth step launch of the timed region" % EVENT_EVERY if EVENT_EVERY > 1 else "CUDA events around each step launch"),
                 value=n * steps / (total_ms * 1e-3))
 
 
